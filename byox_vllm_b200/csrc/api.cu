@@ -1,0 +1,323 @@
+// C ABI of libb200attn.so (declared in include/b200attn.h): argument checking, TMA tensor-map
+// construction and kernel dispatch. No device allocation, no synchronisation, no host reads of
+// device memory => every entry point is CUDA-graph capturable.
+#include "../../include/b200attn.h"
+#include "common.h"
+
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <atomic>
+#include <mutex>
+#include <unordered_map>
+
+namespace b200 {
+static std::atomic<int64_t> g_launches{0};
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+}  // namespace b200
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+int cuda_fail(cudaError_t e, const char* what) {
+    snprintf(g_err, sizeof(g_err), "%s: %s (%s)", what, cudaGetErrorName(e), cudaGetErrorString(e));
+    return static_cast<int>(e);
+}
+
+bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+// ---- cuTensorMapEncodeTiled through the runtime's driver entry point (no -lcuda link) ----------
+using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                   const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = [] {
+        void* sym = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault,
+                                                &qres);
+        if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess) {
+            (void)cudaGetLastError();
+            return static_cast<EncodeTiledFn>(nullptr);
+        }
+        return reinterpret_cast<EncodeTiledFn>(sym);
+    }();
+    return fn;
+}
+
+struct MapKey {
+    const void* base;
+    int64_t num_slots;
+    int32_t num_kv_heads;
+    bool operator==(const MapKey& o) const {
+        return base == o.base && num_slots == o.num_slots && num_kv_heads == o.num_kv_heads;
+    }
+};
+struct MapKeyHash {
+    size_t operator()(const MapKey& k) const {
+        return std::hash<const void*>()(k.base) ^ (std::hash<int64_t>()(k.num_slots) * 1315423911u) ^
+               (static_cast<size_t>(k.num_kv_heads) << 20);
+    }
+};
+
+// A paged cache [num_slots, Hkv, 128] bf16 as a 3-D tensor map (dims fastest-first: 128, Hkv,
+// num_slots), box = 64 dims x 1 head x 64 tokens, SWIZZLE_128B. Encoding is pure host work; the
+// 128-byte descriptors are cached per cache view (nanovllm allocates the KV cache once,
+// model_runner.py:137, and every layer view keeps its address for the life of the engine).
+int get_cache_map(const void* base, int32_t num_kv_heads, int64_t num_slots, CUtensorMap* out) {
+    static std::mutex mu;
+    static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
+    const MapKey key{base, num_slots, num_kv_heads};
+    std::lock_guard<std::mutex> lock(mu);
+    auto it = cache.find(key);
+    if (it != cache.end()) {
+        *out = it->second;
+        return 0;
+    }
+    EncodeTiledFn enc = encode_tiled_fn();
+    if (!enc) return fail(B200ATTN_E_DRIVER, "cuTensorMapEncodeTiled not available from the driver");
+    const cuuint64_t dims[3] = {static_cast<cuuint64_t>(b200::kHeadDim),
+                                static_cast<cuuint64_t>(num_kv_heads),
+                                static_cast<cuuint64_t>(num_slots)};
+    const cuuint64_t strides[2] = {static_cast<cuuint64_t>(b200::kHeadDim) * 2,
+                                   static_cast<cuuint64_t>(num_kv_heads) * b200::kHeadDim * 2};
+    const cuuint32_t box[3] = {64, 1, 64};
+    const cuuint32_t elem_strides[3] = {1, 1, 1};
+    CUtensorMap map;
+    CUresult r = enc(&map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims,
+                     strides, box, elem_strides, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS)
+        return fail(B200ATTN_E_DRIVER, "cuTensorMapEncodeTiled failed with CUresult %d",
+                    static_cast<int>(r));
+    if (cache.size() > 4096) cache.clear();
+    cache.emplace(key, map);
+    *out = map;
+    return 0;
+}
+
+int check_attn_shape(int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim,
+                     int32_t block_size, int32_t dtype) {
+    if (dtype != B200ATTN_DTYPE_BF16)
+        return fail(B200ATTN_E_UNSUPPORTED, "dtype %d unsupported (bf16 only)", dtype);
+    if (head_dim != b200::kHeadDim)
+        return fail(B200ATTN_E_UNSUPPORTED, "head_dim %d unsupported (128 only)", head_dim);
+    if (num_q_heads <= 0 || num_kv_heads <= 0 || num_q_heads % num_kv_heads != 0)
+        return fail(B200ATTN_E_BADARG, "bad head counts Hq=%d Hkv=%d", num_q_heads, num_kv_heads);
+    if (num_q_heads / num_kv_heads > 8)
+        return fail(B200ATTN_E_UNSUPPORTED, "GQA group %d > 8 unsupported",
+                    num_q_heads / num_kv_heads);
+    if (block_size <= 0 || block_size % 64 != 0)
+        return fail(B200ATTN_E_UNSUPPORTED, "block_size %d must be a positive multiple of 64",
+                    block_size);
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int b200attn_abi_version(void) { return B200ATTN_ABI_VERSION; }
+
+const char* b200attn_last_error(void) { return g_err; }
+
+int64_t b200attn_launch_count(void) { return b200::g_launches.load(std::memory_order_relaxed); }
+
+int b200attn_sm_count(void) {
+    static int count = [] {
+        int dev = 0, n = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess ||
+            cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) {
+            (void)cudaGetLastError();
+            return 0;
+        }
+        return n;
+    }();
+    return count;
+}
+
+int b200attn_store_kvcache(const void* key, int64_t key_row_stride, const void* value,
+                           int64_t value_row_stride, void* k_cache, void* v_cache,
+                           const int32_t* slot_mapping, int32_t n_tokens, int32_t row_elems,
+                           int64_t num_slots, int32_t dtype, void* stream) {
+    if (dtype != B200ATTN_DTYPE_BF16)
+        return fail(B200ATTN_E_UNSUPPORTED, "dtype %d unsupported (16-bit bf16 only)", dtype);
+    if (n_tokens < 0 || row_elems <= 0 || num_slots < 0)
+        return fail(B200ATTN_E_BADARG, "negative size");
+    if (n_tokens == 0) return 0;
+    if (!key || !value || !k_cache || !v_cache || !slot_mapping)
+        return fail(B200ATTN_E_BADARG, "null pointer");
+    if (row_elems % 8 != 0 || key_row_stride % 8 != 0 || value_row_stride % 8 != 0)
+        return fail(B200ATTN_E_UNSUPPORTED,
+                    "row_elems/strides must be multiples of 8 elements (16-byte vectors)");
+    if (!aligned16(key) || !aligned16(value) || !aligned16(k_cache) || !aligned16(v_cache))
+        return fail(B200ATTN_E_BADARG, "pointers must be 16-byte aligned");
+    if (key_row_stride < row_elems || value_row_stride < row_elems)
+        return fail(B200ATTN_E_BADARG, "row stride smaller than the row");
+    cudaError_t e = b200::launch_store_kvcache(key, key_row_stride, value, value_row_stride, k_cache,
+                                               v_cache, slot_mapping, n_tokens, row_elems, num_slots,
+                                               static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? 0 : cuda_fail(e, "store_kvcache launch");
+}
+
+int b200attn_decode_pick_splits(int32_t batch, int32_t num_kv_heads, int32_t table_width,
+                                int32_t block_size, int32_t sm_count) {
+    if (sm_count <= 0) sm_count = 148;
+    return b200::decode_pick_splits(batch, num_kv_heads, table_width, block_size, sm_count);
+}
+
+size_t b200attn_decode_workspace_bytes(int32_t batch, int32_t num_q_heads, int32_t head_dim,
+                                       int32_t num_splits) {
+    if (batch <= 0 || num_q_heads <= 0 || head_dim != b200::kHeadDim) return 0;
+    return b200::decode_workspace_bytes(batch, num_q_heads, num_splits);
+}
+
+int b200attn_store_decode(const void* q, const void* key, int64_t key_row_stride, const void* value,
+                          int64_t value_row_stride, const int32_t* slot_mapping, void* k_cache,
+                          void* v_cache, const int32_t* block_tables, int64_t table_row_stride,
+                          int32_t table_width, const int32_t* context_lens, void* out,
+                          void* workspace, size_t workspace_bytes, int32_t batch,
+                          int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim,
+                          int32_t block_size, int64_t num_blocks, float scale, int32_t num_splits,
+                          int32_t dtype, void* stream) {
+    if (int rc = check_attn_shape(num_q_heads, num_kv_heads, head_dim, block_size, dtype)) return rc;
+    if (batch < 0 || num_blocks <= 0 || table_width < 0 || num_splits < 1)
+        return fail(B200ATTN_E_BADARG, "negative or zero size");
+    if (batch == 0) return 0;
+    if (batch > 65535) return fail(B200ATTN_E_UNSUPPORTED, "batch %d > 65535", batch);
+    if (!q || !k_cache || !v_cache || !block_tables || !context_lens || !out)
+        return fail(B200ATTN_E_BADARG, "null pointer");
+    if (!std::isfinite(scale)) return fail(B200ATTN_E_BADARG, "scale is not finite");
+    const int64_t num_slots = num_blocks * block_size;
+    if (num_slots >= (1LL << 31))
+        return fail(B200ATTN_E_UNSUPPORTED, "cache of %lld slots exceeds int32 TMA coordinates",
+                    static_cast<long long>(num_slots));
+    if (!aligned16(q) || !aligned16(out) || !aligned16(k_cache) || !aligned16(v_cache))
+        return fail(B200ATTN_E_BADARG, "pointers must be 16-byte aligned");
+    if (num_splits > 1) {
+        const size_t need = b200::decode_workspace_bytes(batch, num_q_heads, num_splits);
+        if (!workspace || workspace_bytes < need || !aligned16(workspace))
+            return fail(B200ATTN_E_WORKSPACE, "workspace %zu B < %zu B needed for %d splits",
+                        workspace_bytes, need, num_splits);
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (key || value || slot_mapping) {
+        if (int rc = b200attn_store_kvcache(key, key_row_stride, value, value_row_stride, k_cache,
+                                            v_cache, slot_mapping, batch,
+                                            num_kv_heads * head_dim, num_slots, dtype, stream))
+            return rc;
+    }
+    CUtensorMap k_map, v_map;
+    if (int rc = get_cache_map(k_cache, num_kv_heads, num_slots, &k_map)) return rc;
+    if (int rc = get_cache_map(v_cache, num_kv_heads, num_slots, &v_map)) return rc;
+
+    b200::DecodeParams p{};
+    p.q = q;
+    p.out = out;
+    p.block_tables = block_tables;
+    p.context_lens = context_lens;
+    p.table_row_stride = table_row_stride;
+    p.table_width = table_width;
+    p.batch = batch;
+    p.num_q_heads = num_q_heads;
+    p.num_kv_heads = num_kv_heads;
+    p.group = num_q_heads / num_kv_heads;
+    p.block_size = block_size;
+    p.num_splits = num_splits;
+    p.scale_log2 = scale * 1.4426950408889634f;
+    if (num_splits > 1) {
+        p.ws_o = static_cast<float*>(workspace);
+        p.ws_lse = p.ws_o + static_cast<size_t>(batch) * num_q_heads * num_splits * b200::kHeadDim;
+    }
+    cudaError_t e = b200::launch_decode(p, k_map, v_map, st);
+    return e == cudaSuccess ? 0 : cuda_fail(e, "decode launch");
+}
+
+int b200attn_decode(const void* q, const void* k_cache, const void* v_cache,
+                    const int32_t* block_tables, int64_t table_row_stride, int32_t table_width,
+                    const int32_t* context_lens, void* out, void* workspace, size_t workspace_bytes,
+                    int32_t batch, int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim,
+                    int32_t block_size, int64_t num_blocks, float scale, int32_t num_splits,
+                    int32_t dtype, void* stream) {
+    return b200attn_store_decode(q, nullptr, 0, nullptr, 0, nullptr, const_cast<void*>(k_cache),
+                                 const_cast<void*>(v_cache), block_tables, table_row_stride,
+                                 table_width, context_lens, out, workspace, workspace_bytes, batch,
+                                 num_q_heads, num_kv_heads, head_dim, block_size, num_blocks, scale,
+                                 num_splits, dtype, stream);
+}
+
+int b200attn_prefill_varlen(const void* q, const void* key, int64_t key_row_stride,
+                            const void* value, int64_t value_row_stride, const void* k_cache,
+                            const void* v_cache, const int32_t* block_tables,
+                            int64_t table_row_stride, int32_t table_width,
+                            const int32_t* cu_seqlens_q, const int32_t* cu_seqlens_k,
+                            int32_t num_seqs, int32_t total_q, int32_t max_seqlen_q,
+                            int32_t max_seqlen_k, void* out, int32_t num_q_heads,
+                            int32_t num_kv_heads, int32_t head_dim, int32_t block_size,
+                            int64_t num_blocks, float scale, int32_t dtype, void* stream) {
+    const bool paged = block_tables != nullptr;
+    if (int rc = check_attn_shape(num_q_heads, num_kv_heads, head_dim, paged ? block_size : 64,
+                                  dtype))
+        return rc;
+    if (num_seqs < 0 || total_q < 0 || max_seqlen_q < 0 || max_seqlen_k < 0)
+        return fail(B200ATTN_E_BADARG, "negative size");
+    if (num_seqs == 0 || total_q == 0 || max_seqlen_q == 0) return 0;
+    if (!q || !out || !cu_seqlens_q || !cu_seqlens_k) return fail(B200ATTN_E_BADARG, "null pointer");
+    if (!std::isfinite(scale)) return fail(B200ATTN_E_BADARG, "scale is not finite");
+    if (paged) {
+        if (!k_cache || !v_cache) return fail(B200ATTN_E_BADARG, "paged prefill needs the caches");
+        if (num_blocks <= 0 || table_width <= 0)
+            return fail(B200ATTN_E_BADARG, "paged prefill needs num_blocks/table_width > 0");
+        if (!aligned16(k_cache) || !aligned16(v_cache))
+            return fail(B200ATTN_E_BADARG, "caches must be 16-byte aligned");
+    } else {
+        if (!key || !value) return fail(B200ATTN_E_BADARG, "dense prefill needs key/value");
+        if (key_row_stride % 8 != 0 || value_row_stride % 8 != 0 || !aligned16(key) ||
+            !aligned16(value))
+            return fail(B200ATTN_E_UNSUPPORTED, "key/value rows must be 16-byte aligned");
+        if (key_row_stride < num_kv_heads * head_dim || value_row_stride < num_kv_heads * head_dim)
+            return fail(B200ATTN_E_BADARG, "row stride smaller than the row");
+    }
+    if (!aligned16(q) || !aligned16(out))
+        return fail(B200ATTN_E_BADARG, "q/out must be 16-byte aligned");
+
+    b200::PrefillParams p{};
+    p.q = q;
+    p.out = out;
+    p.key = key;
+    p.value = value;
+    p.key_row_stride = key_row_stride;
+    p.value_row_stride = value_row_stride;
+    p.k_cache = k_cache;
+    p.v_cache = v_cache;
+    p.block_tables = block_tables;
+    p.table_row_stride = table_row_stride;
+    p.table_width = table_width;
+    p.cu_seqlens_q = cu_seqlens_q;
+    p.cu_seqlens_k = cu_seqlens_k;
+    p.num_seqs = num_seqs;
+    p.total_q = total_q;
+    p.max_seqlen_q = max_seqlen_q;
+    p.max_seqlen_k = max_seqlen_k;
+    p.num_q_heads = num_q_heads;
+    p.num_kv_heads = num_kv_heads;
+    p.group = num_q_heads / num_kv_heads;
+    p.block_size = block_size;
+    p.scale_log2 = scale * 1.4426950408889634f;
+    cudaError_t e = b200::launch_prefill(p, static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? 0 : cuda_fail(e, "prefill launch");
+}
+
+}  // extern "C"

@@ -1,0 +1,83 @@
+// Internal declarations shared by the kernel translation units and the C ABI (api.cu).
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <cstddef>
+#include <cstdint>
+
+namespace b200 {
+
+constexpr int kHeadDim = 128;  // every BASELINE model (Qwen3 0.6B / 8B / 32B) has head_dim 128
+
+// Launch accounting (b200attn_launch_count): every kernel launch of the library calls this once.
+void count_launch(int n = 1);
+
+// ---- store_kv.cu -----------------------------------------------------------------------------
+cudaError_t launch_store_kvcache(const void* key, int64_t key_row_stride, const void* value,
+                                 int64_t value_row_stride, void* k_cache, void* v_cache,
+                                 const int32_t* slot_mapping, int32_t n_tokens, int32_t row_elems,
+                                 int64_t num_slots, cudaStream_t stream);
+
+// ---- decode_attn.cu --------------------------------------------------------------------------
+struct DecodeParams {
+    const void* q;                // [B, Hq, 128] bf16
+    void* out;                    // [B, Hq, 128] bf16
+    const int32_t* block_tables;  // [B, table_row_stride]
+    const int32_t* context_lens;  // [B]
+    float* ws_o;                  // [B, Hq, S, 128] fp32 normalised partials (S > 1)
+    float* ws_lse;                // [B, Hq, S] fp32 log2-domain log-sum-exp (S > 1)
+    int64_t table_row_stride;
+    int32_t table_width;
+    int32_t batch;
+    int32_t num_q_heads;
+    int32_t num_kv_heads;
+    int32_t group;  // Hq / Hkv, 1..8
+    int32_t block_size;
+    int32_t num_splits;
+    float scale_log2;  // softmax scale * log2(e)
+    // optional fused scatter of this step's K/V rows (nullptr => no store)
+    const void* new_key;
+    const void* new_value;
+    const int32_t* slot_mapping;
+    void* k_cache;
+    void* v_cache;
+    int64_t key_row_stride;
+    int64_t value_row_stride;
+    int64_t num_slots;
+};
+cudaError_t launch_decode(const DecodeParams& p, const CUtensorMap& k_map, const CUtensorMap& v_map,
+                          cudaStream_t stream);
+size_t decode_workspace_bytes(int32_t batch, int32_t num_q_heads, int32_t num_splits);
+int decode_pick_splits(int32_t batch, int32_t num_kv_heads, int32_t table_width, int32_t block_size,
+                       int32_t sm_count);
+
+// ---- prefill_attn.cu -------------------------------------------------------------------------
+struct PrefillParams {
+    const void* q;  // [total_q, Hq, 128]
+    void* out;      // [total_q, Hq, 128]
+    // dense source
+    const void* key;
+    const void* value;
+    int64_t key_row_stride;    // elements
+    int64_t value_row_stride;  // elements
+    // paged source
+    const void* k_cache;
+    const void* v_cache;
+    const int32_t* block_tables;  // nullptr => dense
+    int64_t table_row_stride;
+    int32_t table_width;
+    const int32_t* cu_seqlens_q;
+    const int32_t* cu_seqlens_k;
+    int32_t num_seqs;
+    int32_t total_q;
+    int32_t max_seqlen_q;
+    int32_t max_seqlen_k;
+    int32_t num_q_heads;
+    int32_t num_kv_heads;
+    int32_t group;
+    int32_t block_size;
+    float scale_log2;
+};
+cudaError_t launch_prefill(const PrefillParams& p, cudaStream_t stream);
+
+}  // namespace b200

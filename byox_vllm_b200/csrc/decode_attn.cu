@@ -1,0 +1,415 @@
+// Paged decode attention for sm_100a: split-KV over KV pages, TMA-staged K/V tiles, GQA packing.
+// Replaces flash_attn_with_kvcache on the decode branch of Attention.forward
+// (reference nanovllm/layers/attention.py:87-96).
+//
+// Work item = (sequence b, KV head, split). One CTA = 4 consumer warps + 1 TMA producer warp.
+//   * The producer streams 64-token tiles of the (b, kv-head) slice of K and V through a
+//     kStages-deep shared-memory ring with cp.async.bulk.tensor (SWIZZLE_128B boxes of
+//     64 tokens x 64 dims; one page of 256 tokens = 4 tiles, so tiles never straddle pages) and
+//     mbarrier expect-tx completion. Block-table entries are fetched 32 pages at a time by the
+//     producer warp so the table lookup is off the critical path.
+//   * GQA packing: the G = Hq/Hkv query heads that share this KV head are the N dimension of
+//     mma.sync.m16n8k16 (N = 8 >= G), tokens are M. So every K/V byte is read from HBM once per
+//     KV head and serves all G query heads:  S^T[tok, head] = K[tok, :] . Q^T[:, head].
+//   * Each consumer warp owns 16 tokens of every tile and keeps its own online-softmax state
+//     (running max / sum per head, O^T[128 dims x 8 heads] in registers); the max over tokens is
+//     a 3-step warp shuffle. P^T is moved from accumulator to B-operand layout with
+//     movmatrix.trans, and O^T += V^T . P^T uses ldmatrix.trans on the V tile.
+//   * The 4 warps are merged through shared memory at the end; with num_splits > 1 the CTA writes
+//     a normalised fp32 partial + log2-sum-exp and a small merge kernel combines the splits.
+//
+// Roofline: HBM. Algorithmic bytes per (b, kv-head) = ctx * 128 * 2 B * 2 (K and V), read once.
+#include "common.h"
+#include "ptx.cuh"
+
+#include <cstdlib>
+
+namespace b200 {
+
+namespace {
+
+constexpr int kTile = 64;                   // tokens per stage
+constexpr int kConsumerWarps = 4;           // 16 tokens each
+constexpr int kDecodeThreads = (kConsumerWarps + 1) * 32;
+constexpr int kSubTileBytes = kTile * 128;  // [64 tok][64 dims] bf16 = 8 KiB, 128-byte rows
+constexpr int kStageBytes = 4 * kSubTileBytes;  // K lo/hi + V lo/hi = 32 KiB
+constexpr int kMergeStride = 132;           // padded fp32 row (bank-conflict-free transposed writes)
+
+__device__ __forceinline__ void consumer_bar_sync() {
+    asm volatile("bar.sync 1, %0;" ::"n"(kConsumerWarps * 32) : "memory");
+}
+
+template <int kStages>
+__global__ void __launch_bounds__(kDecodeThreads, 2)
+decode_split_kernel(const __grid_constant__ CUtensorMap k_map,
+                    const __grid_constant__ CUtensorMap v_map, const DecodeParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>(
+        (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kStages * kStageBytes);
+    uint64_t* empty_bar = full_bar + kStages;
+    float* ml_smem = reinterpret_cast<float*>(empty_bar + kStages);  // [4 warps][8 heads][2]
+
+    const int kvh = blockIdx.x;
+    const int split = blockIdx.y;
+    const int b = blockIdx.z;
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int G = p.group;
+    const int Hq = p.num_q_heads;
+    const int S = p.num_splits;
+
+    const int ctx = p.context_lens[b];
+    const int tiles_total = ctx > 0 ? (ctx + kTile - 1) / kTile : 0;
+    const int per_split = (tiles_total + S - 1) / S;
+    const int t_begin = split * per_split;
+    const int t_end = min(t_begin + per_split, tiles_total);
+    const int64_t q_row0 = static_cast<int64_t>(b) * Hq + static_cast<int64_t>(kvh) * G;
+
+    if (t_begin >= t_end) {
+        // Nothing to attend in this split (ctx == 0 padding row of a CUDA-graph batch, or a split
+        // beyond the sequence). No table entry is read.
+        if (S == 1) {
+            __nv_bfloat16* out = static_cast<__nv_bfloat16*>(p.out) + q_row0 * kHeadDim;
+            for (int i = threadIdx.x; i < G * kHeadDim; i += kDecodeThreads)
+                out[i] = __float2bfloat16(0.f);
+        } else if (threadIdx.x < G) {
+            p.ws_lse[(q_row0 + threadIdx.x) * S + split] = -INFINITY;
+        }
+        return;
+    }
+
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], kConsumerWarps);
+        }
+        fence_mbar_init();
+    }
+    __syncthreads();
+
+    if (warp == kConsumerWarps) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            tma_prefetch_desc(&k_map);
+            tma_prefetch_desc(&v_map);
+        }
+        const int tiles_per_page = p.block_size / kTile;
+        const int32_t* table = p.block_tables + static_cast<int64_t>(b) * p.table_row_stride;
+        const int last_page = (t_end - 1) / tiles_per_page;
+        int page_base = t_begin / tiles_per_page;
+        int my_block = (page_base + lane <= last_page) ? table[page_base + lane] : 0;
+        const uint64_t policy = l2_policy_evict_first();
+        for (int t = t_begin, it = 0; t < t_end; ++t, ++it) {
+            const int stage = it % kStages;
+            const uint32_t phase = (it / kStages) & 1u;
+            const int page = t / tiles_per_page;
+            if (page - page_base >= 32) {
+                page_base = page;
+                my_block = (page_base + lane <= last_page) ? table[page_base + lane] : 0;
+            }
+            const int block_id = __shfl_sync(0xffffffffu, my_block, page - page_base);
+            if (lane == 0) {
+                mbar_wait(&empty_bar[stage], phase ^ 1u);
+                mbar_expect_tx(&full_bar[stage], kStageBytes);
+                const int slot = block_id * p.block_size + (t % tiles_per_page) * kTile;
+                uint8_t* dst = smem + stage * kStageBytes;
+                tma_load_3d_hint(dst, &k_map, &full_bar[stage], 0, kvh, slot, policy);
+                tma_load_3d_hint(dst + kSubTileBytes, &k_map, &full_bar[stage], 64, kvh, slot,
+                                 policy);
+                tma_load_3d_hint(dst + 2 * kSubTileBytes, &v_map, &full_bar[stage], 0, kvh, slot,
+                                 policy);
+                tma_load_3d_hint(dst + 3 * kSubTileBytes, &v_map, &full_bar[stage], 64, kvh, slot,
+                                 policy);
+            }
+            __syncwarp();
+        }
+        return;
+    }
+
+    // ===================== consumers =====================
+    // Q^T as the B operand (k = dim, n = head): b0 holds dims 2*(lane%4)+{0,1}, b1 the same +8,
+    // for head n = lane/4. Heads >= G are zero.
+    uint32_t qf[8][2];
+    {
+        const int head = lane >> 2;
+        const __nv_bfloat16* qrow =
+            static_cast<const __nv_bfloat16*>(p.q) + (q_row0 + head) * kHeadDim + 2 * (lane & 3);
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks) {
+            if (head < G) {
+                qf[ks][0] = *reinterpret_cast<const uint32_t*>(qrow + ks * 16);
+                qf[ks][1] = *reinterpret_cast<const uint32_t*>(qrow + ks * 16 + 8);
+            } else {
+                qf[ks][0] = 0u;
+                qf[ks][1] = 0u;
+            }
+        }
+    }
+
+    float m_run[2] = {-INFINITY, -INFINITY};  // running max (log2 domain), heads 2*(lane%4)+{0,1}
+    float l_run[2] = {0.f, 0.f};              // per-thread partial row sums
+    float o[8][4];
+#pragma unroll
+    for (int mt = 0; mt < 8; ++mt)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) o[mt][c] = 0.f;
+
+    const uint32_t smem_base = smem_u32(smem);
+    // K A-fragment addressing (rows = tokens): lane -> row lane%16, 16-byte chunk +(lane/16)
+    const uint32_t k_row = warp * 16 + (lane & 15);
+    const uint32_t k_csel = lane >> 4;
+    // V^T A-fragment addressing via ldmatrix.trans: matrix j = lane/8 -> tokens (j/2)*8 + lane%8,
+    // dim chunk + (j%2)
+    const uint32_t v_row = warp * 16 + ((lane >> 4) << 3) + (lane & 7);
+    const uint32_t v_csel = (lane >> 3) & 1;
+
+    for (int t = t_begin, it = 0; t < t_end; ++t, ++it) {
+        const int stage = it % kStages;
+        const uint32_t phase = (it / kStages) & 1u;
+        mbar_wait(&full_bar[stage], phase);
+        const uint32_t kb = smem_base + stage * kStageBytes;
+        const uint32_t vb = kb + 2 * kSubTileBytes;
+
+        // ---- S^T[16 tok x 8 heads] = K . Q^T ----
+        float s[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks) {
+            uint32_t a[4];
+            ldmatrix_x4(a, kb + (ks >> 2) * kSubTileBytes + swz128(k_row, (ks & 3) * 2 + k_csel));
+            mma_bf16_16816(s, a, qf[ks][0], qf[ks][1]);
+        }
+
+        // ---- mask + online softmax (log2 domain) ----
+        const int tok = t * kTile + warp * 16 + (lane >> 2);
+        const bool v0 = tok < ctx, v1 = tok + 8 < ctx;
+        s[0] = v0 ? s[0] * p.scale_log2 : -INFINITY;
+        s[1] = v0 ? s[1] * p.scale_log2 : -INFINITY;
+        s[2] = v1 ? s[2] * p.scale_log2 : -INFINITY;
+        s[3] = v1 ? s[3] * p.scale_log2 : -INFINITY;
+        float mx0 = fmaxf(s[0], s[2]), mx1 = fmaxf(s[1], s[3]);
+#pragma unroll
+        for (int off = 4; off < 32; off <<= 1) {
+            mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, off));
+            mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, off));
+        }
+        const float mn0 = fmaxf(m_run[0], mx0), mn1 = fmaxf(m_run[1], mx1);
+        const float mu0 = mn0 == -INFINITY ? 0.f : mn0, mu1 = mn1 == -INFINITY ? 0.f : mn1;
+        const float alpha0 = fast_exp2(m_run[0] - mu0), alpha1 = fast_exp2(m_run[1] - mu1);
+        m_run[0] = mn0;
+        m_run[1] = mn1;
+        const float p0 = fast_exp2(s[0] - mu0), p1 = fast_exp2(s[1] - mu1);
+        const float p2 = fast_exp2(s[2] - mu0), p3 = fast_exp2(s[3] - mu1);
+        l_run[0] = l_run[0] * alpha0 + p0 + p2;
+        l_run[1] = l_run[1] * alpha1 + p1 + p3;
+
+        // Tokens beyond ctx inside the last page are whatever the allocator left there; P is 0
+        // for them but 0 * NaN would poison O, so their V rows are cleared in shared memory.
+        if (t == tiles_total - 1) {
+            const int valid_rows = ctx - (t * kTile + warp * 16);  // rows of this warp's 16
+            if (valid_rows < 16) {
+                const int r_lo = max(valid_rows, 0);
+                if (lane < 16) {
+                    uint8_t* vsm = smem + stage * kStageBytes + 2 * kSubTileBytes +
+                                   (lane >> 3) * kSubTileBytes;
+                    for (int r = r_lo; r < 16; ++r)
+                        *reinterpret_cast<int4*>(vsm + (warp * 16 + r) * 128 + (lane & 7) * 16) =
+                            make_int4(0, 0, 0, 0);
+                }
+                __syncwarp();
+            }
+        }
+
+        // ---- O^T[128 dims x 8 heads] = alpha * O^T + V^T . P^T ----
+        const uint32_t pb0 = movmatrix_trans(pack_bf16x2(p0, p1));
+        const uint32_t pb1 = movmatrix_trans(pack_bf16x2(p2, p3));
+#pragma unroll
+        for (int mt = 0; mt < 8; ++mt) {
+            uint32_t a[4];
+            ldmatrix_x4_trans(
+                a, vb + (mt >> 2) * kSubTileBytes + swz128(v_row, (mt & 3) * 2 + v_csel));
+            o[mt][0] *= alpha0;
+            o[mt][1] *= alpha1;
+            o[mt][2] *= alpha0;
+            o[mt][3] *= alpha1;
+            mma_bf16_16816(o[mt], a, pb0, pb1);
+        }
+
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty_bar[stage]);
+    }
+
+    // ---- finish the row sums (tokens are spread over lane/4) ----
+#pragma unroll
+    for (int off = 4; off < 32; off <<= 1) {
+        l_run[0] += __shfl_xor_sync(0xffffffffu, l_run[0], off);
+        l_run[1] += __shfl_xor_sync(0xffffffffu, l_run[1], off);
+    }
+
+    // ---- merge the 4 warps through shared memory (ring is drained; reuse stage 0) ----
+    if (lane < 4) {
+        float* ml = ml_smem + (warp * 8 + 2 * lane) * 2;
+        ml[0] = m_run[0];
+        ml[1] = l_run[0];
+        ml[2] = m_run[1];
+        ml[3] = l_run[1];
+    }
+    consumer_bar_sync();  // all warps done with the ring + ml visible
+    float mg[2], fac[2];
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const int h = 2 * (lane & 3) + i;
+        float m = -INFINITY;
+#pragma unroll
+        for (int w = 0; w < kConsumerWarps; ++w) m = fmaxf(m, ml_smem[(w * 8 + h) * 2]);
+        mg[i] = m;
+        fac[i] = m == -INFINITY ? 0.f : fast_exp2(m_run[i] - m);
+    }
+    float* osc = reinterpret_cast<float*>(smem);  // [4 warps][8 heads][kMergeStride]
+#pragma unroll
+    for (int mt = 0; mt < 8; ++mt)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const int h = 2 * (lane & 3) + (c & 1);
+            const int d = mt * 16 + (lane >> 2) + (c >> 1) * 8;
+            osc[(warp * 8 + h) * kMergeStride + d] = o[mt][c] * fac[c & 1];
+        }
+    consumer_bar_sync();
+
+    const int d = threadIdx.x;  // 128 consumer threads <-> 128 dims
+    for (int h = 0; h < G; ++h) {
+        float m = -INFINITY;
+#pragma unroll
+        for (int w = 0; w < kConsumerWarps; ++w) m = fmaxf(m, ml_smem[(w * 8 + h) * 2]);
+        float l = 0.f, acc = 0.f;
+#pragma unroll
+        for (int w = 0; w < kConsumerWarps; ++w) {
+            const float mw = ml_smem[(w * 8 + h) * 2];
+            l += mw == -INFINITY ? 0.f : ml_smem[(w * 8 + h) * 2 + 1] * fast_exp2(mw - m);
+            acc += osc[(w * 8 + h) * kMergeStride + d];
+        }
+        const float val = l > 0.f ? acc / l : 0.f;
+        if (S == 1) {
+            static_cast<__nv_bfloat16*>(p.out)[(q_row0 + h) * kHeadDim + d] = __float2bfloat16(val);
+        } else {
+            p.ws_o[((q_row0 + h) * S + split) * kHeadDim + d] = val;
+            if (d == 0) p.ws_lse[(q_row0 + h) * S + split] = l > 0.f ? m + log2f(l) : -INFINITY;
+        }
+    }
+    (void)mg;
+}
+
+// Combine num_splits normalised partials per (b, q-head) row: one warp per row, 4 dims per lane.
+__global__ void __launch_bounds__(128)
+decode_merge_kernel(const float* __restrict__ ws_o, const float* __restrict__ ws_lse,
+                    __nv_bfloat16* __restrict__ out, int32_t rows, int32_t S) {
+    const int row = blockIdx.x * 4 + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (row >= rows) return;
+    const float* lse = ws_lse + static_cast<int64_t>(row) * S;
+    float mx = -INFINITY;
+    for (int s = lane; s < S; s += 32) mx = fmaxf(mx, lse[s]);
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    float wsum = 0.f;
+    if (mx != -INFINITY) {
+        for (int s = 0; s < S; ++s) {
+            const float ls = lse[s];
+            if (ls == -INFINITY) continue;  // empty split: its partial was never written
+            const float w = fast_exp2(ls - mx);
+            const float4 v = *reinterpret_cast<const float4*>(
+                ws_o + (static_cast<int64_t>(row) * S + s) * kHeadDim + lane * 4);
+            acc.x += w * v.x;
+            acc.y += w * v.y;
+            acc.z += w * v.z;
+            acc.w += w * v.w;
+            wsum += w;
+        }
+    }
+    const float inv = wsum > 0.f ? 1.f / wsum : 0.f;
+    __nv_bfloat162 lo = __floats2bfloat162_rn(acc.x * inv, acc.y * inv);
+    __nv_bfloat162 hi = __floats2bfloat162_rn(acc.z * inv, acc.w * inv);
+    uint2 pk;
+    pk.x = *reinterpret_cast<uint32_t*>(&lo);
+    pk.y = *reinterpret_cast<uint32_t*>(&hi);
+    *reinterpret_cast<uint2*>(out + static_cast<int64_t>(row) * kHeadDim + lane * 4) = pk;
+}
+
+template <int kStages>
+constexpr int decode_smem_bytes() {
+    return kStages * kStageBytes + 2 * kStages * 8 + kConsumerWarps * 8 * 2 * 4 + 1024;
+}
+
+template <int kStages>
+cudaError_t launch_split(const DecodeParams& p, const CUtensorMap& k_map, const CUtensorMap& v_map,
+                         cudaStream_t stream) {
+    static bool configured = false;
+    constexpr int smem = decode_smem_bytes<kStages>();
+    if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(decode_split_kernel<kStages>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e != cudaSuccess) return e;
+        configured = true;
+    }
+    dim3 grid(p.num_kv_heads, p.num_splits, p.batch);
+    decode_split_kernel<kStages><<<grid, kDecodeThreads, smem, stream>>>(k_map, v_map, p);
+    count_launch();
+    return cudaGetLastError();
+}
+
+int decode_stages_from_env() {
+    static int stages = [] {
+        const char* e = std::getenv("B200ATTN_DECODE_STAGES");
+        int s = e ? std::atoi(e) : 3;
+        return (s == 2 || s == 3 || s == 4 || s == 6) ? s : 3;
+    }();
+    return stages;
+}
+
+}  // namespace
+
+size_t decode_workspace_bytes(int32_t batch, int32_t num_q_heads, int32_t num_splits) {
+    if (num_splits <= 1) return 0;
+    const size_t rows = static_cast<size_t>(batch) * num_q_heads;
+    return rows * num_splits * (kHeadDim + 1) * sizeof(float);
+}
+
+int decode_pick_splits(int32_t batch, int32_t num_kv_heads, int32_t table_width, int32_t block_size,
+                       int32_t sm_count) {
+    // Host-visible sizes only. Aim for >= 2 waves of CTAs at 2 CTAs/SM, but never cut a sequence
+    // into pieces shorter than 4 tiles (256 tokens) of the longest possible context.
+    const int64_t base = static_cast<int64_t>(batch) * num_kv_heads;
+    const int64_t want = 4LL * sm_count;
+    if (base <= 0 || base >= want) return 1;
+    const int64_t max_tiles = static_cast<int64_t>(table_width) * block_size / kTile;
+    int64_t s = (want + base - 1) / base;
+    const int64_t cap = max_tiles / 4 > 1 ? max_tiles / 4 : 1;
+    if (s > cap) s = cap;
+    if (s > 128) s = 128;
+    return static_cast<int>(s < 1 ? 1 : s);
+}
+
+cudaError_t launch_decode(const DecodeParams& p, const CUtensorMap& k_map, const CUtensorMap& v_map,
+                          cudaStream_t stream) {
+    if (p.batch == 0) return cudaSuccess;
+    cudaError_t e;
+    switch (decode_stages_from_env()) {
+        case 2: e = launch_split<2>(p, k_map, v_map, stream); break;
+        case 4: e = launch_split<4>(p, k_map, v_map, stream); break;
+        case 6: e = launch_split<6>(p, k_map, v_map, stream); break;
+        default: e = launch_split<3>(p, k_map, v_map, stream); break;
+    }
+    if (e != cudaSuccess) return e;
+    if (p.num_splits > 1) {
+        const int rows = p.batch * p.num_q_heads;
+        decode_merge_kernel<<<(rows + 3) / 4, 128, 0, stream>>>(
+            p.ws_o, p.ws_lse, static_cast<__nv_bfloat16*>(p.out), rows, p.num_splits);
+        count_launch();
+        e = cudaGetLastError();
+    }
+    return e;
+}
+
+}  // namespace b200

@@ -1,0 +1,140 @@
+/*
+ * b200attn.h — C ABI of the B200-native attention hot path (libb200attn.so).
+ *
+ * This is the drop-in boundary for nanovllm's attention path. Every entry point names the
+ * reference interface it replaces (paths relative to the reference tree):
+ *
+ *   b200attn_store_kvcache     nanovllm/layers/attention.py:10-49   (Triton store_kvcache_kernel
+ *                                                                     + its Python launcher)
+ *   b200attn_decode            nanovllm/layers/attention.py:87-96   (flash_attn_with_kvcache:
+ *                                                                     paged single-query attention)
+ *   b200attn_store_decode      nanovllm/layers/attention.py:70-71 + :87-96 fused in one call
+ *   b200attn_prefill_varlen    nanovllm/layers/attention.py:72-86   (flash_attn_varlen_func:
+ *                                                                     dense and paged-prefix)
+ *
+ * Conventions
+ *   - Plain pointers and sizes only; all buffers are DEVICE pointers owned by the caller (torch
+ *     tensors on the Python side). The library never allocates or frees device memory, never
+ *     synchronises the device and never reads device data on the host, so every call can be
+ *     captured into a CUDA graph (nanovllm/engine/model_runner.py:256-297).
+ *   - `stream` is a cudaStream_t passed as void* (0 = legacy default stream).
+ *   - Return value: 0 on success; negative = argument / unsupported-shape error
+ *     (B200ATTN_E_*); positive = cudaError_t of the failed launch. b200attn_last_error()
+ *     returns a thread-local human-readable message for the last non-zero return.
+ *   - dtype: 16-bit storage; `dtype` 0 = bfloat16 (the only arithmetic type built in this round).
+ *   - There is no CPU fallback: without a CUDA device every compute entry point fails.
+ */
+#ifndef B200ATTN_H_
+#define B200ATTN_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200ATTN_ABI_VERSION 1
+
+#define B200ATTN_DTYPE_BF16 0
+
+#define B200ATTN_E_BADARG (-1)      /* null pointer / negative size / misalignment           */
+#define B200ATTN_E_UNSUPPORTED (-2) /* head_dim != 128, dtype, block_size % 64, G > 8 ...     */
+#define B200ATTN_E_WORKSPACE (-3)   /* workspace too small for the requested split count      */
+#define B200ATTN_E_DRIVER (-4)      /* cuTensorMapEncodeTiled unavailable / failed            */
+
+/* ABI version of the loaded library (== B200ATTN_ABI_VERSION it was built with). */
+int b200attn_abi_version(void);
+
+/* Thread-local message for the last failing call on this thread ("" if none). */
+const char* b200attn_last_error(void);
+
+/* Number of SMs of the current device (cached); <= 0 when no CUDA device is usable. */
+int b200attn_sm_count(void);
+
+/* Total number of kernel launches this library has issued in this process (all threads).
+ * Instrumentation for bench.py's `gpu_launches`; has no reference counterpart. */
+int64_t b200attn_launch_count(void);
+
+/*
+ * KV scatter. For every token i in [0, n_tokens) with slot_mapping[i] >= 0:
+ *     k_cache[slot_mapping[i] * row_elems + j] = key  [i * key_row_stride   + j]
+ *     v_cache[slot_mapping[i] * row_elems + j] = value[i * value_row_stride + j]   j < row_elems
+ * Negative slots are skipped (the reference skips -1: attention.py:23-24). Bit-exact copy of
+ * 16-bit elements; offsets are 64-bit (the reference's int32 `slot * D` overflow is not kept).
+ *   row_elems        = num_kv_heads * head_dim (elements per token row, multiple of 8)
+ *   *_row_stride     in elements (value is a strided view in the caller: models/qwen3.py:76-79)
+ *   num_slots        = num_blocks * block_size, bound for slot_mapping (slots >= num_slots are
+ *                      skipped rather than written out of bounds)
+ */
+int b200attn_store_kvcache(const void* key, int64_t key_row_stride, const void* value,
+                           int64_t value_row_stride, void* k_cache, void* v_cache,
+                           const int32_t* slot_mapping, int32_t n_tokens, int32_t row_elems,
+                           int64_t num_slots, int32_t dtype, void* stream);
+
+/* Host-only heuristic: split count for b200attn_decode. Depends only on host-visible sizes
+ * (graph-capture rule: context_lens is device-only under replay, model_runner.py:242-254). */
+int b200attn_decode_pick_splits(int32_t batch, int32_t num_kv_heads, int32_t table_width,
+                                int32_t block_size, int32_t sm_count);
+
+/* Bytes of fp32 workspace b200attn_decode needs for (batch, num_q_heads, head_dim, num_splits).
+ * 0 when num_splits <= 1. */
+size_t b200attn_decode_workspace_bytes(int32_t batch, int32_t num_q_heads, int32_t head_dim,
+                                       int32_t num_splits);
+
+/*
+ * Paged decode attention (one query token per sequence):
+ *   out[b, h, :] = softmax(scale * q[b, h, :] . K[b, :ctx_b, h / G, :]^T) . V[b, :ctx_b, h / G, :]
+ * K/V rows of sequence b, token t live at cache slot
+ *   block_tables[b * table_row_stride + t / block_size] * block_size + t % block_size,
+ * cache layout [num_blocks, block_size, num_kv_heads, head_dim] contiguous. ctx_b =
+ * context_lens[b] (includes the token being decoded). Rows with ctx_b <= 0 produce zeros and
+ * read no table entry; table entries at or beyond ceil(ctx_b / block_size) are never read.
+ *   q   [batch, num_q_heads, head_dim] contiguous;  out same shape/dtype
+ *   workspace: >= b200attn_decode_workspace_bytes(...) bytes when num_splits > 1, else may be NULL
+ */
+int b200attn_decode(const void* q, const void* k_cache, const void* v_cache,
+                    const int32_t* block_tables, int64_t table_row_stride, int32_t table_width,
+                    const int32_t* context_lens, void* out, void* workspace, size_t workspace_bytes,
+                    int32_t batch, int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim,
+                    int32_t block_size, int64_t num_blocks, float scale, int32_t num_splits,
+                    int32_t dtype, void* stream);
+
+/*
+ * Fused decode step of one layer: scatter this step's K/V rows (as b200attn_store_kvcache with
+ * n_tokens == batch) and then run b200attn_decode, ordered on `stream`. Same results as the two
+ * calls in sequence.
+ */
+int b200attn_store_decode(const void* q, const void* key, int64_t key_row_stride, const void* value,
+                          int64_t value_row_stride, const int32_t* slot_mapping, void* k_cache,
+                          void* v_cache, const int32_t* block_tables, int64_t table_row_stride,
+                          int32_t table_width, const int32_t* context_lens, void* out,
+                          void* workspace, size_t workspace_bytes, int32_t batch,
+                          int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim,
+                          int32_t block_size, int64_t num_blocks, float scale, int32_t num_splits,
+                          int32_t dtype, void* stream);
+
+/*
+ * Varlen causal prefill (bottom-right aligned causal mask, as flash_attn_varlen_func):
+ * query row i of sequence s (i < Lq_s = cu_seqlens_q[s+1] - cu_seqlens_q[s]) attends keys
+ * 0 .. Lk_s - Lq_s + i of that sequence (Lk_s = cu_seqlens_k[s+1] - cu_seqlens_k[s]).
+ *   dense  (block_tables == NULL): K/V rows are key/value[cu_seqlens_k[s] + t] with the given
+ *          row strides (elements); k_cache/v_cache ignored.
+ *   paged  (block_tables != NULL): K/V rows come from the cache through block_tables as in
+ *          b200attn_decode; key/value ignored.
+ *   q [total_q, num_q_heads, head_dim] contiguous; out same. Rows with no visible key get zeros.
+ */
+int b200attn_prefill_varlen(const void* q, const void* key, int64_t key_row_stride,
+                            const void* value, int64_t value_row_stride, const void* k_cache,
+                            const void* v_cache, const int32_t* block_tables,
+                            int64_t table_row_stride, int32_t table_width,
+                            const int32_t* cu_seqlens_q, const int32_t* cu_seqlens_k,
+                            int32_t num_seqs, int32_t total_q, int32_t max_seqlen_q,
+                            int32_t max_seqlen_k, void* out, int32_t num_q_heads,
+                            int32_t num_kv_heads, int32_t head_dim, int32_t block_size,
+                            int64_t num_blocks, float scale, int32_t dtype, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200ATTN_H_ */

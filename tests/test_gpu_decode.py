@@ -1,0 +1,210 @@
+"""-m gpu: paged decode attention through the C-ABI vs the fp32 oracle, the flash-attn golden
+vectors, and size-independent properties at BASELINE sizes."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN
+from gpu_util import assert_close, to_dev
+from oracle import attention_oracle as orc
+from tools import golden_cases as gc, synth
+
+pytestmark = pytest.mark.gpu
+
+
+def _decode(d, scale, **kw):
+    from byox_vllm_b200.attention import paged_decode
+
+    m = d["meta"]
+    o = paged_decode(d["q"], d["k_cache"], d["v_cache"], m["context_lens"], m["block_tables"],
+                     scale, **kw)
+    torch.cuda.synchronize()
+    return o
+
+
+@pytest.mark.parametrize("case", gc.DECODE_CASES, ids=[c[0] for c in gc.DECODE_CASES])
+@pytest.mark.parametrize("splits", [None, 1, 2, 5])
+def test_decode_matches_oracle_and_flash_attn(cuda_dev, case, splits):
+    name, ctx, Hq, Hkv, seed = case
+    c = synth.decode_case(len(ctx), ctx, Hq, Hkv, seed=seed)
+    d = to_dev(c, cuda_dev)
+    got = _decode(d, c.scale, num_splits=splits)
+    assert got.dtype == torch.bfloat16 and got.shape == c.q.shape
+    want = orc.paged_decode_ref(c.q, c.k_cache, c.v_cache, c.meta["context_lens"],
+                                c.meta["block_tables"], c.scale)
+    assert_close(got, want, f"{name} vs oracle")
+    g = np.load(GOLDEN / f"fa_decode_{name}.npz")
+    fa = torch.from_numpy(g["out"]).view(torch.bfloat16)
+    assert_close(got, fa, f"{name} vs flash-attn golden")
+
+
+def test_decode_padding_rows_and_stale_tables(cuda_dev):
+    """CUDA-graph replay semantics (model_runner.py:242-254): rows with context_lens == 0 give
+    zeros and read no table entry; entries beyond ceil(ctx/256) are -1 / garbage and never read;
+    the table may be wider than needed (row stride = ceil(max_model_len/256))."""
+    c = synth.decode_case(6, [300, 1, 700, 256, 513, 90], 16, 8, seed=31)
+    d = to_dev(c, cuda_dev)
+    m = d["meta"]
+    lens = m["context_lens"].clone()
+    lens[1] = 0
+    lens[4] = 0
+    W = 16
+    wide = torch.full((6, W), 2 ** 30, dtype=torch.int32, device=cuda_dev)  # poison
+    bt = c.meta["block_tables"]
+    for b, s in enumerate(c.seqs):
+        n = len(s.block_table)
+        wide[b, :n] = bt[b, :n].to(cuda_dev)
+    wide[1] = -1
+    wide[4] = 2 ** 30
+    from byox_vllm_b200.attention import paged_decode
+
+    for splits in (1, 3, None):
+        got = paged_decode(d["q"], d["k_cache"], d["v_cache"], lens, wide[:, :W], c.scale,
+                           num_splits=splits)
+        torch.cuda.synchronize()
+        want = orc.paged_decode_ref(c.q, c.k_cache, c.v_cache, lens.cpu(), wide.cpu(), c.scale)
+        assert torch.count_nonzero(got[1]) == 0 and torch.count_nonzero(got[4]) == 0
+        assert_close(got, want, f"padding rows, splits={splits}")
+    # a sliced (non-contiguous rows) table view, like graph_vars["block_tables"][:bs]
+    big = torch.full((8, 32), -1, dtype=torch.int32, device=cuda_dev)
+    big[:6, :W] = wide
+    got = paged_decode(d["q"], d["k_cache"], d["v_cache"], lens, big[:6], c.scale)
+    torch.cuda.synchronize()
+    assert_close(got, want, "wide table view")
+
+
+def test_decode_ignores_garbage_beyond_context(cuda_dev):
+    """Slots past ctx inside the last page may hold anything (NaN/Inf): never leaks into out."""
+    c = synth.decode_case(3, [10, 257, 600], 8, 2, seed=32)
+    for b, s in enumerate(c.seqs):
+        last = s.block_table[-1]
+        used = s.num_tokens - (len(s.block_table) - 1) * 256
+        c.k_cache[last, used:] = float("nan")
+        c.v_cache[last, used:] = float("inf")
+    d = to_dev(c, cuda_dev)
+    want = orc.paged_decode_ref(c.q, c.k_cache, c.v_cache, c.meta["context_lens"],
+                                c.meta["block_tables"], c.scale)
+    for splits in (1, 2):
+        got = _decode(d, c.scale, num_splits=splits)
+        assert torch.isfinite(got.float()).all()
+        assert_close(got, want, "garbage beyond ctx")
+
+
+def test_fused_store_decode_equals_store_then_decode(cuda_dev):
+    from byox_vllm_b200.attention import paged_decode, store_kvcache
+
+    c = synth.decode_case(5, [1, 256, 257, 1000, 77], 16, 8, seed=33)
+    d = to_dev(c, cuda_dev)
+    m = d["meta"]
+    kc2, vc2 = d["k_cache"].clone(), d["v_cache"].clone()
+    o1 = paged_decode(d["q"], d["k_cache"], d["v_cache"], m["context_lens"], m["block_tables"],
+                      c.scale, key=d["k"], value=d["v"], slot_mapping=m["slot_mapping"])
+    store_kvcache(d["k"], d["v"], kc2, vc2, m["slot_mapping"])
+    o2 = paged_decode(d["q"], kc2, vc2, m["context_lens"], m["block_tables"], c.scale)
+    torch.cuda.synchronize()
+    assert torch.equal(o1.view(torch.int16), o2.view(torch.int16))
+    assert torch.equal(kc2.view(torch.int16), d["k_cache"].view(torch.int16))
+    # and against the oracle's forward (scatter + decode)
+    ctx = type("Ctx", (), dict(c.meta))()
+    want = orc.attention_forward_ref(c.q, c.k, c.v, c.k_cache, c.v_cache, ctx, c.scale)
+    assert_close(o1, want.squeeze(1), "fused store+decode vs oracle forward")
+    assert torch.equal(d["k_cache"].cpu().view(torch.int16), c.k_cache.view(torch.int16))
+    assert torch.equal(d["v_cache"].cpu().view(torch.int16), c.v_cache.view(torch.int16))
+
+
+def test_decode_under_cuda_graph_capture_and_replay(cuda_dev):
+    """Mimics ModelRunner._capture_cudagraph / _run_model (model_runner.py:242-297): capture with
+    all-zero metadata buffers at a rounded-up batch size, then replay with live metadata copied
+    into the static buffers (slot_mapping padded with -1, context_lens with 0, stale tables)."""
+    from byox_vllm_b200.attention import Attention
+    from byox_vllm_b200.context import reset_context, set_context
+
+    dev = cuda_dev
+    Hq, Hkv, D, bs_graph, W = 16, 8, 128, 8, 12
+    live = synth.decode_case(5, [300, 1, 700, 256, 513], Hq, Hkv, seed=34)
+    d = to_dev(live, dev)
+    attn = Attention(Hq, D, live.scale, Hkv)
+    attn.k_cache, attn.v_cache = d["k_cache"], d["v_cache"]
+    g_q = torch.zeros(bs_graph, Hq, D, dtype=torch.bfloat16, device=dev)
+    g_k = torch.zeros(bs_graph, Hkv, D, dtype=torch.bfloat16, device=dev)
+    g_v = torch.zeros(bs_graph, Hkv, D, dtype=torch.bfloat16, device=dev)
+    g_slots = torch.zeros(bs_graph, dtype=torch.int32, device=dev)
+    g_lens = torch.zeros(bs_graph, dtype=torch.int32, device=dev)
+    g_bt = torch.zeros(bs_graph, W, dtype=torch.int32, device=dev)
+    g_out = torch.zeros(bs_graph, 1, Hq, D, dtype=torch.bfloat16, device=dev)
+    slot0_before = (d["k_cache"].view(-1, Hkv * D)[0].clone(),
+                    d["v_cache"].view(-1, Hkv * D)[0].clone())
+    set_context(False, slot_mapping=g_slots, context_lens=g_lens, block_tables=g_bt)
+    g_out.copy_(attn(g_q, g_k, g_v))  # warm-up (writes the dummy row to slot 0, like the reference)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        g_out.copy_(attn(g_q, g_k, g_v))
+    torch.cuda.synchronize()
+    reset_context()
+    d["k_cache"].view(-1, Hkv * D)[0].copy_(slot0_before[0])  # undo the capture-time dummy write
+    d["v_cache"].view(-1, Hkv * D)[0].copy_(slot0_before[1])
+    # two replays with different live batches through the same graph
+    for n_live in (5, 3):
+        m = d["meta"]
+        g_q[:n_live] = d["q"][:n_live]
+        g_k[:n_live] = d["k"][:n_live]
+        g_v[:n_live] = d["v"][:n_live]
+        g_slots.fill_(-1)
+        g_slots[:n_live] = m["slot_mapping"][:n_live]
+        g_lens.zero_()
+        g_lens[:n_live] = m["context_lens"][:n_live]
+        g_bt[:n_live, : m["block_tables"].size(1)] = m["block_tables"][:n_live]
+        graph.replay()
+        torch.cuda.synchronize()
+        kc, vc = live.k_cache.clone(), live.v_cache.clone()
+        ctx = type("Ctx", (), dict(live.meta))()
+        want = orc.attention_forward_ref(live.q, live.k, live.v, kc, vc, ctx, live.scale)
+        assert_close(g_out[:n_live], want[:n_live], f"graph replay n_live={n_live}")
+        assert torch.count_nonzero(g_out[n_live:]) == 0
+        rows = live.meta["slot_mapping"][:n_live].long()
+        assert torch.equal(d["k_cache"].view(-1, Hkv * D)[rows.to(dev)].cpu().view(torch.int16),
+                           kc.view(-1, Hkv * D)[rows].view(torch.int16))
+
+
+@pytest.mark.parametrize("shape", [(64, 4096, 32, 8), (128, 4096, 4, 1), (4, 32768, 32, 8)],
+                         ids=["b64_ctx4k_32_8", "b128_ctx4k_4_1", "b4_ctx32k_32_8"])
+def test_decode_properties_at_baseline_sizes(cuda_dev, shape):
+    """Sizes the oracle cannot finish in seconds: (a) constant V -> output equals the constant
+    (softmax weights sum to 1); (b) output is invariant to the physical page permutation;
+    (c) split count does not change the result beyond tolerance; (d) a sampled subset of rows
+    matches the oracle."""
+    from byox_vllm_b200.attention import paged_decode
+
+    B, ctx, Hq, Hkv = shape
+    dev = cuda_dev
+    c = synth.decode_case(B, ctx, Hq, Hkv, seed=40, device=dev)
+    m = {k: (v.to(dev) if isinstance(v, torch.Tensor) else v) for k, v in c.meta.items()}
+    o = paged_decode(c.q, c.k_cache, c.v_cache, m["context_lens"], m["block_tables"], c.scale)
+    # (c)
+    o1 = paged_decode(c.q, c.k_cache, c.v_cache, m["context_lens"], m["block_tables"], c.scale,
+                      num_splits=1)
+    o7 = paged_decode(c.q, c.k_cache, c.v_cache, m["context_lens"], m["block_tables"], c.scale,
+                      num_splits=7)
+    assert_close(o, o1, "auto splits vs 1")
+    assert_close(o7, o1, "7 splits vs 1")
+    # (b) move every page to a new physical block
+    nb = c.k_cache.shape[0]
+    perm = torch.randperm(nb, device=dev)
+    inv = torch.empty_like(perm)
+    inv[perm] = torch.arange(nb, device=dev)
+    kc2, vc2 = c.k_cache[perm], c.v_cache[perm]  # new block i holds old block perm[i]
+    bt2 = inv[m["block_tables"].clamp_min(0).long()].to(torch.int32)
+    o_perm = paged_decode(c.q, kc2, vc2, m["context_lens"], bt2, c.scale, num_splits=1)
+    assert torch.equal(o_perm.view(torch.int16), o1.view(torch.int16))
+    del kc2, vc2
+    # (a)
+    vconst = torch.full_like(c.v_cache, 0.75)
+    oc = paged_decode(c.q, c.k_cache, vconst, m["context_lens"], m["block_tables"], c.scale)
+    assert (oc.float() - 0.75).abs().max().item() <= 1e-2
+    del vconst
+    # (d) rows 0 and B-1 against the oracle
+    for b in (0, B - 1):
+        want = orc.paged_decode_ref(c.q[b:b + 1].cpu(), c.k_cache.cpu(), c.v_cache.cpu(),
+                                    c.meta["context_lens"][b:b + 1],
+                                    c.meta["block_tables"][b:b + 1], c.scale)
+        assert_close(o[b:b + 1], want, f"row {b} vs oracle")

@@ -1,0 +1,134 @@
+"""-m gpu: varlen causal prefill (dense and paged-prefix) through the C-ABI vs the fp32 oracle,
+the flash-attn golden vectors and size-independent properties."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN
+from gpu_util import assert_close, to_dev
+from oracle import attention_oracle as orc
+from tools import golden_cases as gc, synth
+
+pytestmark = pytest.mark.gpu
+
+
+def _forward(dev, c, Hq, Hkv):
+    """Attention.forward on the device for a prefill case; returns (out, device dict)."""
+    from byox_vllm_b200.attention import Attention
+    from byox_vllm_b200.context import reset_context, set_context
+    from byox_vllm_b200.metadata import context_kwargs
+
+    d = to_dev(c, dev)
+    attn = Attention(Hq, 128, c.scale, Hkv)
+    attn.k_cache, attn.v_cache = d["k_cache"], d["v_cache"]
+    set_context(**context_kwargs(c.meta, dev))
+    try:
+        o = attn(d["q"], d["k"], d["v"])
+        torch.cuda.synchronize()
+    finally:
+        reset_context()
+    return o, d
+
+
+@pytest.mark.parametrize("case", gc.PREFILL_CASES, ids=[c[0] for c in gc.PREFILL_CASES])
+def test_prefill_matches_oracle_and_flash_attn(cuda_dev, case):
+    name, lens, cached, Hq, Hkv, seed = case
+    c = synth.prefill_case(lens, Hq, Hkv, cached=cached, seed=seed)
+    got, d = _forward(cuda_dev, c, Hq, Hkv)
+    assert got.shape == c.q.shape and got.dtype == torch.bfloat16
+    ctx = type("Ctx", (), dict(c.meta))()
+    want = orc.attention_forward_ref(c.q, c.k, c.v, c.k_cache, c.v_cache, ctx, c.scale)
+    assert_close(got, want, f"{name} vs oracle")
+    # the scatter that precedes attention left the cache bit-identical to the oracle's
+    assert torch.equal(d["k_cache"].cpu().view(torch.int16), c.k_cache.view(torch.int16))
+    assert torch.equal(d["v_cache"].cpu().view(torch.int16), c.v_cache.view(torch.int16))
+    g = np.load(GOLDEN / f"fa_prefill_{name}.npz")
+    fa = torch.from_numpy(g["out"]).view(torch.bfloat16)
+    assert_close(got, fa, f"{name} vs flash-attn golden")
+
+
+@pytest.mark.parametrize("Hq,Hkv", [(16, 8), (32, 8), (8, 1), (4, 1)])
+def test_prefill_more_shapes_vs_oracle(cuda_dev, Hq, Hkv):
+    lens = [1, 2, 64, 127, 128, 129, 300]
+    c = synth.prefill_case(lens, Hq, Hkv, seed=50 + Hq)
+    got, _ = _forward(cuda_dev, c, Hq, Hkv)
+    ctx = type("Ctx", (), dict(c.meta))()
+    want = orc.attention_forward_ref(c.q, c.k, c.v, c.k_cache, c.v_cache, ctx, c.scale)
+    assert_close(got, want, f"dense {Hq}/{Hkv}")
+    c = synth.prefill_case([257, 520, 1100], Hq, Hkv, cached=[256, 256, 1024], seed=60 + Hq)
+    got, _ = _forward(cuda_dev, c, Hq, Hkv)
+    ctx = type("Ctx", (), dict(c.meta))()
+    want = orc.attention_forward_ref(c.q, c.k, c.v, c.k_cache, c.v_cache, ctx, c.scale)
+    assert_close(got, want, f"paged prefix {Hq}/{Hkv}")
+
+
+def test_warmup_path_without_cache(cuda_dev):
+    """_warmup_model (model_runner.py:102-113): empty caches, no slots, dense attention."""
+    from byox_vllm_b200.attention import Attention
+    from byox_vllm_b200.context import reset_context, set_context
+    from byox_vllm_b200.metadata import SeqState, context_kwargs, prepare_prefill
+
+    dev = cuda_dev
+    meta = prepare_prefill([SeqState(300), SeqState(300)], 256)
+    g = torch.Generator().manual_seed(5)
+    q, k, v = synth._qkv(600, 16, 8, 128, g, "cpu")
+    attn = Attention(16, 128, 128 ** -0.5, 8)
+    set_context(**context_kwargs(meta, dev))
+    try:
+        o = attn(q.to(dev), k.to(dev), v.to(dev))  # v.to() keeps the strided view's strides
+        torch.cuda.synchronize()
+    finally:
+        reset_context()
+    want = orc.prefill_varlen_ref(q, k, v, meta["cu_seqlens_q"], meta["cu_seqlens_k"], 128 ** -0.5)
+    assert_close(o, want, "warm-up dense prefill")
+
+
+def test_prefill_last_row_equals_decode(cuda_dev):
+    """Consistency between the two kernels: the last prefill row of a sequence is a decode step
+    over the same keys (bottom-right causal alignment)."""
+    from byox_vllm_b200.attention import paged_decode
+
+    c = synth.prefill_case([700, 129], 16, 8, seed=70)
+    got, d = _forward(cuda_dev, c, 16, 8)
+    ends = c.meta["cu_seqlens_q"][1:].long() - 1
+    qd = d["q"][ends.to(cuda_dev)]
+    lens = torch.tensor([700, 129], dtype=torch.int32, device=cuda_dev)
+    from byox_vllm_b200.metadata import prepare_block_tables
+
+    bt = prepare_block_tables(c.seqs).to(cuda_dev)
+    od = paged_decode(qd, d["k_cache"], d["v_cache"], lens, bt, c.scale)
+    torch.cuda.synchronize()
+    assert_close(od, got[ends.to(cuda_dev)], "decode vs last prefill row")
+
+
+def test_prefill_properties_at_warmup_size(cuda_dev):
+    """4 x 4096 tokens (the reference's warm-up batch, model_runner.py:110-112), Hq 32 / Hkv 8:
+    (a) causality — changing keys/values after position p leaves rows <= p bit-identical;
+    (b) constant V gives the constant; (c) sampled rows match the oracle."""
+    from byox_vllm_b200.attention import prefill_varlen
+
+    dev = cuda_dev
+    L, S, Hq, Hkv = 4096, 4, 32, 8
+    g = torch.Generator(device=dev).manual_seed(1)
+    q, k, v = synth._qkv(L * S, Hq, Hkv, 128, g, dev)
+    cu = torch.arange(0, S + 1, dtype=torch.int32, device=dev) * L
+    scale = 128 ** -0.5
+    o = prefill_varlen(q, k, v, cu, cu, L, L, scale)
+    p = 2500
+    k2, v2 = k.clone(), v.contiguous().clone()
+    k2[p + 1:L] = 3.0
+    v2[p + 1:L] = -5.0
+    o2 = prefill_varlen(q, k2, v2, cu, cu, L, L, scale)
+    torch.cuda.synchronize()
+    assert torch.equal(o[:p + 1].view(torch.int16), o2[:p + 1].view(torch.int16))
+    assert torch.equal(o[L:].view(torch.int16), o2[L:].view(torch.int16))
+    oc = prefill_varlen(q, k, torch.full_like(v2, 0.5), cu, cu, L, L, scale)
+    assert (oc.float() - 0.5).abs().max().item() <= 1e-2
+    rows = [0, 1, 63, 64, 2047, 4095]
+    for r in rows:
+        i = L + r  # second sequence
+        s = torch.einsum("hd,khd->hk", q[i].float(),
+                         k[L:L + r + 1].float().repeat_interleave(Hq // Hkv, 1)) * scale
+        want = torch.einsum("hk,khd->hd", torch.softmax(s, -1),
+                            v[L:L + r + 1].float().repeat_interleave(Hq // Hkv, 1))
+        assert_close(o[i], want.cpu(), f"row {r}")

@@ -1,0 +1,140 @@
+"""Host-side logic that needs no GPU: argument validation of the C-ABI (errors are returned
+before any CUDA call), the split heuristic, the module surface and the install shim."""
+import importlib
+import sys
+import textwrap
+
+import pytest
+import torch
+
+from byox_vllm_b200 import _lib
+
+
+@pytest.fixture(scope="module")
+def lib(built_lib):
+    return _lib.load()
+
+
+def test_pick_splits_is_host_only_and_sane(lib):
+    sm = 148
+    # big batches never split; tiny batches with long tables split; never more splits than
+    # 256-token pieces of the longest possible context
+    assert lib.b200attn_decode_pick_splits(512, 8, 4, 256, sm) == 1
+    assert lib.b200attn_decode_pick_splits(128, 8, 16, 256, sm) == 1
+    s = lib.b200attn_decode_pick_splits(1, 8, 512, 256, sm)
+    assert 16 <= s <= 128
+    assert lib.b200attn_decode_pick_splits(1, 8, 1, 256, sm) == 1
+    for b in (1, 2, 4, 8, 16, 64):
+        for w in (1, 4, 16, 128):
+            s = lib.b200attn_decode_pick_splits(b, 1, w, 256, sm)
+            assert 1 <= s <= max(1, w)
+    assert lib.b200attn_decode_pick_splits(4, 8, 16, 256, 0) >= 1  # unknown SM count -> 148
+
+
+def test_workspace_bytes(lib):
+    assert lib.b200attn_decode_workspace_bytes(4, 16, 128, 1) == 0
+    n = lib.b200attn_decode_workspace_bytes(4, 16, 128, 3)
+    assert n == 4 * 16 * 3 * (128 + 1) * 4
+    assert lib.b200attn_decode_workspace_bytes(4, 16, 64, 3) == 0  # unsupported head_dim
+
+
+def test_argument_errors_have_codes_and_messages(lib):
+    # all rejected before touching CUDA, so this runs without a GPU
+    rc = lib.b200attn_store_kvcache(None, 1024, None, 1024, None, None, None, 4, 1024, 64, 0, None)
+    assert rc == _lib.E_BADARG and b"null" in lib.b200attn_last_error()
+    rc = lib.b200attn_store_kvcache(16, 1024, 16, 1024, 16, 16, 16, 4, 1020, 64, 0, None)
+    assert rc == _lib.E_UNSUPPORTED
+    rc = lib.b200attn_store_kvcache(16, 1024, 16, 1024, 16, 16, 16, 4, 1024, 64, 7, None)
+    assert rc == _lib.E_UNSUPPORTED and b"dtype" in lib.b200attn_last_error()
+    rc = lib.b200attn_store_kvcache(16, 1024, 16, 1024, 16, 16, 16, 0, 1024, 64, 0, None)
+    assert rc == 0  # empty batch is a no-op
+    rc = lib.b200attn_decode(16, 16, 16, 16, 4, 4, 16, 16, None, 0, 2, 16, 8, 64, 256, 8, 0.1, 1, 0,
+                             None)
+    assert rc == _lib.E_UNSUPPORTED and b"head_dim" in lib.b200attn_last_error()
+    rc = lib.b200attn_decode(16, 16, 16, 16, 4, 4, 16, 16, None, 0, 2, 16, 5, 128, 256, 8, 0.1, 1, 0,
+                             None)
+    assert rc == _lib.E_BADARG  # Hq % Hkv != 0
+    rc = lib.b200attn_decode(16, 16, 16, 16, 4, 4, 16, 16, None, 0, 2, 16, 8, 128, 256, 8, 0.1, 4, 0,
+                             None)
+    assert rc == _lib.E_WORKSPACE
+    rc = lib.b200attn_prefill_varlen(16, None, 0, None, 0, None, None, None, 0, 0, 16, 16, 1, 8, 8,
+                                     8, 16, 16, 8, 128, 0, 0, 0.1, 0, None)
+    assert rc == _lib.E_BADARG  # dense prefill without key/value
+    with pytest.raises(_lib.B200AttnError) as ei:
+        _lib.check("b200attn_decode", lib.b200attn_decode(
+            16, 16, 16, 16, 4, 4, 16, 16, None, 0, 2, 16, 8, 64, 256, 8, 0.1, 1, 0, None))
+    assert ei.value.code == _lib.E_UNSUPPORTED
+
+
+def test_attention_module_surface_and_no_cpu_fallback(built_lib):
+    from byox_vllm_b200.attention import Attention, store_kvcache
+    from byox_vllm_b200.context import reset_context, set_context
+
+    a = Attention(16, 128, 128 ** -0.5, 8)  # positional ctor as reference models/qwen3.py:60-65
+    assert (a.num_heads, a.head_dim, a.num_kv_heads) == (16, 128, 8)
+    assert a.k_cache.numel() == 0 and a.v_cache.numel() == 0  # placeholders (attention.py:65)
+    assert hasattr(a, "k_cache") and hasattr(a, "v_cache")  # what ModelRunner looks for
+    assert list(a.state_dict().keys()) == []  # caches are plain attributes, not buffers
+    q = torch.zeros(2, 16, 128, dtype=torch.bfloat16)
+    k = torch.zeros(2, 8, 128, dtype=torch.bfloat16)
+    set_context(True, torch.tensor([0, 2], dtype=torch.int32), torch.tensor([0, 2], dtype=torch.int32),
+                2, 2, torch.zeros(0, dtype=torch.int32), None, None)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        a(q, k, k)
+    reset_context()
+    kc = torch.zeros(1, 16, 8, 128, dtype=torch.bfloat16)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        store_kvcache(k, k, kc, kc.clone(), torch.zeros(2, dtype=torch.int32))
+    with pytest.raises(AssertionError):  # reference precondition attention.py:46
+        store_kvcache(k, k, kc, kc.clone(), torch.zeros(3, dtype=torch.int32))
+
+
+def test_product_never_imports_oracle():
+    from conftest import ROOT
+
+    for path in (ROOT / "byox_vllm_b200").rglob("*"):
+        if path.suffix in (".py", ".cu", ".cuh", ".h"):
+            text = path.read_text()
+            assert "oracle" not in text.replace("oracle/", "").lower() or path.name == "__init__.py", path
+            assert "import triton" not in text and "flash_attn import" not in text, path
+
+
+def test_install_under_a_nanovllm_package(tmp_path, monkeypatch, built_lib):
+    """install() must make `from nanovllm.layers.attention import Attention` resolve to ours and
+    route set_context() of nanovllm.utils.context into our forward — checked on a stand-in package
+    with the reference's module layout (the real one needs CUDA-only deps to import)."""
+    pkg = tmp_path / "nanovllm"
+    (pkg / "utils").mkdir(parents=True)
+    (pkg / "layers").mkdir()
+    (pkg / "models").mkdir()
+    for d in (pkg, pkg / "utils", pkg / "layers", pkg / "models"):
+        (d / "__init__.py").write_text("")
+    (pkg / "utils" / "context.py").write_text(textwrap.dedent("""
+        from dataclasses import dataclass
+        @dataclass
+        class Context:
+            is_prefill: bool = False
+            marker: str = "reference-context"
+        _CONTEXT = Context()
+        def get_context():
+            return _CONTEXT
+    """))
+    (pkg / "layers" / "attention.py").write_text("raise ImportError('needs triton + flash_attn')\n")
+    (pkg / "models" / "qwen3.py").write_text("from nanovllm.layers.attention import Attention\n")
+    monkeypatch.syspath_prepend(str(tmp_path))
+    for m in [m for m in sys.modules if m == "nanovllm" or m.startswith("nanovllm.")]:
+        monkeypatch.delitem(sys.modules, m)
+    from byox_vllm_b200 import attention as ours, install
+
+    install.install()
+    try:
+        qwen3 = importlib.import_module("nanovllm.models.qwen3")
+        assert qwen3.Attention is ours.Attention
+        assert ours.get_context().marker == "reference-context"
+    finally:
+        install.uninstall()
+        for m in [m for m in sys.modules if m == "nanovllm" or m.startswith("nanovllm.")]:
+            sys.modules.pop(m, None)
+    from byox_vllm_b200.context import get_context
+
+    assert ours.get_context is get_context
