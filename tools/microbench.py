@@ -1,0 +1,261 @@
+"""Kernel-level microbenchmarks on one B200: ours vs the reference's kernels on the same inputs.
+
+    gpurun -- python tools/microbench.py [decode] [store] [prefill] [--quick]
+
+Writes one JSON object per line to gpurun_out/microbench.jsonl. The reference bars are the kernels
+the reference calls (flash_attn_with_kvcache / flash_attn_varlen_func of flash-attn 2.8.3, and a
+Triton scatter equivalent to the reference's store_kvcache_kernel) — they are measured beside
+ours, never used by the product path. SURVEY.md §7.3(e), §8(d) config C5.
+
+Timing: CUDA events on the current stream around ONE call, L2 flushed (512 MiB memset) before
+every timed call, 3 warm-ups, `iters` timed calls, min and median reported. Bytes are the
+algorithmic bytes of SURVEY.md §8(d).
+"""
+from __future__ import annotations
+
+import json
+import statistics
+import sys
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parents[1]
+sys.path.insert(0, str(ROOT))
+
+import torch  # noqa: E402
+
+D, BLOCK = 128, 256
+PEAK = 6543.4
+_p = ROOT / "MEASURED_PEAKS.json"
+if _p.exists():
+    PEAK = json.loads(_p.read_text())["hbm_gbs"]
+TF_PEAK = json.loads(_p.read_text())["bf16_tflops"] if _p.exists() else 1590.0
+
+_flush = None
+
+
+def timed(fn, iters=10, warm=3):
+    global _flush
+    if _flush is None:
+        _flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(iters):
+        _flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    return min(ts), statistics.median(ts)
+
+
+def decode_inputs(B, ctx, Hq, Hkv, ragged=False, seed=0):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    if ragged:
+        lens = torch.randint(ctx // 2, ctx + 1, (B,), generator=g, device="cuda", dtype=torch.int32)
+    else:
+        lens = torch.full((B,), ctx, dtype=torch.int32, device="cuda")
+    pages = (lens + BLOCK - 1) // BLOCK
+    W = int(pages.max())
+    nb = B * W + 4
+    perm = torch.randperm(nb, generator=g, device="cuda")[:B * W].to(torch.int32).view(B, W)
+    ar = torch.arange(W, device="cuda").unsqueeze(0)
+    bt = torch.where(ar < pages.unsqueeze(1), perm, torch.full_like(perm, -1))
+    kc = torch.empty(nb, BLOCK, Hkv, D, dtype=torch.bfloat16, device="cuda").normal_(generator=g)
+    vc = torch.empty(nb, BLOCK, Hkv, D, dtype=torch.bfloat16, device="cuda").normal_(generator=g)
+    q = torch.empty(B, Hq, D, dtype=torch.bfloat16, device="cuda").normal_(generator=g)
+    toks = int(lens.sum())
+    alg = toks * Hkv * D * 2 * 2 + 2 * B * Hq * D * 2 + 4 * int(pages.sum()) + 4 * B
+    return q, kc, vc, lens, bt, alg
+
+
+DECODE_SHAPES = [  # (B, ctx, Hq, Hkv)
+    (128, 4096, 32, 8), (64, 4096, 32, 8), (128, 4096, 4, 1), (256, 8192, 8, 1),
+    (256, 640, 16, 8), (1, 131072, 32, 8), (8, 16384, 32, 8), (512, 1024, 32, 8),
+    (1, 1024, 32, 8), (64, 8192, 32, 8), (16, 4096, 32, 8), (4, 4096, 32, 8),
+    (32, 2048, 16, 8), (1, 4096, 16, 8), (128, 4096, 16, 4), (128, 4096, 8, 2),
+    (2, 32768, 32, 8), (256, 1024, 16, 8),
+]
+DECODE_QUICK = [(128, 4096, 32, 8), (1, 131072, 32, 8), (256, 640, 16, 8), (8, 16384, 32, 8),
+                (1, 1024, 32, 8), (128, 4096, 4, 1)]
+
+
+def bench_decode(out, quick):
+    from flash_attn import flash_attn_with_kvcache
+
+    from byox_vllm_b200.attention import decode_num_splits, paged_decode
+
+    for (B, ctx, Hq, Hkv) in (DECODE_QUICK if quick else DECODE_SHAPES):
+        for ragged in ((False,) if quick else (False, True)):
+            q, kc, vc, lens, bt, alg = decode_inputs(B, ctx, Hq, Hkv, ragged)
+            scale = D ** -0.5
+            o = torch.empty_like(q)
+            splits = decode_num_splits(B, Hkv, bt.size(1), BLOCK)
+            t_min, t_med = timed(lambda: paged_decode(q, kc, vc, lens, bt, scale, out=o))
+            q4 = q.unsqueeze(1)
+            btc = bt.clamp_min(0)
+            f_min, f_med = timed(lambda: flash_attn_with_kvcache(
+                q4, kc, vc, cache_seqlens=lens, block_table=btc, softmax_scale=scale, causal=True))
+            ref = flash_attn_with_kvcache(q4, kc, vc, cache_seqlens=lens, block_table=btc,
+                                          softmax_scale=scale, causal=True).squeeze(1)
+            err = (o.float() - ref.float()).abs().max().item()
+            rec = dict(kind="decode", B=B, ctx=ctx, Hq=Hq, Hkv=Hkv, ragged=ragged, splits=splits,
+                       alg_bytes=alg, ours_us=t_med * 1e3, ours_min_us=t_min * 1e3,
+                       ours_gbs=alg / t_med / 1e6, ours_frac=alg / t_med / 1e6 / PEAK,
+                       fa2_us=f_med * 1e3, fa2_gbs=alg / f_med / 1e6, speedup=f_med / t_med,
+                       max_abs_diff_vs_fa2=err)
+            out.write(json.dumps(rec) + "\n")
+            out.flush()
+            print(f"decode B={B:4d} ctx={ctx:6d} {Hq}/{Hkv} rag={int(ragged)} S={splits:3d}: ours "
+                  f"{t_med * 1e3:8.1f} us {rec['ours_gbs']:7.0f} GB/s ({rec['ours_frac']:.2f}) | "
+                  f"fa2 {f_med * 1e3:8.1f} us {rec['fa2_gbs']:7.0f} GB/s | x{rec['speedup']:.2f} "
+                  f"err {err:.4f}", flush=True)
+            del q, kc, vc, lens, bt
+            torch.cuda.empty_cache()
+
+
+def bench_store(out, quick):
+    import triton
+    import triton.language as tl
+
+    from byox_vllm_b200.attention import store_kvcache
+
+    # A Triton scatter with the same program structure as the reference's kernel (one program per
+    # token, one row of Hkv*D elements per program; reference layers/attention.py:10-31), written
+    # here only as the measured bar.
+    @triton.jit
+    def bar_kernel(k_ptr, ks, v_ptr, vs, kc_ptr, vc_ptr, slot_ptr, ROW: tl.constexpr):
+        i = tl.program_id(0)
+        slot = tl.load(slot_ptr + i)
+        if slot == -1:
+            return
+        offs = tl.arange(0, ROW)
+        tl.store(kc_ptr + slot * ROW + offs, tl.load(k_ptr + i * ks + offs))
+        tl.store(vc_ptr + slot * ROW + offs, tl.load(v_ptr + i * vs + offs))
+
+    for N in ((128, 16384) if quick else (1, 128, 256, 512, 2048, 16384)):
+        for Hkv, Hq in ((8, 16), (8, 32), (1, 4)):
+            row = Hkv * D
+            g = torch.Generator(device="cuda").manual_seed(N)
+            k = torch.empty(N, Hkv, D, dtype=torch.bfloat16, device="cuda").normal_(generator=g)
+            packed = torch.empty(N, (Hq + 2 * Hkv) * D, dtype=torch.bfloat16,
+                                 device="cuda").normal_(generator=g)
+            v = packed[:, (Hq + Hkv) * D:].view(N, Hkv, D)
+            nb = max(64, (N + BLOCK - 1) // BLOCK * 2)
+            kc = torch.zeros(nb, BLOCK, Hkv, D, dtype=torch.bfloat16, device="cuda")
+            vc = torch.zeros_like(kc)
+            kc2, vc2 = torch.zeros_like(kc), torch.zeros_like(kc)
+            slots = torch.randperm(nb * BLOCK, generator=g, device="cuda")[:N].to(torch.int32)
+            alg = N * row * 2 * 2 * 2 + 4 * N
+            t_min, t_med = timed(lambda: store_kvcache(k, v, kc, vc, slots), iters=20)
+            f_min, f_med = timed(lambda: bar_kernel[(N,)](k, k.stride(0), v, v.stride(0), kc2, vc2,
+                                                          slots, row), iters=20)
+            same = torch.equal(kc, kc2) and torch.equal(vc, vc2)
+            rec = dict(kind="store", N=N, Hkv=Hkv, Hq=Hq, alg_bytes=alg, ours_us=t_med * 1e3,
+                       ours_min_us=t_min * 1e3, ours_gbs=alg / t_med / 1e6,
+                       triton_us=f_med * 1e3, triton_min_us=f_min * 1e3,
+                       triton_gbs=alg / f_med / 1e6, bit_equal=same)
+            out.write(json.dumps(rec) + "\n")
+            out.flush()
+            print(f"store N={N:6d} Hkv={Hkv}: ours {t_med * 1e3:7.1f} us {rec['ours_gbs']:7.0f} GB/s"
+                  f" | triton {f_med * 1e3:7.1f} us {rec['triton_gbs']:7.0f} GB/s equal={same}",
+                  flush=True)
+
+
+PREFILL_SHAPES = [  # (lens list spec, cached, Hq, Hkv)
+    ("4x4096", [4096] * 4, None, 32, 8), ("4x4096", [4096] * 4, None, 16, 8),
+    ("16x1024", [1024] * 16, None, 16, 8), ("1x16384", [16384], None, 32, 8),
+    ("2x8192", [8192] * 2, None, 8, 1), ("bench24", None, None, 16, 8),
+    ("32x(7680+512)", [8192] * 32, [7680] * 32, 8, 1), ("8x(3840+256)", [4096] * 8, [3840] * 8, 32, 8),
+]
+
+
+def prefill_flops(lens, cached, Hq):
+    fl = 0
+    for n, c in zip(lens, cached):
+        lq = n - c
+        fl += 4 * Hq * D * (lq * c + lq * (lq + 1) // 2)
+    return fl
+
+
+def bench_prefill(out, quick):
+    import random
+
+    from flash_attn import flash_attn_varlen_func
+
+    from byox_vllm_b200 import metadata as md
+    from byox_vllm_b200.attention import prefill_varlen
+
+    shapes = PREFILL_SHAPES[:3] if quick else PREFILL_SHAPES
+    for name, lens, cached, Hq, Hkv in shapes:
+        if lens is None:
+            rng = random.Random(0)
+            lens = [rng.randint(100, 1024) for _ in range(24)]
+        cached = cached or [0] * len(lens)
+        g = torch.Generator(device="cuda").manual_seed(1)
+        need = [(n + BLOCK - 1) // BLOCK for n in lens]
+        nb = sum(need) + 2
+        ids = torch.randperm(nb, generator=g, device="cuda").tolist()
+        seqs, at = [], 0
+        for n, nbk, c in zip(lens, need, cached):
+            seqs.append(md.SeqState(n, ids[at:at + nbk], c))
+            at += nbk
+        m = md.prepare_prefill(seqs, BLOCK)
+        total_q = sum(n - c for n, c in zip(lens, cached))
+        q = torch.empty(total_q, Hq, D, dtype=torch.bfloat16, device="cuda").normal_(generator=g)
+        cu_q, cu_k = m["cu_seqlens_q"].cuda(), m["cu_seqlens_k"].cuda()
+        scale = D ** -0.5
+        if any(cached):
+            kc = torch.empty(nb, BLOCK, Hkv, D, dtype=torch.bfloat16,
+                             device="cuda").normal_(generator=g)
+            vc = torch.empty_like(kc).normal_(generator=g)
+            k, v, bt = kc, vc, m["block_tables"].cuda()
+        else:
+            packed = torch.empty(total_q, (Hq + 2 * Hkv) * D, dtype=torch.bfloat16,
+                                 device="cuda").normal_(generator=g)
+            k = packed[:, Hq * D:(Hq + Hkv) * D].contiguous().view(total_q, Hkv, D)
+            v = packed[:, (Hq + Hkv) * D:].view(total_q, Hkv, D)
+            bt = None
+        o = torch.empty_like(q)
+        fl = prefill_flops(lens, cached, Hq)
+        t_min, t_med = timed(lambda: prefill_varlen(q, k, v, cu_q, cu_k, m["max_seqlen_q"],
+                                                    m["max_seqlen_k"], scale, block_tables=bt,
+                                                    out=o), iters=8)
+        fa = lambda: flash_attn_varlen_func(  # noqa: E731
+            q, k, v, max_seqlen_q=m["max_seqlen_q"], cu_seqlens_q=cu_q,
+            max_seqlen_k=m["max_seqlen_k"], cu_seqlens_k=cu_k, softmax_scale=scale, causal=True,
+            block_table=bt)
+        f_min, f_med = timed(fa, iters=8)
+        err = (o.float() - fa().float()).abs().max().item()
+        rec = dict(kind="prefill", name=name, Hq=Hq, Hkv=Hkv, total_q=total_q, flops=fl,
+                   ours_us=t_med * 1e3, ours_tflops=fl / t_med / 1e9,
+                   ours_frac=fl / t_med / 1e9 / TF_PEAK, fa2_us=f_med * 1e3,
+                   fa2_tflops=fl / f_med / 1e9, speedup=f_med / t_med, max_abs_diff_vs_fa2=err)
+        out.write(json.dumps(rec) + "\n")
+        out.flush()
+        print(f"prefill {name:>14s} {Hq}/{Hkv}: ours {t_med * 1e3:9.1f} us {rec['ours_tflops']:7.1f}"
+              f" TF/s ({rec['ours_frac']:.3f}) | fa2 {f_med * 1e3:9.1f} us {rec['fa2_tflops']:7.1f}"
+              f" TF/s | x{rec['speedup']:.2f} err {err:.4f}", flush=True)
+        del q, k, v, o
+        torch.cuda.empty_cache()
+
+
+def main():
+    args = [a for a in sys.argv[1:] if not a.startswith("--")]
+    quick = "--quick" in sys.argv
+    kinds = args or ["decode", "store", "prefill"]
+    out_dir = ROOT / "gpurun_out"
+    out_dir.mkdir(exist_ok=True)
+    tag = "_".join(kinds)
+    with torch.inference_mode(), open(out_dir / f"microbench_{tag}.jsonl", "w") as out:
+        out.write(json.dumps(dict(kind="env", gpu=torch.cuda.get_device_name(0), hbm_peak=PEAK,
+                                  tf_peak=TF_PEAK, torch=torch.__version__)) + "\n")
+        for k in kinds:
+            {"decode": bench_decode, "store": bench_store, "prefill": bench_prefill}[k](out, quick)
+
+
+if __name__ == "__main__":
+    main()
