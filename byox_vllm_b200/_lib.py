@@ -12,7 +12,7 @@ from pathlib import Path
 
 LIB_PATH = Path(__file__).resolve().parent / "libb200attn.so"
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 DTYPE_BF16 = 0
 
 E_BADARG = -1
@@ -39,7 +39,7 @@ PROTOTYPES = {
                _i32, _i32, _i32, _i32, _i32, _i64, _f32, _i32, _i32, _vp]),
     "b200attn_prefill_varlen": (
         _i32, [_vp, _vp, _i64, _vp, _i64, _vp, _vp, _vp, _i64, _i32, _vp, _vp,
-               _i32, _i32, _i32, _i32, _vp, _i32, _i32, _i32, _i32, _i64, _f32, _i32, _vp]),
+               _i32, _i32, _i32, _i32, _i32, _vp, _i32, _i32, _i32, _i32, _i64, _f32, _i32, _vp]),
     "b200attn_launch_count": (_i64, []),
 }
 

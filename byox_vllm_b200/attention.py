@@ -180,7 +180,7 @@ def prefill_varlen(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, cu_seqlens
         k, v = _kv_rows(k, D), _kv_rows(v, D)
         rc = lib.b200attn_prefill_varlen(
             q.data_ptr(), k.data_ptr(), k.stride(0), v.data_ptr(), v.stride(0), None, None, None,
-            0, 0, cu_seqlens_q.data_ptr(), cu_seqlens_k.data_ptr(), num_seqs, total_q,
+            0, 0, cu_seqlens_q.data_ptr(), cu_seqlens_k.data_ptr(), num_seqs, total_q, k.size(0),
             int(max_seqlen_q), int(max_seqlen_k), out.data_ptr(), Hq, Hkv, D, 0, 0, float(scale),
             _lib.DTYPE_BF16, stream)
     else:
@@ -192,7 +192,7 @@ def prefill_varlen(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, cu_seqlens
         rc = lib.b200attn_prefill_varlen(
             q.data_ptr(), None, 0, None, 0, k.data_ptr(), v.data_ptr(), block_tables.data_ptr(),
             block_tables.stride(0), block_tables.size(1), cu_seqlens_q.data_ptr(),
-            cu_seqlens_k.data_ptr(), num_seqs, total_q, int(max_seqlen_q), int(max_seqlen_k),
+            cu_seqlens_k.data_ptr(), num_seqs, total_q, 0, int(max_seqlen_q), int(max_seqlen_k),
             out.data_ptr(), Hq, Hkv, D, block_size, num_blocks, float(scale), _lib.DTYPE_BF16,
             stream)
     _lib.check("b200attn_prefill_varlen", rc)

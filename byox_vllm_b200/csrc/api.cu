@@ -7,6 +7,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <atomic>
 #include <mutex>
 #include <unordered_map>
@@ -58,54 +59,82 @@ EncodeTiledFn encode_tiled_fn() {
 
 struct MapKey {
     const void* base;
-    int64_t num_slots;
-    int32_t num_kv_heads;
+    int64_t rows;
+    int64_t row_stride;
+    int32_t heads;
+    int32_t box_rows;
     bool operator==(const MapKey& o) const {
-        return base == o.base && num_slots == o.num_slots && num_kv_heads == o.num_kv_heads;
+        return base == o.base && rows == o.rows && row_stride == o.row_stride &&
+               heads == o.heads && box_rows == o.box_rows;
     }
 };
 struct MapKeyHash {
     size_t operator()(const MapKey& k) const {
-        return std::hash<const void*>()(k.base) ^ (std::hash<int64_t>()(k.num_slots) * 1315423911u) ^
-               (static_cast<size_t>(k.num_kv_heads) << 20);
+        size_t h = std::hash<const void*>()(k.base);
+        h ^= std::hash<int64_t>()(k.rows) * 1315423911u;
+        h ^= std::hash<int64_t>()(k.row_stride) * 2654435761u;
+        h ^= (static_cast<size_t>(k.heads) << 20) ^ (static_cast<size_t>(k.box_rows) << 40);
+        return h;
     }
 };
 
-// A paged cache [num_slots, Hkv, 128] bf16 as a 3-D tensor map (dims fastest-first: 128, Hkv,
-// num_slots), box = 64 dims x 1 head x 64 tokens, SWIZZLE_128B. Encoding is pure host work; the
-// 128-byte descriptors are cached per cache view (nanovllm allocates the KV cache once,
-// model_runner.py:137, and every layer view keeps its address for the life of the engine).
-int get_cache_map(const void* base, int32_t num_kv_heads, int64_t num_slots, CUtensorMap* out) {
-    static std::mutex mu;
-    static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
-    const MapKey key{base, num_slots, num_kv_heads};
-    std::lock_guard<std::mutex> lock(mu);
-    auto it = cache.find(key);
-    if (it != cache.end()) {
-        *out = it->second;
-        return 0;
-    }
+// Rows of `heads` x 128 bf16 ([rows, heads, 128], row stride in elements) as a 3-D tensor map
+// (dims fastest-first: 128, heads, rows), box = 64 dims x 1 head x box_rows rows, SWIZZLE_128B,
+// out-of-bounds rows read as zero. Encoding is pure host work (no driver call touches the
+// device), so it is legal during stream capture.
+int encode_rows_map(const void* base, int32_t heads, int64_t rows, int64_t row_stride,
+                    int32_t box_rows, CUtensorMap* out) {
     EncodeTiledFn enc = encode_tiled_fn();
     if (!enc) return fail(B200ATTN_E_DRIVER, "cuTensorMapEncodeTiled not available from the driver");
     const cuuint64_t dims[3] = {static_cast<cuuint64_t>(b200::kHeadDim),
-                                static_cast<cuuint64_t>(num_kv_heads),
-                                static_cast<cuuint64_t>(num_slots)};
+                                static_cast<cuuint64_t>(heads), static_cast<cuuint64_t>(rows)};
     const cuuint64_t strides[2] = {static_cast<cuuint64_t>(b200::kHeadDim) * 2,
-                                   static_cast<cuuint64_t>(num_kv_heads) * b200::kHeadDim * 2};
-    const cuuint32_t box[3] = {64, 1, 64};
+                                   static_cast<cuuint64_t>(row_stride) * 2};
+    const cuuint32_t box[3] = {64, 1, static_cast<cuuint32_t>(box_rows)};
     const cuuint32_t elem_strides[3] = {1, 1, 1};
-    CUtensorMap map;
-    CUresult r = enc(&map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims,
+    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims,
                      strides, box, elem_strides, CU_TENSOR_MAP_INTERLEAVE_NONE,
                      CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS)
         return fail(B200ATTN_E_DRIVER, "cuTensorMapEncodeTiled failed with CUresult %d",
                     static_cast<int>(r));
+    return 0;
+}
+
+// The paged cache [num_slots, Hkv, 128] keeps its address for the life of the engine (nanovllm
+// allocates it once, model_runner.py:137), so its descriptors are cached per (view, box).
+int get_cache_map(const void* base, int32_t num_kv_heads, int64_t num_slots, int32_t box_rows,
+                  CUtensorMap* out) {
+    static std::mutex mu;
+    static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
+    const int64_t row_stride = static_cast<int64_t>(num_kv_heads) * b200::kHeadDim;
+    const MapKey key{base, num_slots, row_stride, num_kv_heads, box_rows};
+    std::lock_guard<std::mutex> lock(mu);
+    auto it = cache.find(key);
+    if (it != cache.end()) {
+        *out = it->second;
+        return 0;
+    }
+    CUtensorMap map;
+    if (int rc = encode_rows_map(base, num_kv_heads, num_slots, row_stride, box_rows, &map))
+        return rc;
     if (cache.size() > 4096) cache.clear();
     cache.emplace(key, map);
     *out = map;
     return 0;
+}
+
+// B200ATTN_PREFILL=tc|mma forces one prefill kernel (tests, microbench); default: by shape.
+int prefill_mode_from_env() {
+    static int mode = [] {
+        const char* e = std::getenv("B200ATTN_PREFILL");
+        if (!e) return 0;
+        if (e[0] == 't') return 1;
+        if (e[0] == 'm') return 2;
+        return 0;
+    }();
+    return mode;
 }
 
 int check_attn_shape(int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim,
@@ -220,8 +249,8 @@ int b200attn_store_decode(const void* q, const void* key, int64_t key_row_stride
             return rc;
     }
     CUtensorMap k_map, v_map;
-    if (int rc = get_cache_map(k_cache, num_kv_heads, num_slots, &k_map)) return rc;
-    if (int rc = get_cache_map(v_cache, num_kv_heads, num_slots, &v_map)) return rc;
+    if (int rc = get_cache_map(k_cache, num_kv_heads, num_slots, 64, &k_map)) return rc;
+    if (int rc = get_cache_map(v_cache, num_kv_heads, num_slots, 64, &v_map)) return rc;
 
     b200::DecodeParams p{};
     p.q = q;
@@ -263,15 +292,16 @@ int b200attn_prefill_varlen(const void* q, const void* key, int64_t key_row_stri
                             const void* v_cache, const int32_t* block_tables,
                             int64_t table_row_stride, int32_t table_width,
                             const int32_t* cu_seqlens_q, const int32_t* cu_seqlens_k,
-                            int32_t num_seqs, int32_t total_q, int32_t max_seqlen_q,
-                            int32_t max_seqlen_k, void* out, int32_t num_q_heads,
+                            int32_t num_seqs, int32_t total_q, int32_t total_k,
+                            int32_t max_seqlen_q, int32_t max_seqlen_k, void* out,
+                            int32_t num_q_heads,
                             int32_t num_kv_heads, int32_t head_dim, int32_t block_size,
                             int64_t num_blocks, float scale, int32_t dtype, void* stream) {
     const bool paged = block_tables != nullptr;
     if (int rc = check_attn_shape(num_q_heads, num_kv_heads, head_dim, paged ? block_size : 64,
                                   dtype))
         return rc;
-    if (num_seqs < 0 || total_q < 0 || max_seqlen_q < 0 || max_seqlen_k < 0)
+    if (num_seqs < 0 || total_q < 0 || total_k < 0 || max_seqlen_q < 0 || max_seqlen_k < 0)
         return fail(B200ATTN_E_BADARG, "negative size");
     if (num_seqs == 0 || total_q == 0 || max_seqlen_q == 0) return 0;
     if (!q || !out || !cu_seqlens_q || !cu_seqlens_k) return fail(B200ATTN_E_BADARG, "null pointer");
@@ -309,6 +339,7 @@ int b200attn_prefill_varlen(const void* q, const void* key, int64_t key_row_stri
     p.cu_seqlens_k = cu_seqlens_k;
     p.num_seqs = num_seqs;
     p.total_q = total_q;
+    p.total_k = total_k;
     p.max_seqlen_q = max_seqlen_q;
     p.max_seqlen_k = max_seqlen_k;
     p.num_q_heads = num_q_heads;
@@ -316,7 +347,39 @@ int b200attn_prefill_varlen(const void* q, const void* key, int64_t key_row_stri
     p.group = num_q_heads / num_kv_heads;
     p.block_size = block_size;
     p.scale_log2 = scale * 1.4426950408889634f;
-    cudaError_t e = b200::launch_prefill(p, static_cast<cudaStream_t>(stream));
+    // Kernel choice from host-visible sizes only. The tcgen05 kernel works on 256-row query
+    // tile pairs and 128-token KV tiles: it needs pages that are multiples of 128 tokens.
+    const int mode = prefill_mode_from_env();
+    const bool tc_ok = scale > 0.f && (!paged || block_size % 128 == 0) &&
+                       static_cast<int64_t>(num_blocks) * block_size < (1LL << 31);
+    bool use_tc = tc_ok && max_seqlen_q >= 256;
+    if (mode == 1) {
+        if (!tc_ok) return fail(B200ATTN_E_UNSUPPORTED, "B200ATTN_PREFILL=tc: shape unsupported");
+        use_tc = true;
+    } else if (mode == 2) {
+        use_tc = false;
+    }
+    cudaError_t e;
+    if (use_tc) {
+        CUtensorMap q_map, k_map, v_map;
+        if (int rc = encode_rows_map(q, num_q_heads, total_q,
+                                     static_cast<int64_t>(num_q_heads) * head_dim, 128, &q_map))
+            return rc;
+        if (paged) {
+            const int64_t num_slots = num_blocks * block_size;
+            if (int rc = get_cache_map(k_cache, num_kv_heads, num_slots, 128, &k_map)) return rc;
+            if (int rc = get_cache_map(v_cache, num_kv_heads, num_slots, 128, &v_map)) return rc;
+        } else {
+            if (int rc = encode_rows_map(key, num_kv_heads, total_k, key_row_stride, 128, &k_map))
+                return rc;
+            if (int rc = encode_rows_map(value, num_kv_heads, total_k, value_row_stride, 128,
+                                         &v_map))
+                return rc;
+        }
+        e = b200::launch_prefill_tc(p, q_map, k_map, v_map, static_cast<cudaStream_t>(stream));
+    } else {
+        e = b200::launch_prefill(p, static_cast<cudaStream_t>(stream));
+    }
     return e == cudaSuccess ? 0 : cuda_fail(e, "prefill launch");
 }
 

@@ -70,6 +70,7 @@ struct PrefillParams {
     const int32_t* cu_seqlens_k;
     int32_t num_seqs;
     int32_t total_q;
+    int32_t total_k;  // rows of key/value (dense source)
     int32_t max_seqlen_q;
     int32_t max_seqlen_k;
     int32_t num_q_heads;
@@ -79,5 +80,11 @@ struct PrefillParams {
     float scale_log2;
 };
 cudaError_t launch_prefill(const PrefillParams& p, cudaStream_t stream);
+
+// ---- prefill_tc.cu (tcgen05 / TMEM / TMA) ----------------------------------------------------
+// q_map / k_map / v_map: 3-D tensor maps (128 dims, heads, rows), box 64 x 1 x 128, SWIZZLE_128B.
+cudaError_t launch_prefill_tc(const PrefillParams& p, const CUtensorMap& q_map,
+                              const CUtensorMap& k_map, const CUtensorMap& v_map,
+                              cudaStream_t stream);
 
 }  // namespace b200

@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 1
+#define B200ATTN_ABI_VERSION 2
 
 #define B200ATTN_DTYPE_BF16 0
 
@@ -123,15 +123,18 @@ int b200attn_store_decode(const void* q, const void* key, int64_t key_row_stride
  *   paged  (block_tables != NULL): K/V rows come from the cache through block_tables as in
  *          b200attn_decode; key/value ignored.
  *   q [total_q, num_q_heads, head_dim] contiguous; out same. Rows with no visible key get zeros.
+ *   total_k = number of rows of key/value (dense; bounds the TMA tensor map), ignored when paged.
+ * Kernel choice depends on host-visible sizes only: sequences of >= 256 query rows run on the
+ * tcgen05/TMEM kernel, shorter batches on the mma.sync kernel (B200ATTN_PREFILL=tc|mma forces one).
  */
 int b200attn_prefill_varlen(const void* q, const void* key, int64_t key_row_stride,
                             const void* value, int64_t value_row_stride, const void* k_cache,
                             const void* v_cache, const int32_t* block_tables,
                             int64_t table_row_stride, int32_t table_width,
                             const int32_t* cu_seqlens_q, const int32_t* cu_seqlens_k,
-                            int32_t num_seqs, int32_t total_q, int32_t max_seqlen_q,
-                            int32_t max_seqlen_k, void* out, int32_t num_q_heads,
-                            int32_t num_kv_heads, int32_t head_dim, int32_t block_size,
+                            int32_t num_seqs, int32_t total_q, int32_t total_k,
+                            int32_t max_seqlen_q, int32_t max_seqlen_k, void* out,
+                            int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim, int32_t block_size,
                             int64_t num_blocks, float scale, int32_t dtype, void* stream);
 
 #ifdef __cplusplus

@@ -58,7 +58,7 @@ def test_argument_errors_have_codes_and_messages(lib):
                              None)
     assert rc == _lib.E_WORKSPACE
     rc = lib.b200attn_prefill_varlen(16, None, 0, None, 0, None, None, None, 0, 0, 16, 16, 1, 8, 8,
-                                     8, 16, 16, 8, 128, 0, 0, 0.1, 0, None)
+                                     8, 8, 16, 16, 8, 128, 0, 0, 0.1, 0, None)
     assert rc == _lib.E_BADARG  # dense prefill without key/value
     with pytest.raises(_lib.B200AttnError) as ei:
         _lib.check("b200attn_decode", lib.b200attn_decode(
