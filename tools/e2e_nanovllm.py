@@ -1,0 +1,214 @@
+"""End-to-end run of the REFERENCE ENGINE (nanovllm, unmodified, from baseline/_ref) with either its
+own attention (Triton store + flash-attn: `--impl ref`) or the B200 drop-in (`--impl ours`,
+byox_vllm_b200.install) — same scheduler, block manager, model runner, CUDA graphs, sampler.
+
+    gpurun -- python tools/e2e_nanovllm.py --impl ours --model 0.6b
+    gpurun -- python tools/e2e_nanovllm.py --impl ref  --model 0.6b
+
+Workload = the reference's bench (bench.py:17-42): seed(0), N prompts of randint(100, max_in) random
+token ids, max_tokens = randint(100, max_out), temperature 0.6, ignore_eos; metric = sum(max_tokens)
+/ wall time of generate() (prefill included). BASELINE.json config 2: 256 seqs, 100-1024 / 100-1024.
+
+No weights and no network exist here, so (identically for both arms):
+  * the model directory is synthetic: config.json with the public Qwen3 dimensions + a WordLevel
+    tokenizer; parameters are seeded random (the reference's load_model finds no *.safetensors);
+  * transformers 5.x hands `rope_scaling` as a dict: get_rope is wrapped to pass None for the
+    default rope type (reference rotary_embedding.py:51-59 asserts None).
+Prints one JSON line; also checks (`--check`) that both arms produce the same greedy-ish tokens on
+a short prompt set.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import tempfile
+import time
+from pathlib import Path
+from random import randint, seed
+
+ROOT = Path(__file__).resolve().parents[1]
+sys.path.insert(0, str(ROOT))
+sys.path.insert(0, str(ROOT / "baseline" / "_ref"))
+os.environ.setdefault("TOKENIZERS_PARALLELISM", "false")
+
+MODELS = {
+    "0.6b": dict(hidden_size=1024, num_hidden_layers=28, num_attention_heads=16,
+                 num_key_value_heads=8, intermediate_size=3072, tie_word_embeddings=True),
+    "8b": dict(hidden_size=4096, num_hidden_layers=36, num_attention_heads=32,
+               num_key_value_heads=8, intermediate_size=12288, tie_word_embeddings=False),
+    "32b": dict(hidden_size=5120, num_hidden_layers=64, num_attention_heads=64,
+                num_key_value_heads=8, intermediate_size=25600, tie_word_embeddings=False),
+}
+
+
+def make_model_dir(name: str) -> str:
+    d = Path(tempfile.gettempdir()) / f"synthetic-qwen3-{name}"
+    d.mkdir(exist_ok=True)
+    cfg = dict(architectures=["Qwen3ForCausalLM"], model_type="qwen3", head_dim=128,
+               hidden_act="silu", vocab_size=151936, max_position_embeddings=40960,
+               rms_norm_eps=1e-6, rope_theta=1000000, attention_bias=False,
+               torch_dtype="bfloat16", dtype="bfloat16", bos_token_id=151643,
+               eos_token_id=151645, **MODELS[name])
+    (d / "config.json").write_text(json.dumps(cfg))
+    if not (d / "tokenizer.json").exists():
+        from tokenizers import Tokenizer, models, pre_tokenizers
+
+        vocab = {f"t{i}": i for i in range(20000)}
+        vocab["<unk>"] = 20000
+        vocab["<eos>"] = 20001
+        tok = Tokenizer(models.WordLevel(vocab=vocab, unk_token="<unk>"))
+        tok.pre_tokenizer = pre_tokenizers.Whitespace()
+        tok.save(str(d / "tokenizer.json"))
+        (d / "tokenizer_config.json").write_text(json.dumps(
+            dict(tokenizer_class="PreTrainedTokenizerFast", eos_token="<eos>",
+                 unk_token="<unk>", model_max_length=40960)))
+    return str(d)
+
+
+def patch_reference(impl: str) -> None:
+    """Harness shims applied identically to both arms, plus the drop-in for `ours`."""
+    if impl == "ours":
+        from byox_vllm_b200 import install
+
+        install.install(verbose=True)
+    import torch
+    import nanovllm.layers.rotary_embedding as rot
+    import nanovllm.models.qwen3 as qwen3
+    import nanovllm.engine.model_runner as mr
+
+    orig_get_rope = rot.get_rope
+
+    def get_rope(head_size, rotary_dim, max_position, base, rope_scaling=None):
+        if isinstance(rope_scaling, dict):
+            assert rope_scaling.get("rope_type", "default") == "default"
+            rope_scaling = None
+        return orig_get_rope(head_size, rotary_dim, max_position, float(base), rope_scaling)
+
+    qwen3.get_rope = get_rope
+
+    def seeded_load_model(model, path):
+        rank = torch.distributed.get_rank() if torch.distributed.is_initialized() else 0
+        g = torch.Generator(device="cuda").manual_seed(1234 + rank)
+        for name, p in model.named_parameters():
+            if name.endswith("norm.weight"):
+                p.data.fill_(1.0)
+            else:
+                p.data.normal_(0.0, 0.02, generator=g)
+
+    mr.load_model = seeded_load_model
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--impl", choices=["ours", "ref"], required=True)
+    ap.add_argument("--model", choices=sorted(MODELS), default="0.6b")
+    ap.add_argument("--num-seqs", type=int, default=256)
+    ap.add_argument("--max-in", type=int, default=1024)
+    ap.add_argument("--max-out", type=int, default=1024)
+    ap.add_argument("--max-model-len", type=int, default=4096)
+    ap.add_argument("--util", type=float, default=0.9)
+    ap.add_argument("--tp", type=int, default=1)
+    ap.add_argument("--eager", action="store_true")
+    ap.add_argument("--check", action="store_true",
+                    help="also dump near-greedy tokens of 8 short prompts for cross-arm comparison")
+    ap.add_argument("--out", default=None)
+    ap.add_argument("--profile", action="store_true",
+                    help="torch.profiler table of a short generate instead of the benchmark")
+    args = ap.parse_args()
+
+    patch_reference(args.impl)
+    import logging
+
+    import torch
+    from nanovllm import LLM, SamplingParams, set_global_log_level
+
+    set_global_log_level(logging.WARNING)
+    path = make_model_dir(args.model)
+    t0 = time.time()
+    llm = LLM(path, enforce_eager=args.eager, max_model_len=args.max_model_len,
+              gpu_memory_utilization=args.util, tensor_parallel_size=args.tp)
+    t_init = time.time() - t0
+
+    # per-phase accounting without touching the engine: wrap LLMEngine._step
+    phase = dict(prefill_s=0.0, decode_s=0.0, prefill_tokens=0, decode_tokens=0, decode_steps=0)
+    orig_step = llm._step
+
+    def timed_step():
+        t = time.perf_counter()
+        out, n = orig_step()
+        dt = time.perf_counter() - t
+        if n > 0:
+            phase["prefill_s"] += dt
+            phase["prefill_tokens"] += n
+        elif n < 0:
+            phase["decode_s"] += dt
+            phase["decode_tokens"] += -n
+            phase["decode_steps"] += 1
+        return out, n
+
+    llm._step = timed_step
+
+    seed(0)
+    prompts = [[randint(0, 10000) for _ in range(randint(100, args.max_in))]
+               for _ in range(args.num_seqs)]
+    sps = [SamplingParams(temperature=0.6, ignore_eos=True, max_tokens=randint(100, args.max_out))
+           for _ in range(args.num_seqs)]
+    llm.generate(["t1 t2 t3"], SamplingParams(), use_tqdm=False)  # warm-up as bench.py:37
+    if args.profile:
+        from torch.profiler import ProfilerActivity, profile
+
+        sp8 = SamplingParams(temperature=0.6, ignore_eos=True, max_tokens=8)
+        llm.generate(prompts[:32], sp8, use_tqdm=False)
+        with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
+            llm.generate(prompts[:32], sp8, use_tqdm=False)
+        print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=25,
+                                        max_name_column_width=70))
+        print(prof.key_averages().table(sort_by="cpu_time_total", row_limit=15,
+                                        max_name_column_width=70))
+        return
+    # Warm pass on DIFFERENT prompts (no prefix-cache hits for the timed run) so torch.compile's
+    # dynamic-shape recompiles of the reference's own @torch.compile regions and every lazy kernel
+    # load happen before the clock starts — identically for both arms.
+    seed(123)
+    wp = [[randint(10001, 19999) for _ in range(randint(100, args.max_in))] for _ in range(48)]
+    llm.generate(wp, SamplingParams(temperature=0.6, ignore_eos=True, max_tokens=16),
+                 use_tqdm=False)
+    for k in phase:
+        phase[k] = 0 if isinstance(phase[k], int) else 0.0
+    torch.cuda.synchronize()
+    t = time.time()
+    llm.generate(prompts, sps, use_tqdm=False)
+    t = time.time() - t
+    total = sum(sp.max_tokens for sp in sps)
+
+    line = {
+        "tool": "e2e_nanovllm", "impl": args.impl, "model": f"Qwen3-{args.model} (random init)",
+        "tp": args.tp, "num_seqs": args.num_seqs, "in": [100, args.max_in],
+        "out": [100, args.max_out], "max_model_len": args.max_model_len,
+        "cuda_graphs": not args.eager, "total_output_tokens": total, "seconds": t,
+        "tokens_per_s": total / t, "init_s": t_init,
+        "decode_tokens_per_s": phase["decode_tokens"] / max(phase["decode_s"], 1e-9),
+        "prefill_tokens_per_s": phase["prefill_tokens"] / max(phase["prefill_s"], 1e-9),
+        "decode_steps": phase["decode_steps"], "decode_s": phase["decode_s"],
+        "prefill_s": phase["prefill_s"],
+    }
+    if args.check:
+        seed(1)
+        cps = [[randint(0, 10000) for _ in range(randint(20, 600))] for _ in range(8)]
+        outs = llm.generate(cps, SamplingParams(temperature=1e-5, max_tokens=24, ignore_eos=True),
+                            use_tqdm=False)
+        line["check_tokens"] = [o["token_ids"] for o in outs]
+    if args.impl == "ours":
+        from byox_vllm_b200 import _lib
+
+        line["libb200attn_launches"] = int(_lib.load().b200attn_launch_count())
+    print(json.dumps(line), flush=True)
+    if args.out:
+        Path(args.out).parent.mkdir(parents=True, exist_ok=True)
+        Path(args.out).write_text(json.dumps(line) + "\n")
+
+
+if __name__ == "__main__":
+    main()
