@@ -190,7 +190,11 @@ def bench_prefill(out, quick):
     from byox_vllm_b200.attention import prefill_varlen
 
     shapes = PREFILL_SHAPES[:3] if quick else PREFILL_SHAPES
+    only = [a.split("=", 1)[1] for a in sys.argv if a.startswith("--only=")]
+    no_ref = "--no-ref" in sys.argv  # ours alone (ncu captures)
     for name, lens, cached, Hq, Hkv in shapes:
+        if only and not any(o in name for o in only):
+            continue
         if lens is None:
             rng = random.Random(0)
             lens = [rng.randint(100, 1024) for _ in range(24)]
@@ -223,13 +227,16 @@ def bench_prefill(out, quick):
         fl = prefill_flops(lens, cached, Hq)
         t_min, t_med = timed(lambda: prefill_varlen(q, k, v, cu_q, cu_k, m["max_seqlen_q"],
                                                     m["max_seqlen_k"], scale, block_tables=bt,
-                                                    out=o), iters=8)
+                                                    out=o), iters=3 if no_ref else 8)
         fa = lambda: flash_attn_varlen_func(  # noqa: E731
             q, k, v, max_seqlen_q=m["max_seqlen_q"], cu_seqlens_q=cu_q,
             max_seqlen_k=m["max_seqlen_k"], cu_seqlens_k=cu_k, softmax_scale=scale, causal=True,
             block_table=bt)
-        f_min, f_med = timed(fa, iters=8)
-        err = (o.float() - fa().float()).abs().max().item()
+        if no_ref:
+            f_med, err = float("nan"), float("nan")
+        else:
+            f_min, f_med = timed(fa, iters=8)
+            err = (o.float() - fa().float()).abs().max().item()
         rec = dict(kind="prefill", name=name, Hq=Hq, Hkv=Hkv, total_q=total_q, flops=fl,
                    ours_us=t_med * 1e3, ours_tflops=fl / t_med / 1e9,
                    ours_frac=fl / t_med / 1e9 / TF_PEAK, fa2_us=f_med * 1e3,
