@@ -2,7 +2,8 @@
 // Replaces flash_attn_varlen_func on the prefill branch of Attention.forward
 // (reference nanovllm/layers/attention.py:72-86), dense and paged-prefix K/V.
 //
-// One CTA = 256 query rows (two 128-row sub-tiles) of one (sequence, q-head); 10 warps:
+// One CTA = 256 query rows (two 128-row sub-tiles) of one (sequence, q-head); 12 warps (the last
+// warpgroup gives most of its registers to the softmax groups with setmaxnreg):
 //   warps 0-3   softmax group 0: one thread per query row of sub-tile 0 (TMEM lane = row)
 //   warps 4-7   softmax group 1: sub-tile 1
 //   warp  8     TMA producer: Q once, then 128-token K and V tiles through two 2-stage rings
@@ -33,10 +34,16 @@ constexpr int kTN = 128;                       // KV tokens per tile
 constexpr int kStages = 2;                     // K ring and V ring depth
 constexpr int kHalfBytes = 128 * 128;          // [128 rows][64 dims] bf16, 128-byte rows, SW128
 constexpr int kTileBytes = 2 * kHalfBytes;     // 32 KiB: dims 0-63 | dims 64-127
-constexpr int kSoftmaxThreads = 256;
 constexpr int kProducerWarp = 8;
 constexpr int kMmaWarp = 9;
-constexpr int kTcThreads = 320;
+constexpr int kTcThreads = 384;                // 3 warpgroups: softmax 0, softmax 1, {TMA, MMA, 2 idle}
+// setmaxnreg budgets. The pool is what the CTA got at launch (168 regs x 384 threads), not the
+// whole register file: an inc that does not fit waits forever.
+constexpr int kRegsLaunch = 168;
+constexpr int kRegsSoftmax = 224;
+constexpr int kRegsControl = 48;
+static_assert(256 * kRegsSoftmax + 128 * kRegsControl <= kTcThreads * kRegsLaunch,
+              "setmaxnreg budgets exceed the registers the CTA owns");
 constexpr uint32_t kTmemCols = 512;
 constexpr float kRescaleThreshold = 8.0f;      // log2 domain
 
@@ -118,8 +125,10 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
     tc::fence_after_sync();
     const uint32_t tmem = bar->tmem_base;
 
+    // setmaxnreg sits inside each role branch so ptxas budgets every role separately.
     if (warp == kProducerWarp) {
         // ============================ TMA producer ============================
+        tc::reg_dec<kRegsControl>();
         if (lane == 0 && n_max > 0) {
             tma_prefetch_desc(&q_map);
             tma_prefetch_desc(&k_map);
@@ -159,6 +168,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
         }
     } else if (warp == kMmaWarp) {
         // ============================ MMA issuer ============================
+        tc::reg_dec<kRegsControl>();
         constexpr uint32_t idesc_s = tc::idesc_bf16_f32(kTM, kTN, false);
         constexpr uint32_t idesc_o = tc::idesc_bf16_f32(kTM, kHeadDim, true);
         const uint32_t q_addr = smem_u32(smem + kSmemQ);
@@ -240,8 +250,9 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
             }
             __syncwarp();
         }
-    } else {
+    } else if (warp < kProducerWarp) {
         // ============================ softmax / correction / epilogue ============================
+        tc::reg_inc<kRegsSoftmax>();
         const int i = warp >> 2;                       // sub-tile
         const int r = (warp & 3) * 32 + lane;          // row inside the sub-tile = TMEM lane
         const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
@@ -257,24 +268,24 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
             wait_bar(&bar->s_full[i], j & 1u);
             tc::fence_after_sync();
             uint32_t sr[128];
-#pragma unroll
-            for (int q4 = 0; q4 < 4; ++q4) tc::tmem_ld32(s_tmem + q4 * 32, sr + q4 * 32);
+            tc::tmem_ld128(s_tmem, sr);
 
             const int key0 = j * kTN;
             const int lim = min(row + offset, Lk - 1) - key0;  // columns <= lim are visible
-            float mx = -INFINITY;
             if (lim < kTN - 1) {
 #pragma unroll
-                for (int t = 0; t < 128; ++t) {
-                    float v = __uint_as_float(sr[t]);
-                    v = t <= lim ? v : -INFINITY;
-                    sr[t] = __float_as_uint(v);
-                    mx = fmaxf(mx, v);
-                }
-            } else {
-#pragma unroll
-                for (int t = 0; t < 128; ++t) mx = fmaxf(mx, __uint_as_float(sr[t]));
+                for (int t = 0; t < 128; ++t)
+                    sr[t] = t <= lim ? sr[t] : 0xff800000u;  // -inf
             }
+            float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+            for (int t = 0; t < 128; t += 8) {
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    mx4[u] = tc::fmax3(mx4[u], __uint_as_float(sr[t + 2 * u]),
+                                       __uint_as_float(sr[t + 2 * u + 1]));
+            }
+            const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
             const float m_new = fmaxf(m_ref, mx * c);
             if (j == 0) {
                 m_ref = m_new;
@@ -298,16 +309,25 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
                 }
             }
             const float mu = m_ref == -INFINITY ? 0.f : m_ref;
-            uint32_t pr[64];
+            // p = exp2(s*c - mu): packed f32x2 FMA / ADD halve the issue slots next to MUFU.ex2
+            const float2 c2 = make_float2(c, c), nmu2 = make_float2(-mu, -mu);
+            float2 ls[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
 #pragma unroll
-            for (int t = 0; t < 64; ++t) {
-                const float e0 = fast_exp2(fmaf(__uint_as_float(sr[2 * t]), c, -mu));
-                const float e1 = fast_exp2(fmaf(__uint_as_float(sr[2 * t + 1]), c, -mu));
-                l += e0 + e1;
-                pr[t] = pack_bf16x2(e0, e1);
+            for (int hh = 0; hh < 2; ++hh) {  // 32 packed columns at a time: P regs die early
+                uint32_t pr[32];
+#pragma unroll
+                for (int t = 0; t < 32; ++t) {
+                    const int e = hh * 64 + 2 * t;
+                    float2 x = make_float2(__uint_as_float(sr[e]), __uint_as_float(sr[e + 1]));
+                    x = __ffma2_rn(x, c2, nmu2);
+                    x.x = fast_exp2(x.x);
+                    x.y = fast_exp2(x.y);
+                    ls[t & 1] = __fadd2_rn(ls[t & 1], x);
+                    pr[t] = pack_bf16x2(x.x, x.y);
+                }
+                tc::tmem_st32(s_tmem + hh * 32, pr);
             }
-            tc::tmem_st32(s_tmem, pr);
-            tc::tmem_st32(s_tmem + 32, pr + 32);
+            l += (ls[0].x + ls[0].y) + (ls[1].x + ls[1].y);
             tc::wait_st();
             tc::fence_before_sync();
             mbar_arrive(&bar->p_full[i]);
@@ -346,6 +366,10 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
 #pragma unroll
             for (int v = 0; v < 16; ++v) st_v4(orow_g + v * 16, make_int4(0, 0, 0, 0));
         }
+    }
+
+    else {
+        tc::reg_dec<kRegsControl>();  // idle warps of the control warpgroup
     }
 
     tc::fence_before_sync();
