@@ -352,6 +352,8 @@ def cpu_reference(w, steps, warmup, sample_seqs=None, budget_s=20.0):
 def run_reference(args, w, rank, world):
     if rank != 0:
         return None
+    # torchrun exports OMP_NUM_THREADS=1; the reference arm uses every host thread it can.
+    torch.set_num_threads(len(os.sched_getaffinity(0)))
     tok_s, t, n, done = cpu_reference(w, args.steps, max(args.warmup, 1), budget_s=120.0)
     cores = torch.get_num_threads()
     sample = (f"1 of {w['layers']} layers x {n} of {w['batch']} sequences (store + paged decode, "
@@ -399,7 +401,10 @@ def main():
     try:
         with torch.inference_mode():
             line = run_ours(args, w, rank, world, dev)
-        if rank == 0:
+        if rank == 0 and world > 1:
+            line["cpu_baseline"] = None  # timed at N=1 only
+            print(json.dumps(line), flush=True)
+        elif rank == 0:
             tok_s, t, n, done = cpu_reference(w, 5, 1, sample_seqs=64, budget_s=20.0)
             line["cpu_baseline"] = {
                 "value": tok_s, "unit": "tokens/s", "cores": torch.get_num_threads(),
