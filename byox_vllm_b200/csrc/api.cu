@@ -242,11 +242,27 @@ int b200attn_store_decode(const void* q, const void* key, int64_t key_row_stride
                         workspace_bytes, need, num_splits);
     }
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    if (key || value || slot_mapping) {
-        if (int rc = b200attn_store_kvcache(key, key_row_stride, value, value_row_stride, k_cache,
-                                            v_cache, slot_mapping, batch,
-                                            num_kv_heads * head_dim, num_slots, dtype, stream))
-            return rc;
+    const bool with_store = key || value || slot_mapping;
+    // One launch: the decode kernel scatters the new rows itself (B200ATTN_FUSED_STORE=0 keeps the
+    // two-launch sequence for A/B runs).
+    static const bool fused_store = [] {
+        const char* e = std::getenv("B200ATTN_FUSED_STORE");
+        return !(e && e[0] == '0');
+    }();
+    if (with_store) {
+        if (!key || !value || !slot_mapping)
+            return fail(B200ATTN_E_BADARG, "store_decode needs key, value and slot_mapping");
+        if (key_row_stride % 8 != 0 || value_row_stride % 8 != 0 || !aligned16(key) ||
+            !aligned16(value))
+            return fail(B200ATTN_E_UNSUPPORTED, "key/value rows must be 16-byte aligned");
+        if (key_row_stride < num_kv_heads * head_dim || value_row_stride < num_kv_heads * head_dim)
+            return fail(B200ATTN_E_BADARG, "row stride smaller than the row");
+        if (!fused_store) {
+            if (int rc = b200attn_store_kvcache(key, key_row_stride, value, value_row_stride,
+                                                k_cache, v_cache, slot_mapping, batch,
+                                                num_kv_heads * head_dim, num_slots, dtype, stream))
+                return rc;
+        }
     }
     CUtensorMap k_map, v_map;
     if (int rc = get_cache_map(k_cache, num_kv_heads, num_slots, 64, &k_map)) return rc;
@@ -266,6 +282,16 @@ int b200attn_store_decode(const void* q, const void* key, int64_t key_row_stride
     p.block_size = block_size;
     p.num_splits = num_splits;
     p.scale_log2 = scale * 1.4426950408889634f;
+    if (with_store && fused_store) {
+        p.new_key = key;
+        p.new_value = value;
+        p.slot_mapping = slot_mapping;
+        p.k_cache = k_cache;
+        p.v_cache = v_cache;
+        p.key_row_stride = key_row_stride;
+        p.value_row_stride = value_row_stride;
+        p.num_slots = num_slots;
+    }
     if (num_splits > 1) {
         p.ws_o = static_cast<float*>(workspace);
         p.ws_lse = p.ws_o + static_cast<size_t>(batch) * num_q_heads * num_splits * b200::kHeadDim;

@@ -101,6 +101,26 @@ decode_split_kernel(const __grid_constant__ CUtensorMap k_map,
         int page_base = t_begin / tiles_per_page;
         int my_block = (page_base + lane <= last_page) ? table[page_base + lane] : 0;
         const uint64_t policy = l2_policy_evict_first();
+        // Fused scatter (reference attention.py:70-71): the CTA whose split ends at the newest
+        // token writes this step's K/V row of its KV head into the cache slot, then orders the
+        // generic-proxy stores before its own TMA reads of that slot (fence.proxy.async). Other
+        // CTAs never read the slot: it is token ctx-1 of sequence b, private to this split.
+        if (p.new_key != nullptr && t_end == tiles_total) {
+            const int64_t slot = p.slot_mapping[b];
+            if (slot >= 0 && slot < p.num_slots) {
+                const bool is_v = lane >= 16;
+                const int c = lane & 15;  // 16-byte chunk of the 256-byte head row
+                const uint8_t* src =
+                    static_cast<const uint8_t*>(is_v ? p.new_value : p.new_key) +
+                    static_cast<int64_t>(b) * (is_v ? p.value_row_stride : p.key_row_stride) * 2 +
+                    kvh * 256 + c * 16;
+                uint8_t* dst = static_cast<uint8_t*>(is_v ? p.v_cache : p.k_cache) +
+                               (slot * p.num_kv_heads + kvh) * 256 + c * 16;
+                st_v4(dst, ld_nc_v4(src));
+                asm volatile("fence.proxy.async.global;" ::: "memory");
+            }
+            __syncwarp();
+        }
         for (int t = t_begin, it = 0; t < t_end; ++t, ++it) {
             const int stage = it % kStages;
             const uint32_t phase = (it / kStages) & 1u;

@@ -101,9 +101,14 @@ int b200attn_decode(const void* q, const void* k_cache, const void* v_cache,
                     int32_t dtype, void* stream);
 
 /*
- * Fused decode step of one layer: scatter this step's K/V rows (as b200attn_store_kvcache with
- * n_tokens == batch) and then run b200attn_decode, ordered on `stream`. Same results as the two
- * calls in sequence.
+ * Fused decode step of one layer in ONE launch: scatter this step's K/V rows (as
+ * b200attn_store_kvcache with n_tokens == batch) and run b200attn_decode over the updated cache.
+ * Same results as the two calls in sequence under the precondition the reference's decode step
+ * guarantees (engine/model_runner.py:211-215): slot_mapping[b] is negative (row skipped) or the
+ * cache slot of token context_lens[b] - 1 of row b, i.e.
+ *     block_tables[b][(ctx_b-1)/block_size] * block_size + (ctx_b-1) % block_size.
+ * The CTA that attends that token writes it first (generic stores, fence.proxy.async, then its
+ * own TMA reads), so no other work item ever reads a slot being written.
  */
 int b200attn_store_decode(const void* q, const void* key, int64_t key_row_stride, const void* value,
                           int64_t value_row_stride, const int32_t* slot_mapping, void* k_cache,
