@@ -398,16 +398,18 @@ size_t decode_workspace_bytes(int32_t batch, int32_t num_q_heads, int32_t num_sp
 
 int decode_pick_splits(int32_t batch, int32_t num_kv_heads, int32_t table_width, int32_t block_size,
                        int32_t sm_count) {
-    // Host-visible sizes only. Aim for >= 2 waves of CTAs at 2 CTAs/SM, but never cut a sequence
-    // into pieces shorter than 4 tiles (256 tokens) of the longest possible context.
+    // Host-visible sizes only (graph-capture rule). Calibrated with tools/sweep_splits.py on B200
+    // (profiles/r01_sweep_splits.log): one streaming CTA per SM already saturates HBM, so splitting
+    // only pays while (sequence, KV head) items are fewer than ~0.7 x SMs; then aim for about one
+    // CTA per SM and never cut the longest possible context into pieces shorter than 8 tiles
+    // (512 tokens) - below that the split partials + merge cost more than they hide.
     const int64_t base = static_cast<int64_t>(batch) * num_kv_heads;
-    const int64_t want = 4LL * sm_count;
-    if (base <= 0 || base >= want) return 1;
+    if (base <= 0 || base * 10 >= static_cast<int64_t>(sm_count) * 7) return 1;
     const int64_t max_tiles = static_cast<int64_t>(table_width) * block_size / kTile;
-    int64_t s = (want + base - 1) / base;
-    const int64_t cap = max_tiles / 4 > 1 ? max_tiles / 4 : 1;
+    int64_t s = (sm_count + base / 2) / base;  // round(sm_count / base)
+    const int64_t cap = max_tiles / 8 > 1 ? max_tiles / 8 : 1;
     if (s > cap) s = cap;
-    if (s > 128) s = 128;
+    if (s > 64) s = 64;
     return static_cast<int>(s < 1 ? 1 : s);
 }
 

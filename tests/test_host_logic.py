@@ -29,6 +29,14 @@ def test_pick_splits_is_host_only_and_sane(lib):
             s = lib.b200attn_decode_pick_splits(b, 1, w, 256, sm)
             assert 1 <= s <= max(1, w)
     assert lib.b200attn_decode_pick_splits(4, 8, 16, 256, 0) >= 1  # unknown SM count -> 148
+    # calibration points of tools/sweep_splits.py (profiles/r01_sweep_splits.log): about one CTA
+    # per SM, no split once (sequence, KV head) items reach ~0.7 x SMs, pieces >= 512 tokens
+    assert lib.b200attn_decode_pick_splits(16, 8, 16, 256, sm) == 1
+    assert lib.b200attn_decode_pick_splits(128, 1, 16, 256, sm) == 1
+    assert lib.b200attn_decode_pick_splits(8, 8, 64, 256, sm) == 2
+    assert lib.b200attn_decode_pick_splits(4, 8, 16, 256, sm) == 5
+    assert lib.b200attn_decode_pick_splits(1, 8, 16, 256, sm) == 8
+    assert lib.b200attn_decode_pick_splits(1, 8, 512, 256, sm) in (18, 19)
 
 
 def test_workspace_bytes(lib):

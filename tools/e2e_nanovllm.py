@@ -100,6 +100,12 @@ def patch_reference(impl: str) -> None:
     mr.load_model = seeded_load_model
 
 
+# Tensor-parallel ranks are spawned (llm_engine.py:24-31) and re-import this file as __mp_main__
+# without running main(): they pick the arm up from the environment and patch at import time.
+if __name__ != "__main__" and os.environ.get("E2E_NANOVLLM_IMPL"):
+    patch_reference(os.environ["E2E_NANOVLLM_IMPL"])
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--impl", choices=["ours", "ref"], required=True)
@@ -107,7 +113,10 @@ def main():
     ap.add_argument("--num-seqs", type=int, default=256)
     ap.add_argument("--max-in", type=int, default=1024)
     ap.add_argument("--max-out", type=int, default=1024)
+    ap.add_argument("--fixed-in", type=int, default=0, help="every prompt has exactly this length")
+    ap.add_argument("--fixed-out", type=int, default=0, help="every request decodes this many")
     ap.add_argument("--max-model-len", type=int, default=4096)
+    ap.add_argument("--max-batched", type=int, default=16384)
     ap.add_argument("--util", type=float, default=0.9)
     ap.add_argument("--tp", type=int, default=1)
     ap.add_argument("--eager", action="store_true")
@@ -118,6 +127,7 @@ def main():
                     help="torch.profiler table of a short generate instead of the benchmark")
     args = ap.parse_args()
 
+    os.environ["E2E_NANOVLLM_IMPL"] = args.impl
     patch_reference(args.impl)
     import logging
 
@@ -128,7 +138,8 @@ def main():
     path = make_model_dir(args.model)
     t0 = time.time()
     llm = LLM(path, enforce_eager=args.eager, max_model_len=args.max_model_len,
-              gpu_memory_utilization=args.util, tensor_parallel_size=args.tp)
+              gpu_memory_utilization=args.util, tensor_parallel_size=args.tp,
+              max_num_batched_tokens=args.max_batched)
     t_init = time.time() - t0
 
     # per-phase accounting without touching the engine: wrap LLMEngine._step
@@ -151,9 +162,10 @@ def main():
     llm._step = timed_step
 
     seed(0)
-    prompts = [[randint(0, 10000) for _ in range(randint(100, args.max_in))]
+    prompts = [[randint(0, 10000) for _ in range(args.fixed_in or randint(100, args.max_in))]
                for _ in range(args.num_seqs)]
-    sps = [SamplingParams(temperature=0.6, ignore_eos=True, max_tokens=randint(100, args.max_out))
+    sps = [SamplingParams(temperature=0.6, ignore_eos=True,
+                          max_tokens=args.fixed_out or randint(100, args.max_out))
            for _ in range(args.num_seqs)]
     llm.generate(["t1 t2 t3"], SamplingParams(), use_tqdm=False)  # warm-up as bench.py:37
     if args.profile:
@@ -172,7 +184,8 @@ def main():
     # dynamic-shape recompiles of the reference's own @torch.compile regions and every lazy kernel
     # load happen before the clock starts — identically for both arms.
     seed(123)
-    wp = [[randint(10001, 19999) for _ in range(randint(100, args.max_in))] for _ in range(48)]
+    wp = [[randint(10001, 19999) for _ in range(args.fixed_in or randint(100, args.max_in))]
+          for _ in range(8 if args.fixed_in else 48)]
     llm.generate(wp, SamplingParams(temperature=0.6, ignore_eos=True, max_tokens=16),
                  use_tqdm=False)
     for k in phase:
@@ -185,8 +198,8 @@ def main():
 
     line = {
         "tool": "e2e_nanovllm", "impl": args.impl, "model": f"Qwen3-{args.model} (random init)",
-        "tp": args.tp, "num_seqs": args.num_seqs, "in": [100, args.max_in],
-        "out": [100, args.max_out], "max_model_len": args.max_model_len,
+        "tp": args.tp, "num_seqs": args.num_seqs, "in": args.fixed_in or [100, args.max_in],
+        "out": args.fixed_out or [100, args.max_out], "max_model_len": args.max_model_len,
         "cuda_graphs": not args.eager, "total_output_tokens": total, "seconds": t,
         "tokens_per_s": total / t, "init_s": t_init,
         "decode_tokens_per_s": phase["decode_tokens"] / max(phase["decode_s"], 1e-9),
