@@ -99,6 +99,46 @@ def patch_reference(impl: str) -> None:
 
     mr.load_model = seeded_load_model
 
+    # TP control plane: the reference pickles whole Sequences (all token ids) into
+    # a 1 MiB shared-memory block every step, which overflows at the BASELINE batch sizes. Both
+    # arms get the same two harness fixes: a larger block, and decode steps ship token-free copies
+    # (the workers' _prepare_decode reads only last_token / num_tokens / block_table).
+    import copy
+    from multiprocessing.shared_memory import SharedMemory as _SharedMemory
+
+    class BigSharedMemory(_SharedMemory):
+        def __init__(self, name=None, create=False, size=0):
+            super().__init__(name=name, create=create, size=(1 << 27) if create else 0)
+
+    mr.SharedMemory = BigSharedMemory
+    orig_write = mr.ModelRunner._write_shm
+
+    def write_shm(self, method_name, *args):
+        if method_name == "run" and len(args) == 2 and args[1] is False:
+            light = []
+            for seq in args[0]:
+                c = copy.copy(seq)
+                c.token_ids = []
+                light.append(c)
+            args = (light, False)
+        return orig_write(self, method_name, *args)
+
+    mr.ModelRunner._write_shm = write_shm
+
+    # The reference's ModelRunner.run evaluates `logits.shape` inside a debug f-string
+    # (model_runner.py:63); logits is None on ranks > 0, so every TP > 1 run of the unmodified
+    # reference dies on its first step. Same body without the two debug lines, for both arms.
+    def run(self, seqs, is_prefill):
+        input_ids, positions = (self._prepare_prefill(seqs) if is_prefill
+                                else self._prepare_decode(seqs))
+        temperatures = self._prepare_sample(seqs) if self.rank == 0 else None
+        logits = self._run_model(input_ids, positions, is_prefill)
+        token_ids = self.sampler(logits, temperatures).tolist() if self.rank == 0 else None
+        mr.reset_context()
+        return token_ids
+
+    mr.ModelRunner.run = run
+
 
 # Tensor-parallel ranks are spawned (llm_engine.py:24-31) and re-import this file as __mp_main__
 # without running main(): they pick the arm up from the environment and patch at import time.
