@@ -12,7 +12,7 @@ from pathlib import Path
 
 LIB_PATH = Path(__file__).resolve().parent / "libb200attn.so"
 
-ABI_VERSION = 2
+ABI_VERSION = 3
 DTYPE_BF16 = 0
 
 E_BADARG = -1
@@ -37,6 +37,11 @@ PROTOTYPES = {
     "b200attn_store_decode": (
         _i32, [_vp, _vp, _i64, _vp, _i64, _vp, _vp, _vp, _vp, _i64, _i32, _vp, _vp, _vp, _sz,
                _i32, _i32, _i32, _i32, _i32, _i64, _f32, _i32, _i32, _vp]),
+    "b200attn_cascade_pick_chunks": (_i32, [_i32, _i32, _i32, _i32, _i32, _i32]),
+    "b200attn_cascade_plan": (_i32, [_vp, _i64, _i32, _vp, _i32, _i32, _vp, _vp]),
+    "b200attn_store_decode_cascade": (
+        _i32, [_vp, _vp, _i64, _vp, _i64, _vp, _vp, _vp, _vp, _i64, _i32, _vp, _vp, _vp, _sz,
+               _i32, _i32, _i32, _i32, _i32, _i64, _f32, _i32, _vp, _i32, _i32, _vp]),
     "b200attn_prefill_varlen": (
         _i32, [_vp, _vp, _i64, _vp, _i64, _vp, _vp, _vp, _i64, _i32, _vp, _vp,
                _i32, _i32, _i32, _i32, _i32, _vp, _i32, _i32, _i32, _i32, _i64, _f32, _i32, _vp]),

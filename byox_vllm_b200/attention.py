@@ -80,16 +80,46 @@ def decode_num_splits(batch: int, num_kv_heads: int, table_width: int, block_siz
                                            lib.b200attn_sm_count())
 
 
+def cascade_chunks(batch: int, num_q_heads: int, num_kv_heads: int, table_width: int,
+                   block_size: int) -> int:
+    """Host-only: split-KV chunks of the shared-prefix pass, 0 = cascade not armed for this shape
+    (B200ATTN_CASCADE=0|1 forces it off / on)."""
+    lib = _lib.load()
+    return lib.b200attn_cascade_pick_chunks(batch, num_q_heads, num_kv_heads, table_width,
+                                            block_size, lib.b200attn_sm_count())
+
+
+def cascade_plan(context_lens: torch.Tensor, block_tables: torch.Tensor,
+                 block_size: int) -> torch.Tensor:
+    """Device int32[4] {shared pages P, first active row, active rows, 0} for this step's metadata
+    (one tiny launch; depends only on block_tables / context_lens, so all layers share it)."""
+    _require_cuda(context_lens, block_tables)
+    assert context_lens.dtype == torch.int32 and context_lens.is_contiguous()
+    assert block_tables.dtype == torch.int32 and block_tables.dim() == 2
+    assert block_tables.stride(1) == 1 and block_tables.size(0) == context_lens.numel()
+    plan = torch.empty(4, dtype=torch.int32, device=block_tables.device)
+    lib = _lib.load()
+    rc = lib.b200attn_cascade_plan(
+        block_tables.data_ptr(), block_tables.stride(0), block_tables.size(1),
+        context_lens.data_ptr(), context_lens.numel(), block_size, plan.data_ptr(),
+        _stream(block_tables.device))
+    _lib.check("b200attn_cascade_plan", rc)
+    return plan
+
+
 def paged_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
                  context_lens: torch.Tensor, block_tables: torch.Tensor, scale: float,
                  *, key: torch.Tensor | None = None, value: torch.Tensor | None = None,
                  slot_mapping: torch.Tensor | None = None, num_splits: int | None = None,
-                 out: torch.Tensor | None = None) -> torch.Tensor:
+                 out: torch.Tensor | None = None, plan: torch.Tensor | None = None,
+                 prefix_chunks: int = 0) -> torch.Tensor:
     """Paged single-query attention (the decode branch, reference attention.py:87-96).
 
     q [B, Hq, D]; caches [num_blocks, block_size, Hkv, D]; context_lens [B] int32 (includes the
     current token); block_tables [B, W] int32. If key/value/slot_mapping are given, this step's
     K/V rows are scattered into the cache first (same stream), as Attention.forward does.
+    `plan` (from cascade_plan) + `prefix_chunks` (from cascade_chunks, > 0) arm the shared-prefix
+    cascade: same result, shared leading pages attended once per KV head on the tensor cores.
     Returns [B, Hq, D].
     """
     _require_cuda(q, k_cache, v_cache, context_lens, block_tables, key, value, slot_mapping)
@@ -116,9 +146,13 @@ def paged_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
     if num_splits is None:
         num_splits = decode_num_splits(B, Hkv, W, block_size)
     lib = _lib.load()
+    if plan is None or prefix_chunks <= 0:
+        plan, prefix_chunks = None, 0
+    else:
+        assert plan.dtype == torch.int32 and plan.numel() >= 4 and plan.is_cuda
     ws, ws_bytes = None, 0
-    if num_splits > 1:
-        ws_bytes = lib.b200attn_decode_workspace_bytes(B, Hq, D, num_splits)
+    if num_splits + prefix_chunks > 1:
+        ws_bytes = lib.b200attn_decode_workspace_bytes(B, Hq, D, num_splits + prefix_chunks)
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=q.device)
     stream = _stream(q.device)
     if key is not None:
@@ -128,6 +162,16 @@ def paged_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
         assert key.stride(1) == D and value.stride(1) == D
         assert slot_mapping.dtype == torch.int32 and slot_mapping.numel() == B
         assert slot_mapping.is_contiguous()
+    if plan is not None:
+        rc = lib.b200attn_store_decode_cascade(
+            q.data_ptr(), _ptr(key), 0 if key is None else key.stride(0), _ptr(value),
+            0 if key is None else value.stride(0), None if key is None else _ptr(slot_mapping),
+            k_cache.data_ptr(), v_cache.data_ptr(), block_tables.data_ptr(),
+            block_tables.stride(0), W, context_lens.data_ptr(), out.data_ptr(), _ptr(ws),
+            ws_bytes, B, Hq, Hkv, D, block_size, num_blocks, float(scale), num_splits,
+            plan.data_ptr(), prefix_chunks, _lib.DTYPE_BF16, stream)
+        _lib.check("b200attn_store_decode_cascade", rc)
+    elif key is not None:
         rc = lib.b200attn_store_decode(
             q.data_ptr(), key.data_ptr(), key.stride(0), value.data_ptr(), value.stride(0),
             slot_mapping.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(),
@@ -230,8 +274,37 @@ class Attention(nn.Module):
                                   context.max_seqlen_q, context.max_seqlen_k, self.scale,
                                   block_tables=context.block_tables)
         # decode: one fused library call = scatter of this step's rows + paged attention
+        plan, chunks = _step_plan(context, q.size(0), self.num_heads, self.num_kv_heads, k_cache)
         o = paged_decode(q, k_cache, v_cache, context.context_lens, context.block_tables,
                          self.scale, key=k if have_cache else None,
                          value=v if have_cache else None,
-                         slot_mapping=context.slot_mapping if have_cache else None)
+                         slot_mapping=context.slot_mapping if have_cache else None,
+                         plan=plan, prefix_chunks=chunks)
         return o.unsqueeze(1)  # [B, 1, Hq, D] as flash_attn_with_kvcache returns
+
+
+def _step_plan(context, batch: int, num_heads: int, num_kv_heads: int, k_cache: torch.Tensor):
+    """(plan, prefix_chunks) of the shared-prefix cascade for this decode step, or (None, 0).
+
+    The plan depends only on this step's metadata, and the reference builds a fresh Context per
+    step and per captured graph (utils/context.py:23-45, model_runner.py:225,275-280), so the first
+    layer computes it and parks it on the Context object; the other layers (and, under capture, the
+    other layers of the same graph) reuse it: one plan launch per step, not per layer."""
+    bt = context.block_tables
+    if bt is None or k_cache.dim() != 4:
+        return None, 0
+    block_size = k_cache.size(1)
+    chunks = cascade_chunks(batch, num_heads, num_kv_heads, bt.size(1), block_size)
+    if chunks <= 0:
+        return None, 0
+    # ModelRunner warms a graph batch size up and then captures it under the SAME Context
+    # (model_runner.py:281-284): a plan launched eagerly must not be reused inside the capture,
+    # or the graph would replay without its plan kernel.
+    key = (bt.data_ptr(), context.context_lens.data_ptr(), batch,
+           torch.cuda.is_current_stream_capturing())
+    cached = getattr(context, "_b200_cascade_plan", None)
+    if cached is not None and cached[0] == key:
+        return cached[1], chunks
+    plan = cascade_plan(context.context_lens, bt, block_size)
+    context._b200_cascade_plan = (key, plan)
+    return plan, chunks

@@ -18,8 +18,9 @@ CSRC = PKG_DIR / "csrc"
 BUILD_DIR = PKG_DIR / "_build"
 LIB_PATH = PKG_DIR / "libb200attn.so"
 
-SOURCES = ["store_kv.cu", "decode_attn.cu", "prefill_attn.cu", "prefill_tc.cu", "api.cu"]
-HEADERS = ["common.h", "ptx.cuh", "../../include/b200attn.h"]
+SOURCES = ["store_kv.cu", "decode_attn.cu", "prefill_attn.cu", "prefill_tc.cu", "cascade.cu",
+           "api.cu"]
+HEADERS = ["common.h", "ptx.cuh", "tcgen05.cuh", "../../include/b200attn.h"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

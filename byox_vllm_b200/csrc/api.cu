@@ -83,14 +83,15 @@ struct MapKeyHash {
 // out-of-bounds rows read as zero. Encoding is pure host work (no driver call touches the
 // device), so it is legal during stream capture.
 int encode_rows_map(const void* base, int32_t heads, int64_t rows, int64_t row_stride,
-                    int32_t box_rows, CUtensorMap* out) {
+                    int32_t box_rows, CUtensorMap* out, int32_t box_heads = 1) {
     EncodeTiledFn enc = encode_tiled_fn();
     if (!enc) return fail(B200ATTN_E_DRIVER, "cuTensorMapEncodeTiled not available from the driver");
     const cuuint64_t dims[3] = {static_cast<cuuint64_t>(b200::kHeadDim),
                                 static_cast<cuuint64_t>(heads), static_cast<cuuint64_t>(rows)};
     const cuuint64_t strides[2] = {static_cast<cuuint64_t>(b200::kHeadDim) * 2,
                                    static_cast<cuuint64_t>(row_stride) * 2};
-    const cuuint32_t box[3] = {64, 1, static_cast<cuuint32_t>(box_rows)};
+    const cuuint32_t box[3] = {64, static_cast<cuuint32_t>(box_heads),
+                               static_cast<cuuint32_t>(box_rows)};
     const cuuint32_t elem_strides[3] = {1, 1, 1};
     CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims,
                      strides, box, elem_strides, CU_TENSOR_MAP_INTERLEAVE_NONE,
@@ -213,6 +214,28 @@ size_t b200attn_decode_workspace_bytes(int32_t batch, int32_t num_q_heads, int32
     return b200::decode_workspace_bytes(batch, num_q_heads, num_splits);
 }
 
+int b200attn_cascade_pick_chunks(int32_t batch, int32_t num_q_heads, int32_t num_kv_heads,
+                                 int32_t table_width, int32_t block_size, int32_t sm_count) {
+    if (sm_count <= 0) sm_count = 148;
+    if (batch <= 0 || num_q_heads <= 0 || num_kv_heads <= 0 || table_width <= 0 || block_size <= 0)
+        return 0;
+    return b200::cascade_pick_chunks(batch, num_q_heads, num_kv_heads, table_width, block_size,
+                                     sm_count);
+}
+
+int b200attn_cascade_plan(const int32_t* block_tables, int64_t table_row_stride,
+                          int32_t table_width, const int32_t* context_lens, int32_t batch,
+                          int32_t block_size, int32_t* plan, void* stream) {
+    if (batch < 0 || table_width < 0 || block_size <= 0)
+        return fail(B200ATTN_E_BADARG, "negative or zero size");
+    if (!plan) return fail(B200ATTN_E_BADARG, "null plan");
+    if (batch > 0 && (!block_tables || !context_lens)) return fail(B200ATTN_E_BADARG, "null pointer");
+    cudaError_t e = b200::launch_cascade_plan(block_tables, table_row_stride, table_width,
+                                              context_lens, batch, block_size, plan,
+                                              static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? 0 : cuda_fail(e, "cascade_plan launch");
+}
+
 int b200attn_store_decode(const void* q, const void* key, int64_t key_row_stride, const void* value,
                           int64_t value_row_stride, const int32_t* slot_mapping, void* k_cache,
                           void* v_cache, const int32_t* block_tables, int64_t table_row_stride,
@@ -221,7 +244,30 @@ int b200attn_store_decode(const void* q, const void* key, int64_t key_row_stride
                           int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim,
                           int32_t block_size, int64_t num_blocks, float scale, int32_t num_splits,
                           int32_t dtype, void* stream) {
+    return b200attn_store_decode_cascade(q, key, key_row_stride, value, value_row_stride,
+                                         slot_mapping, k_cache, v_cache, block_tables,
+                                         table_row_stride, table_width, context_lens, out,
+                                         workspace, workspace_bytes, batch, num_q_heads,
+                                         num_kv_heads, head_dim, block_size, num_blocks, scale,
+                                         num_splits, nullptr, 0, dtype, stream);
+}
+
+int b200attn_store_decode_cascade(const void* q, const void* key, int64_t key_row_stride,
+                                  const void* value, int64_t value_row_stride,
+                                  const int32_t* slot_mapping, void* k_cache, void* v_cache,
+                                  const int32_t* block_tables, int64_t table_row_stride,
+                                  int32_t table_width, const int32_t* context_lens, void* out,
+                                  void* workspace, size_t workspace_bytes, int32_t batch,
+                                  int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim,
+                                  int32_t block_size, int64_t num_blocks, float scale,
+                                  int32_t num_splits, const int32_t* plan, int32_t prefix_chunks,
+                                  int32_t dtype, void* stream) {
     if (int rc = check_attn_shape(num_q_heads, num_kv_heads, head_dim, block_size, dtype)) return rc;
+    if (prefix_chunks < 0 || prefix_chunks > 64 || (prefix_chunks > 0) != (plan != nullptr))
+        return fail(B200ATTN_E_BADARG, "plan and prefix_chunks (0..64) must be given together");
+    if (prefix_chunks > 0 && (block_size % 128 != 0 || 128 % (num_q_heads / num_kv_heads) != 0))
+        return fail(B200ATTN_E_UNSUPPORTED,
+                    "cascade needs block_size %% 128 == 0 and a GQA group dividing 128");
     if (batch < 0 || num_blocks <= 0 || table_width < 0 || num_splits < 1)
         return fail(B200ATTN_E_BADARG, "negative or zero size");
     if (batch == 0) return 0;
@@ -235,11 +281,13 @@ int b200attn_store_decode(const void* q, const void* key, int64_t key_row_stride
                     static_cast<long long>(num_slots));
     if (!aligned16(q) || !aligned16(out) || !aligned16(k_cache) || !aligned16(v_cache))
         return fail(B200ATTN_E_BADARG, "pointers must be 16-byte aligned");
-    if (num_splits > 1) {
-        const size_t need = b200::decode_workspace_bytes(batch, num_q_heads, num_splits);
+    const int32_t ws_slots = num_splits + prefix_chunks;
+    if (ws_slots > 1) {
+        const size_t need = b200::decode_workspace_bytes(batch, num_q_heads, ws_slots);
         if (!workspace || workspace_bytes < need || !aligned16(workspace))
-            return fail(B200ATTN_E_WORKSPACE, "workspace %zu B < %zu B needed for %d splits",
-                        workspace_bytes, need, num_splits);
+            return fail(B200ATTN_E_WORKSPACE,
+                        "workspace %zu B < %zu B needed for %d splits + %d prefix chunks",
+                        workspace_bytes, need, num_splits, prefix_chunks);
     }
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const bool with_store = key || value || slot_mapping;
@@ -292,9 +340,45 @@ int b200attn_store_decode(const void* q, const void* key, int64_t key_row_stride
         p.value_row_stride = value_row_stride;
         p.num_slots = num_slots;
     }
-    if (num_splits > 1) {
+    if (ws_slots > 1) {
         p.ws_o = static_cast<float*>(workspace);
-        p.ws_lse = p.ws_o + static_cast<size_t>(batch) * num_q_heads * num_splits * b200::kHeadDim;
+        p.ws_lse = p.ws_o + static_cast<size_t>(batch) * num_q_heads * ws_slots * b200::kHeadDim;
+    }
+    p.plan = plan;
+    p.prefix_chunks = prefix_chunks;
+    if (prefix_chunks > 0) {
+        // Shared-prefix pass first (tcgen05): B*G query rows of every KV head against the P
+        // shared pages, partials into workspace slots [num_splits, num_splits + prefix_chunks).
+        // It never touches the slot the fused scatter writes (that token lies after the prefix).
+        const int group = num_q_heads / num_kv_heads;
+        CUtensorMap q_map, k_map128, v_map128;
+        if (int rc = encode_rows_map(q, num_q_heads, batch,
+                                     static_cast<int64_t>(num_q_heads) * head_dim, 128 / group,
+                                     &q_map, group))
+            return rc;
+        if (int rc = get_cache_map(k_cache, num_kv_heads, num_slots, 128, &k_map128)) return rc;
+        if (int rc = get_cache_map(v_cache, num_kv_heads, num_slots, 128, &v_map128)) return rc;
+        b200::PrefillParams pp{};
+        pp.q = q;
+        pp.k_cache = k_cache;
+        pp.v_cache = v_cache;
+        pp.block_tables = block_tables;
+        pp.table_row_stride = table_row_stride;
+        pp.table_width = table_width;
+        pp.num_q_heads = num_q_heads;
+        pp.num_kv_heads = num_kv_heads;
+        pp.group = group;
+        pp.block_size = block_size;
+        pp.scale_log2 = p.scale_log2;
+        pp.plan = plan;
+        pp.ws_o = p.ws_o;
+        pp.ws_lse = p.ws_lse;
+        pp.batch = batch;
+        pp.prefix_chunks = prefix_chunks;
+        pp.ws_slot0 = num_splits;
+        pp.ws_slots = ws_slots;
+        cudaError_t e0 = b200::launch_cascade_prefix(pp, q_map, k_map128, v_map128, st);
+        if (e0 != cudaSuccess) return cuda_fail(e0, "cascade prefix launch");
     }
     cudaError_t e = b200::launch_decode(p, k_map, v_map, st);
     return e == cudaSuccess ? 0 : cuda_fail(e, "decode launch");

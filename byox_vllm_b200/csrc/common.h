@@ -44,6 +44,11 @@ struct DecodeParams {
     int64_t key_row_stride;
     int64_t value_row_stride;
     int64_t num_slots;
+    // optional shared-prefix cascade (cascade.cu): plan[0] = leading pages shared by every active
+    // row (device-resident, written by cascade_plan_kernel); their attention was computed by the
+    // prefix kernel into workspace slots [num_splits, num_splits + prefix_chunks).
+    const int32_t* plan;
+    int32_t prefix_chunks;  // 0 => no cascade
 };
 cudaError_t launch_decode(const DecodeParams& p, const CUtensorMap& k_map, const CUtensorMap& v_map,
                           cudaStream_t stream);
@@ -78,6 +83,14 @@ struct PrefillParams {
     int32_t group;
     int32_t block_size;
     float scale_log2;
+    // shared-prefix cascade mode (launch_cascade_prefix): q is the decode batch [batch, Hq, 128]
+    const int32_t* plan;   // device int32[4]: {shared pages P, first active row b0, active rows, 0}
+    float* ws_o;           // [batch * Hq, ws_slots, 128] fp32 normalised partials
+    float* ws_lse;         // [batch * Hq, ws_slots] log2-domain log-sum-exp
+    int32_t batch;
+    int32_t prefix_chunks; // split-KV chunks over the shared prefix (grid.y)
+    int32_t ws_slot0;      // chunk c writes slot ws_slot0 + c
+    int32_t ws_slots;
 };
 cudaError_t launch_prefill(const PrefillParams& p, cudaStream_t stream);
 
@@ -86,5 +99,34 @@ cudaError_t launch_prefill(const PrefillParams& p, cudaStream_t stream);
 cudaError_t launch_prefill_tc(const PrefillParams& p, const CUtensorMap& q_map,
                               const CUtensorMap& k_map, const CUtensorMap& v_map,
                               cudaStream_t stream);
+
+// Shared-prefix pass of the cascade decode: q_map is the decode batch q viewed as
+// (128 dims, Hq, batch) with box 64 x G x 128/G; k_map / v_map as for launch_prefill_tc.
+cudaError_t launch_cascade_prefix(const PrefillParams& p, const CUtensorMap& q_map,
+                                  const CUtensorMap& k_map, const CUtensorMap& v_map,
+                                  cudaStream_t stream);
+
+// ---- cascade.cu ------------------------------------------------------------------------------
+// Chunk geometry of the shared prefix, used identically by the prefix kernel (writer) and by the
+// decode epilogue / merge kernel (readers): 128-token tiles of the P shared pages are cut into at
+// most `chunks` contiguous ranges of `per` tiles; `valid` of them are non-empty.
+struct PrefixChunks {
+    int tiles;  // 128-token tiles in the shared prefix
+    int per;    // tiles per chunk
+    int valid;  // non-empty chunks
+};
+__host__ __device__ inline PrefixChunks prefix_chunks_of(int shared_pages, int block_size,
+                                                         int chunks) {
+    PrefixChunks c;
+    c.tiles = shared_pages * (block_size / 128);
+    c.per = chunks > 0 ? (c.tiles + chunks - 1) / chunks : 0;
+    c.valid = c.per > 0 ? (c.tiles + c.per - 1) / c.per : 0;
+    return c;
+}
+cudaError_t launch_cascade_plan(const int32_t* block_tables, int64_t table_row_stride,
+                                int32_t table_width, const int32_t* context_lens, int32_t batch,
+                                int32_t block_size, int32_t* plan, cudaStream_t stream);
+int cascade_pick_chunks(int32_t batch, int32_t num_q_heads, int32_t num_kv_heads,
+                        int32_t table_width, int32_t block_size, int32_t sm_count);
 
 }  // namespace b200

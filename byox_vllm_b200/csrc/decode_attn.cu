@@ -61,9 +61,15 @@ decode_split_kernel(const __grid_constant__ CUtensorMap k_map,
 
     const int ctx = p.context_lens[b];
     const int tiles_total = ctx > 0 ? (ctx + kTile - 1) / kTile : 0;
-    const int per_split = (tiles_total + S - 1) / S;
-    const int t_begin = split * per_split;
+    // Shared-prefix cascade: the first P pages were attended by the prefix kernel (its partials
+    // sit in workspace slots [S, S + chunks)); this kernel streams the remainder only. P pages
+    // lie entirely before token ctx-1 of every active row, so the remainder is never empty.
+    const int shared_pages = (p.plan != nullptr && ctx > 0) ? p.plan[0] : 0;
+    const int t_skip = shared_pages * (p.block_size / kTile);
+    const int per_split = (tiles_total - t_skip + S - 1) / S;
+    const int t_begin = t_skip + split * per_split;
     const int t_end = min(t_begin + per_split, tiles_total);
+    const int St = S + p.prefix_chunks;  // workspace slots per (b, q-head) row
     const int64_t q_row0 = static_cast<int64_t>(b) * Hq + static_cast<int64_t>(kvh) * G;
 
     if (t_begin >= t_end) {
@@ -74,7 +80,7 @@ decode_split_kernel(const __grid_constant__ CUtensorMap k_map,
             for (int i = threadIdx.x; i < G * kHeadDim; i += kDecodeThreads)
                 out[i] = __float2bfloat16(0.f);
         } else if (threadIdx.x < G) {
-            p.ws_lse[(q_row0 + threadIdx.x) * S + split] = -INFINITY;
+            p.ws_lse[(q_row0 + threadIdx.x) * St + split] = -INFINITY;
         }
         return;
     }
@@ -298,6 +304,8 @@ decode_split_kernel(const __grid_constant__ CUtensorMap k_map,
     consumer_bar_sync();
 
     const int d = threadIdx.x;  // 128 consumer threads <-> 128 dims
+    const int n_prefix =
+        shared_pages > 0 ? prefix_chunks_of(shared_pages, p.block_size, p.prefix_chunks).valid : 0;
     for (int h = 0; h < G; ++h) {
         float m = -INFINITY;
 #pragma unroll
@@ -309,25 +317,52 @@ decode_split_kernel(const __grid_constant__ CUtensorMap k_map,
             l += mw == -INFINITY ? 0.f : ml_smem[(w * 8 + h) * 2 + 1] * fast_exp2(mw - m);
             acc += osc[(w * 8 + h) * kMergeStride + d];
         }
-        const float val = l > 0.f ? acc / l : 0.f;
         if (S == 1) {
+            if (n_prefix > 0) {
+                // fold in the shared-prefix partials (normalised O_c, lse_c) of this row:
+                // out = (acc 2^(m-M) + sum_c O_c 2^(lse_c-M)) / (l 2^(m-M) + sum_c 2^(lse_c-M))
+                const float* lse_c = p.ws_lse + (q_row0 + h) * St + 1;
+                const float* o_c = p.ws_o + ((q_row0 + h) * St + 1) * kHeadDim + d;
+                float M = m;
+                for (int c = 0; c < n_prefix; ++c) M = fmaxf(M, lse_c[c]);
+                const float f = m == -INFINITY ? 0.f : fast_exp2(m - M);
+                acc *= f;
+                l *= f;
+                for (int c = 0; c < n_prefix; ++c) {
+                    const float ls = lse_c[c];
+                    if (ls == -INFINITY) continue;
+                    const float w = fast_exp2(ls - M);
+                    acc += w * o_c[c * kHeadDim];
+                    l += w;
+                }
+            }
+            const float val = l > 0.f ? acc / l : 0.f;
             static_cast<__nv_bfloat16*>(p.out)[(q_row0 + h) * kHeadDim + d] = __float2bfloat16(val);
         } else {
-            p.ws_o[((q_row0 + h) * S + split) * kHeadDim + d] = val;
-            if (d == 0) p.ws_lse[(q_row0 + h) * S + split] = l > 0.f ? m + log2f(l) : -INFINITY;
+            const float val = l > 0.f ? acc / l : 0.f;
+            p.ws_o[((q_row0 + h) * St + split) * kHeadDim + d] = val;
+            if (d == 0) p.ws_lse[(q_row0 + h) * St + split] = l > 0.f ? m + log2f(l) : -INFINITY;
         }
     }
     (void)mg;
 }
 
 // Combine num_splits normalised partials per (b, q-head) row: one warp per row, 4 dims per lane.
+// Slots [0, S_split) hold the split partials; with the cascade, slots [S_split, S_split + valid
+// prefix chunks) hold the shared-prefix partials of rows with context_lens > 0 (the other prefix
+// slots are never written and never read).
 __global__ void __launch_bounds__(128)
 decode_merge_kernel(const float* __restrict__ ws_o, const float* __restrict__ ws_lse,
-                    __nv_bfloat16* __restrict__ out, int32_t rows, int32_t S) {
+                    __nv_bfloat16* __restrict__ out, int32_t rows, int32_t S_split, int32_t St,
+                    int32_t num_q_heads, const int32_t* __restrict__ context_lens,
+                    const int32_t* __restrict__ plan, int32_t prefix_chunks, int32_t block_size) {
     const int row = blockIdx.x * 4 + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (row >= rows) return;
-    const float* lse = ws_lse + static_cast<int64_t>(row) * S;
+    int S = S_split;
+    if (plan != nullptr && context_lens[row / num_q_heads] > 0)
+        S += prefix_chunks_of(plan[0], block_size, prefix_chunks).valid;
+    const float* lse = ws_lse + static_cast<int64_t>(row) * St;
     float mx = -INFINITY;
     for (int s = lane; s < S; s += 32) mx = fmaxf(mx, lse[s]);
 #pragma unroll
@@ -340,7 +375,7 @@ decode_merge_kernel(const float* __restrict__ ws_o, const float* __restrict__ ws
             if (ls == -INFINITY) continue;  // empty split: its partial was never written
             const float w = fast_exp2(ls - mx);
             const float4 v = *reinterpret_cast<const float4*>(
-                ws_o + (static_cast<int64_t>(row) * S + s) * kHeadDim + lane * 4);
+                ws_o + (static_cast<int64_t>(row) * St + s) * kHeadDim + lane * 4);
             acc.x += w * v.x;
             acc.y += w * v.y;
             acc.z += w * v.z;
@@ -427,7 +462,9 @@ cudaError_t launch_decode(const DecodeParams& p, const CUtensorMap& k_map, const
     if (p.num_splits > 1) {
         const int rows = p.batch * p.num_q_heads;
         decode_merge_kernel<<<(rows + 3) / 4, 128, 0, stream>>>(
-            p.ws_o, p.ws_lse, static_cast<__nv_bfloat16*>(p.out), rows, p.num_splits);
+            p.ws_o, p.ws_lse, static_cast<__nv_bfloat16*>(p.out), rows, p.num_splits,
+            p.num_splits + p.prefix_chunks, p.num_q_heads, p.context_lens, p.plan,
+            p.prefix_chunks, p.block_size);
         count_launch();
         e = cudaGetLastError();
     }

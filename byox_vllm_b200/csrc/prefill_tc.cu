@@ -69,29 +69,60 @@ __device__ __forceinline__ void wait_bar(uint64_t* bar, uint32_t parity) {
     }
 }
 
+// kCascade = false: varlen causal prefill, CTA = (query-row pair, q-head, sequence).
+// kCascade = true:  shared-prefix pass of the cascade decode (cascade.cu). CTA = (pair of 128-row
+//   tiles of the B*G query rows of one KV head, prefix chunk, KV head). A tile row r is
+//   (batch row r / G, group head r % G): the TMA box 64 dims x G heads x 128/G batch rows of
+//   q [B, Hq, 128] lands in shared memory in exactly that order. Keys are the tiles of this
+//   chunk of the P shared pages (block ids from row b0's table), all visible: no masking. The
+//   epilogue writes normalised fp32 partials + log2-sum-exp for the decode merge.
+template <bool kCascade>
 __global__ void __launch_bounds__(kTcThreads, 1)
 prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
                   const __grid_constant__ CUtensorMap k_map,
                   const __grid_constant__ CUtensorMap v_map, const PrefillParams p) {
-    const int seq = blockIdx.z;
-    const int h = blockIdx.y;
-    const int q_begin = p.cu_seqlens_q[seq];
-    const int Lq = p.cu_seqlens_q[seq + 1] - q_begin;
-    const int k_begin = p.cu_seqlens_k[seq];
-    const int Lk = p.cu_seqlens_k[seq + 1] - k_begin;
-    const int n_pairs = (Lq + 2 * kTM - 1) / (2 * kTM);
-    if (static_cast<int>(blockIdx.x) >= n_pairs) return;  // uniform for the whole CTA
-    const int pair = n_pairs - 1 - blockIdx.x;            // heaviest (last) rows first
-    const int offset = Lk - Lq;                           // row i sees keys j <= i + offset
-    const int kvh = h / p.group;
-
-    int row0[2], n_kv[2];
+    int seq = 0, h = 0, kvh = 0, q_begin = 0, Lq = 0, k_begin = 0, Lk = 0, offset = 0;
+    int j0 = 0;       // first 128-token KV tile of this CTA (cascade: start of the chunk)
+    int chunk = 0;    // cascade: prefix chunk = workspace slot ws_slot0 + chunk
+    int q_c1 = 0;     // TMA head coordinate of the Q boxes
+    int row0[2], n_kv[2], q_c2[2];
+    if constexpr (kCascade) {
+        const PrefixChunks pc = prefix_chunks_of(p.plan[0], p.block_size, p.prefix_chunks);
+        chunk = blockIdx.y;
+        if (chunk >= pc.valid) return;  // uniform for the whole CTA (also: no shared prefix)
+        kvh = blockIdx.z;
+        seq = p.plan[1];                // row whose table names the shared pages
+        j0 = chunk * pc.per;
+        const int n = min(pc.per, pc.tiles - j0);
+        const int rows_per_sub = kTM / p.group;
 #pragma unroll
-    for (int i = 0; i < 2; ++i) {
-        row0[i] = pair * 2 * kTM + i * kTM;
-        const int rows_end = min(Lq, row0[i] + kTM);
-        const int vis = row0[i] < Lq ? min(Lk, rows_end + offset) : 0;  // visible keys [0, vis)
-        n_kv[i] = vis > 0 ? (vis + kTN - 1) / kTN : 0;
+        for (int i = 0; i < 2; ++i) {
+            row0[i] = (static_cast<int>(blockIdx.x) * 2 + i) * rows_per_sub;  // first batch row
+            n_kv[i] = row0[i] < p.batch ? n : 0;
+            q_c2[i] = row0[i];
+        }
+        q_c1 = kvh * p.group;
+    } else {
+        seq = blockIdx.z;
+        h = blockIdx.y;
+        q_begin = p.cu_seqlens_q[seq];
+        Lq = p.cu_seqlens_q[seq + 1] - q_begin;
+        k_begin = p.cu_seqlens_k[seq];
+        Lk = p.cu_seqlens_k[seq + 1] - k_begin;
+        const int n_pairs = (Lq + 2 * kTM - 1) / (2 * kTM);
+        if (static_cast<int>(blockIdx.x) >= n_pairs) return;  // uniform for the whole CTA
+        const int pair = n_pairs - 1 - blockIdx.x;            // heaviest (last) rows first
+        offset = Lk - Lq;                                     // row i sees keys j <= i + offset
+        kvh = h / p.group;
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            row0[i] = pair * 2 * kTM + i * kTM;
+            const int rows_end = min(Lq, row0[i] + kTM);
+            const int vis = row0[i] < Lq ? min(Lk, rows_end + offset) : 0;  // visible keys [0, vis)
+            n_kv[i] = vis > 0 ? (vis + kTN - 1) / kTN : 0;
+            q_c2[i] = q_begin + row0[i];
+        }
+        q_c1 = h;
     }
     const int n_max = max(n_kv[0], n_kv[1]);
 
@@ -137,16 +168,16 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
             mbar_expect_tx(&bar->q_full, n_q * kTileBytes);
             for (int i = 0; i < n_q; ++i) {
                 uint8_t* dst = smem + kSmemQ + i * kTileBytes;
-                tma_load_3d(dst, &q_map, &bar->q_full, 0, h, q_begin + row0[i]);
-                tma_load_3d(dst + kHalfBytes, &q_map, &bar->q_full, 64, h, q_begin + row0[i]);
+                tma_load_3d(dst, &q_map, &bar->q_full, 0, q_c1, q_c2[i]);
+                tma_load_3d(dst + kHalfBytes, &q_map, &bar->q_full, 64, q_c1, q_c2[i]);
             }
-            const bool paged = p.block_tables != nullptr;
+            const bool paged = kCascade || p.block_tables != nullptr;
             const int32_t* table =
                 paged ? p.block_tables + static_cast<int64_t>(seq) * p.table_row_stride : nullptr;
             for (int j = 0; j < n_max; ++j) {
                 const int s = j % kStages;
                 const uint32_t ph = (j / kStages) & 1u;
-                const int tok0 = j * kTN;
+                const int tok0 = (j0 + j) * kTN;
                 int slot;
                 if (paged) {
                     // a 128-token tile never straddles a page (block_size % 128 == 0)
@@ -217,7 +248,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
             wait_bar(&bar->v_full[s], (j / kStages) & 1u);
             // Rows at or beyond Lk inside the tile are masked (P = 0), but 0 * NaN would still
             // poison O: clear those V rows (unwritten cache slots may hold anything).
-            const int valid = Lk - j * kTN;
+            const int valid = kCascade ? kTN : Lk - j * kTN;  // shared pages are full
             if (valid < kTN) {
                 uint8_t* vs = smem + kSmemV + s * kTileBytes;
                 const int r_lo = max(valid, 0);
@@ -271,7 +302,8 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
             tc::tmem_ld128(s_tmem, sr);
 
             const int key0 = j * kTN;
-            const int lim = min(row + offset, Lk - 1) - key0;  // columns <= lim are visible
+            // columns <= lim are visible (cascade: every key of the shared prefix is)
+            const int lim = kCascade ? kTN - 1 : min(row + offset, Lk - 1) - key0;
             if (lim < kTN - 1) {
 #pragma unroll
                 for (int t = 0; t < 128; ++t)
@@ -333,6 +365,36 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
             mbar_arrive(&bar->p_full[i]);
         }
 
+        if constexpr (kCascade) {
+            // ---- epilogue: normalised fp32 partial + log2-sum-exp of this prefix chunk ----
+            const int b = row0[i] + r / p.group;
+            if (n > 0) {  // warp-uniform: n depends on the sub-tile only
+                wait_bar(&bar->o_full[i], 0);
+                tc::fence_after_sync();
+                const int64_t qrow =
+                    static_cast<int64_t>(b) * p.num_q_heads + kvh * p.group + r % p.group;
+                const int64_t slot = qrow * p.ws_slots + p.ws_slot0 + chunk;
+                const float inv = l > 0.f ? 1.f / l : 0.f;
+                float* og = p.ws_o + slot * kHeadDim;
+#pragma unroll
+                for (int q4 = 0; q4 < 4; ++q4) {
+                    uint32_t orow[32];
+                    tc::tmem_ld32(o_tmem + q4 * 32, orow);
+                    if (b < p.batch) {
+#pragma unroll
+                        for (int v4 = 0; v4 < 8; ++v4) {
+                            float4 f;
+                            f.x = __uint_as_float(orow[v4 * 4 + 0]) * inv;
+                            f.y = __uint_as_float(orow[v4 * 4 + 1]) * inv;
+                            f.z = __uint_as_float(orow[v4 * 4 + 2]) * inv;
+                            f.w = __uint_as_float(orow[v4 * 4 + 3]) * inv;
+                            *reinterpret_cast<float4*>(og + q4 * 32 + v4 * 4) = f;
+                        }
+                    }
+                }
+                if (b < p.batch) p.ws_lse[slot] = l > 0.f ? m_ref + log2f(l) : -INFINITY;
+            }
+        } else {
         // ---- epilogue: O / l -> bf16 -> global (row-predicated 16-byte stores) ----
         const bool row_ok = row < Lq;
         uint8_t* orow_g = static_cast<uint8_t*>(p.out) +
@@ -366,6 +428,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
 #pragma unroll
             for (int v = 0; v < 16; ++v) st_v4(orow_g + v * 16, make_int4(0, 0, 0, 0));
         }
+        }  // !kCascade
     }
 
     else {
@@ -388,13 +451,30 @@ cudaError_t launch_prefill_tc(const PrefillParams& p, const CUtensorMap& q_map,
     static bool configured = false;
     if (!configured) {
         cudaError_t e = cudaFuncSetAttribute(
-            prefill_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes);
+            prefill_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes);
         if (e != cudaSuccess) return e;
         configured = true;
     }
     const int pairs = (p.max_seqlen_q + 2 * kTM - 1) / (2 * kTM);
     dim3 grid(pairs, p.num_q_heads, p.num_seqs);
-    prefill_tc_kernel<<<grid, kTcThreads, kTcSmemBytes, stream>>>(q_map, k_map, v_map, p);
+    prefill_tc_kernel<false><<<grid, kTcThreads, kTcSmemBytes, stream>>>(q_map, k_map, v_map, p);
+    count_launch();
+    return cudaGetLastError();
+}
+
+cudaError_t launch_cascade_prefix(const PrefillParams& p, const CUtensorMap& q_map,
+                                  const CUtensorMap& k_map, const CUtensorMap& v_map,
+                                  cudaStream_t stream) {
+    static bool configured = false;
+    if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(
+            prefill_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes);
+        if (e != cudaSuccess) return e;
+        configured = true;
+    }
+    const int rows = p.batch * p.group;  // query rows per KV head
+    dim3 grid((rows + 2 * kTM - 1) / (2 * kTM), p.prefix_chunks, p.num_kv_heads);
+    prefill_tc_kernel<true><<<grid, kTcThreads, kTcSmemBytes, stream>>>(q_map, k_map, v_map, p);
     count_launch();
     return cudaGetLastError();
 }

@@ -11,6 +11,9 @@
  *   b200attn_store_decode      nanovllm/layers/attention.py:70-71 + :87-96 fused in one call
  *   b200attn_prefill_varlen    nanovllm/layers/attention.py:72-86   (flash_attn_varlen_func:
  *                                                                     dense and paged-prefix)
+ *   b200attn_cascade_*,        same decode call site (:87-96) for batches whose block tables
+ *   b200attn_store_decode_cascade   start with identical block ids — the prefix-cache hits
+ *                              nanovllm/engine/block_manager.py:41-71 produces
  *
  * Conventions
  *   - Plain pointers and sizes only; all buffers are DEVICE pointers owned by the caller (torch
@@ -34,7 +37,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 2
+#define B200ATTN_ABI_VERSION 3
 
 #define B200ATTN_DTYPE_BF16 0
 
@@ -118,6 +121,45 @@ int b200attn_store_decode(const void* q, const void* key, int64_t key_row_stride
                           int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim,
                           int32_t block_size, int64_t num_blocks, float scale, int32_t num_splits,
                           int32_t dtype, void* stream);
+
+/*
+ * Shared-prefix ("cascade") decode. When many rows of a decode batch start with the same
+ * physical pages (prefix-cache hits), the shared pages are attended once per KV head as a dense
+ * tensor-core problem (all batch * G query rows against P * block_size keys) instead of once per
+ * row, the remainder of every row is streamed as in b200attn_decode, and the two are merged by
+ * log-sum-exp. Results equal b200attn_store_decode within the same tolerance.
+ *
+ *   b200attn_cascade_pick_chunks  host-only: number of split-KV chunks for the shared-prefix pass,
+ *       or 0 when the cascade should not be armed for this shape (small batch / short tables /
+ *       block_size % 128 != 0; B200ATTN_CASCADE=0|1 forces it off / on).
+ *   b200attn_cascade_plan  one tiny launch per decode STEP (the plan depends only on the
+ *       metadata, so every layer of the step reuses it): writes plan[0] = P, the number of leading
+ *       pages whose block id is identical in every row with context_lens > 0 and that lie
+ *       entirely before every such row's newest token (P = 0 with fewer than 2 active rows);
+ *       plan[1] = first active row; plan[2] = active rows; plan[3] = 0. `plan` is a device int32[4].
+ *   b200attn_store_decode_cascade  = b200attn_store_decode + (plan, prefix_chunks). The split
+ *       counts and launch shapes depend on host-visible sizes only; P is read on the device, so the
+ *       call is graph-capturable and P == 0 degrades to the plain path. The workspace must hold
+ *       b200attn_decode_workspace_bytes(batch, num_q_heads, head_dim, num_splits + prefix_chunks).
+ *       plan == NULL and prefix_chunks == 0 is exactly b200attn_store_decode.
+ */
+int b200attn_cascade_pick_chunks(int32_t batch, int32_t num_q_heads, int32_t num_kv_heads,
+                                 int32_t table_width, int32_t block_size, int32_t sm_count);
+
+int b200attn_cascade_plan(const int32_t* block_tables, int64_t table_row_stride,
+                          int32_t table_width, const int32_t* context_lens, int32_t batch,
+                          int32_t block_size, int32_t* plan, void* stream);
+
+int b200attn_store_decode_cascade(const void* q, const void* key, int64_t key_row_stride,
+                                  const void* value, int64_t value_row_stride,
+                                  const int32_t* slot_mapping, void* k_cache, void* v_cache,
+                                  const int32_t* block_tables, int64_t table_row_stride,
+                                  int32_t table_width, const int32_t* context_lens, void* out,
+                                  void* workspace, size_t workspace_bytes, int32_t batch,
+                                  int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim,
+                                  int32_t block_size, int64_t num_blocks, float scale,
+                                  int32_t num_splits, const int32_t* plan, int32_t prefix_chunks,
+                                  int32_t dtype, void* stream);
 
 /*
  * Varlen causal prefill (bottom-right aligned causal mask, as flash_attn_varlen_func):

@@ -108,6 +108,25 @@ def paged_decode_ref(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tens
     return out
 
 
+def shared_prefix_pages_ref(context_lens: torch.Tensor, block_tables: torch.Tensor,
+                            block_size: int) -> tuple[int, int, int]:
+    """(P, b0, active): checker for the cascade plan kernel (byox_vllm_b200/csrc/cascade.cu).
+    P = leading table columns whose block id is equal in every row with context_lens > 0 and whose
+    page ends before every such row's newest token (index ctx-1); 0 with fewer than two active
+    rows. The sharing itself is what reference engine/block_manager.py:41-71 produces on prefix
+    hits; the attention result does not depend on P (paged_decode_ref is the oracle for that)."""
+    lens = [int(x) for x in context_lens.tolist()]
+    rows = [b for b, c in enumerate(lens) if c > 0]
+    if len(rows) < 2:
+        return 0, 0, len(rows)
+    pmax = min(min((lens[b] - 1) // block_size for b in rows), block_tables.shape[1])
+    t0 = block_tables[rows[0]].tolist()
+    P = 0
+    while P < pmax and all(int(block_tables[b, P]) == t0[P] for b in rows):
+        P += 1
+    return P, rows[0], len(rows)
+
+
 def prefill_varlen_ref(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor,
                        cu_seqlens_q: torch.Tensor, cu_seqlens_k: torch.Tensor,
                        scale: float | None = None,

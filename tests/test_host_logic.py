@@ -146,3 +146,58 @@ def test_install_under_a_nanovllm_package(tmp_path, monkeypatch, built_lib):
     from byox_vllm_b200.context import get_context
 
     assert ours.get_context is get_context
+
+
+def test_cascade_chunks_heuristic_is_host_only(lib):
+    """Armed only where a shared prefix can pay: batch >= 64, tables holding >= 8192 tokens, pages
+    that are multiples of 128 tokens; about one prefix CTA per SM; never more chunks than tiles."""
+    sm = 148
+    pick = lib.b200attn_cascade_pick_chunks
+    assert pick(256, 16, 8, 16, 256, sm) == 0      # bench shape c2: tables hold 4096 tokens
+    assert pick(128, 32, 8, 17, 256, sm) == 0      # c3
+    assert pick(32, 8, 1, 40, 256, sm) == 0        # small batch
+    assert pick(256, 8, 1, 40, 64, sm) == 0        # 64-token pages
+    c4 = pick(256, 8, 1, 40, 256, sm)              # config 4 per rank: 8 row-tile pairs x 1 head
+    assert c4 == 16
+    assert pick(256, 64, 8, 40, 256, sm) == 2      # 32B at TP=1: 8 pairs x 8 KV heads = 64 CTAs
+    assert 1 <= pick(512, 32, 8, 64, 256, 0) <= 16  # unknown SM count -> 148
+    assert pick(0, 8, 1, 40, 256, sm) == 0 and pick(256, 8, 1, 0, 256, sm) == 0
+
+
+def test_cascade_argument_errors(lib):
+    from byox_vllm_b200._lib import E_BADARG
+
+    z = 0x1000  # fake non-null, 16-byte aligned device pointers: rejected before any CUDA call
+    rc = lib.b200attn_store_decode_cascade(z, None, 0, None, 0, None, z, z, z, 4, 4, z, z, None, 0,
+                                           2, 8, 2, 128, 256, 8, 0.1, 1, None, 3, 0, None)
+    assert rc == E_BADARG and b"plan" in lib.b200attn_last_error()
+    rc = lib.b200attn_store_decode_cascade(z, None, 0, None, 0, None, z, z, z, 4, 4, z, z, None, 0,
+                                           2, 8, 2, 128, 256, 8, 0.1, 1, z, 0, 0, None)
+    assert rc == E_BADARG
+    rc = lib.b200attn_store_decode_cascade(z, None, 0, None, 0, None, z, z, z, 4, 4, z, z, None, 0,
+                                           2, 8, 2, 128, 256, 8, 0.1, 1, z, 3, 0, None)
+    assert rc == _lib.E_WORKSPACE  # a cascade always needs the partial workspace
+    assert lib.b200attn_cascade_plan(z, 4, 4, z, 2, 256, None, None) == E_BADARG
+
+
+def test_shared_prefix_oracle_on_block_manager_style_tables():
+    """The plan checker itself: tables as BlockManager hands them out for prefix hits
+    (reference engine/block_manager.py:41-71 reuses the cached block ids in order)."""
+    from oracle import attention_oracle as orc
+    from tools import synth
+
+    c = synth.shared_prefix_decode_case([900, 1000, 1100, 800], 3, 8, 2, seed=1)
+    assert orc.shared_prefix_pages_ref(c.meta["context_lens"], c.meta["block_tables"], 256) == \
+        (3, 0, 4)
+    c = synth.shared_prefix_decode_case([300, 1000, 1100], 3, 8, 2, seed=1)
+    assert orc.shared_prefix_pages_ref(c.meta["context_lens"], c.meta["block_tables"], 256)[0] == 1
+    c = synth.shared_prefix_decode_case([512, 769], 2, 8, 2, seed=1)  # token 511 opens page 1
+    assert orc.shared_prefix_pages_ref(c.meta["context_lens"], c.meta["block_tables"], 256)[0] == 1
+    c = synth.shared_prefix_decode_case([900, 1000, 1100], [3, 1, 3], 8, 2, seed=1)
+    assert orc.shared_prefix_pages_ref(c.meta["context_lens"], c.meta["block_tables"], 256)[0] == 1
+    lens = c.meta["context_lens"].clone()
+    lens[1] = 0  # the diverging row becomes a padding row
+    assert orc.shared_prefix_pages_ref(lens, c.meta["block_tables"], 256) == (3, 0, 2)
+    one = synth.shared_prefix_decode_case([2000], 4, 8, 2, seed=1)
+    assert orc.shared_prefix_pages_ref(one.meta["context_lens"], one.meta["block_tables"], 256) == \
+        (0, 0, 1)

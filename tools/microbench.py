@@ -117,6 +117,130 @@ def bench_decode(out, quick):
             torch.cuda.empty_cache()
 
 
+def bench_sweep(out, quick):
+    """BASELINE config 5: B in 1..512 x ctx in 1k..128k (Hq 32 / Hkv 8), capped at B*ctx <= 4 Mi
+    tokens (16 GiB of KV) so the whole grid runs in a couple of minutes."""
+    from flash_attn import flash_attn_with_kvcache
+
+    from byox_vllm_b200.attention import decode_num_splits, paged_decode
+
+    Hq, Hkv = 32, 8
+    no_ref = "--no-ref" in sys.argv
+    batches = (1, 8, 64, 512) if quick else (1, 2, 4, 8, 16, 32, 64, 128, 256, 512)
+    ctxs = (1024, 8192, 131072) if quick else (1024, 2048, 4096, 8192, 16384, 32768, 65536, 131072)
+    for B in batches:
+        for ctx in ctxs:
+            if B * ctx > (4 << 20):
+                continue
+            q, kc, vc, lens, bt, alg = decode_inputs(B, ctx, Hq, Hkv, False)
+            scale = D ** -0.5
+            o = torch.empty_like(q)
+            splits = decode_num_splits(B, Hkv, bt.size(1), BLOCK)
+            t_min, t_med = timed(lambda: paged_decode(q, kc, vc, lens, bt, scale, out=o), iters=6)
+            rec = dict(kind="sweep", B=B, ctx=ctx, Hq=Hq, Hkv=Hkv, splits=splits, alg_bytes=alg,
+                       ours_us=t_med * 1e3, ours_min_us=t_min * 1e3, ours_gbs=alg / t_med / 1e6,
+                       ours_frac=alg / t_med / 1e6 / PEAK)
+            if not no_ref:
+                q4 = q.unsqueeze(1)
+                f_min, f_med = timed(lambda: flash_attn_with_kvcache(
+                    q4, kc, vc, cache_seqlens=lens, block_table=bt, softmax_scale=scale,
+                    causal=True), iters=6)
+                rec.update(fa2_us=f_med * 1e3, fa2_gbs=alg / f_med / 1e6, speedup=f_med / t_med)
+            out.write(json.dumps(rec) + "\n")
+            out.flush()
+            print(f"sweep B={B:4d} ctx={ctx:6d} S={splits:3d}: ours {t_med * 1e3:8.1f} us "
+                  f"{rec['ours_gbs']:7.0f} GB/s ({rec['ours_frac']:.2f})"
+                  + (f" | fa2 {rec['fa2_us']:8.1f} us x{rec['speedup']:.2f}" if not no_ref else ""),
+                  flush=True)
+            del q, kc, vc, lens, bt
+            torch.cuda.empty_cache()
+
+
+CASCADE_SHAPES = [  # (B, ctx, shared tokens, Hq, Hkv)  -- BASELINE config 4 per rank first
+    (256, 8192, 7680, 8, 1), (256, 8192, 7680, 64, 8), (128, 4096, 3840, 32, 8),
+    (64, 8192, 4096, 8, 1), (256, 8192, 0, 8, 1), (256, 2048, 1024, 16, 8),
+]
+
+
+def cascade_inputs(B, ctx, shared, Hq, Hkv, seed=0):
+    """Rows share the first `shared` tokens (whole pages, same physical block ids) and own the
+    rest; pages are scattered. Returns unique-page and per-row (logical) algorithmic bytes."""
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    W = (ctx + BLOCK - 1) // BLOCK
+    P = shared // BLOCK
+    own = W - P
+    nb = P + B * own + 4
+    perm = torch.randperm(nb, generator=g, device="cuda").to(torch.int32)
+    bt = torch.empty(B, W, dtype=torch.int32, device="cuda")
+    bt[:, :P] = perm[:P].unsqueeze(0)
+    bt[:, P:] = perm[P:P + B * own].view(B, own)
+    lens = torch.full((B,), ctx, dtype=torch.int32, device="cuda")
+    kc = torch.empty(nb, BLOCK, Hkv, D, dtype=torch.bfloat16, device="cuda").normal_(generator=g)
+    vc = torch.empty(nb, BLOCK, Hkv, D, dtype=torch.bfloat16, device="cuda").normal_(generator=g)
+    q = torch.empty(B, Hq, D, dtype=torch.bfloat16, device="cuda").normal_(generator=g)
+    row = Hkv * D * 2 * 2
+    io = 2 * B * Hq * D * 2 + 4 * B * W + 4 * B
+    unique = (shared + B * (ctx - shared)) * row + io
+    logical = B * ctx * row + io
+    flops = 4 * B * Hq * D * ctx
+    return q, kc, vc, lens, bt, unique, logical, flops
+
+
+def bench_cascade(out, quick):
+    from flash_attn import flash_attn_with_kvcache
+
+    from byox_vllm_b200.attention import (cascade_chunks, cascade_plan, decode_num_splits,
+                                          paged_decode)
+
+    no_ref = "--no-ref" in sys.argv
+    for (B, ctx, shared, Hq, Hkv) in (CASCADE_SHAPES[:2] if quick else CASCADE_SHAPES):
+        q, kc, vc, lens, bt, unique, logical, flops = cascade_inputs(B, ctx, shared, Hq, Hkv)
+        scale = D ** -0.5
+        o, o2 = torch.empty_like(q), torch.empty_like(q)
+        splits = decode_num_splits(B, Hkv, bt.size(1), BLOCK)
+        auto = cascade_chunks(B, Hq, Hkv, bt.size(1), BLOCK)
+        p_min, p_med = timed(lambda: paged_decode(q, kc, vc, lens, bt, scale, out=o2))
+        plan = cascade_plan(lens, bt, BLOCK)
+        pl_min, pl_med = timed(lambda: cascade_plan(lens, bt, BLOCK))
+        rec = dict(kind="cascade", B=B, ctx=ctx, shared=shared, Hq=Hq, Hkv=Hkv, splits=splits,
+                   auto_chunks=auto, plan=plan.cpu().tolist(), unique_bytes=unique,
+                   logical_bytes=logical, flops=flops, plain_us=p_med * 1e3,
+                   plain_logical_gbs=logical / p_med / 1e6, plan_us=pl_med * 1e3)
+        best = None
+        for chunks in sorted({max(auto, 1), 2, 4, 8, 16}):
+            c_min, c_med = timed(lambda: paged_decode(q, kc, vc, lens, bt, scale, out=o, plan=plan,
+                                                      prefix_chunks=chunks))
+            rec[f"cascade_us_c{chunks}"] = c_med * 1e3
+            if chunks == max(auto, 1):
+                rec["cascade_us"] = c_med * 1e3
+            if best is None or c_med < best[1]:
+                best = (chunks, c_med)
+        err_plain = (o.float() - o2.float()).abs().max().item()
+        rec.update(best_chunks=best[0], best_us=best[1] * 1e3,
+                   cascade_unique_gbs=unique / (rec["cascade_us"] * 1e-6) / 1e9,
+                   cascade_logical_gbs=logical / (rec["cascade_us"] * 1e-6) / 1e9,
+                   cascade_tflops=flops / (rec["cascade_us"] * 1e-6) / 1e12,
+                   speedup_vs_plain=p_med * 1e3 / rec["cascade_us"],
+                   max_abs_diff_vs_plain=err_plain)
+        if not no_ref:
+            q4 = q.unsqueeze(1)
+            f_min, f_med = timed(lambda: flash_attn_with_kvcache(
+                q4, kc, vc, cache_seqlens=lens, block_table=bt, softmax_scale=scale, causal=True))
+            ref = flash_attn_with_kvcache(q4, kc, vc, cache_seqlens=lens, block_table=bt,
+                                          softmax_scale=scale, causal=True).squeeze(1)
+            rec.update(fa2_us=f_med * 1e3, speedup_vs_fa2=f_med * 1e3 / rec["cascade_us"],
+                       max_abs_diff_vs_fa2=(o.float() - ref.float()).abs().max().item())
+        out.write(json.dumps(rec) + "\n")
+        out.flush()
+        print(f"cascade B={B} ctx={ctx} shared={shared} {Hq}/{Hkv} P={rec['plan'][0]} "
+              f"chunks={auto}: cascade {rec['cascade_us']:.1f} us (best c{best[0]} "
+              f"{best[1] * 1e3:.1f}) | plain {p_med * 1e3:.1f} us | fa2 "
+              f"{rec.get('fa2_us', float('nan')):.1f} us | plan {pl_med * 1e3:.1f} us | "
+              f"x{rec['speedup_vs_plain']:.2f} vs plain, err {err_plain:.4f}", flush=True)
+        del q, kc, vc, lens, bt
+        torch.cuda.empty_cache()
+
+
 def bench_store(out, quick):
     import triton
     import triton.language as tl
@@ -261,7 +385,8 @@ def main():
         out.write(json.dumps(dict(kind="env", gpu=torch.cuda.get_device_name(0), hbm_peak=PEAK,
                                   tf_peak=TF_PEAK, torch=torch.__version__)) + "\n")
         for k in kinds:
-            {"decode": bench_decode, "store": bench_store, "prefill": bench_prefill}[k](out, quick)
+            {"decode": bench_decode, "store": bench_store, "prefill": bench_prefill,
+             "sweep": bench_sweep, "cascade": bench_cascade}[k](out, quick)
 
 
 if __name__ == "__main__":

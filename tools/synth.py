@@ -87,6 +87,37 @@ def decode_case(batch: int, ctx, Hq: int, Hkv: int, D: int = 128, block_size: in
                       float(D) ** -0.5)
 
 
+def shared_prefix_decode_case(ctx, shared_pages, Hq: int, Hkv: int, D: int = 128,
+                              block_size: int = 256, seed: int = 0, device="cpu",
+                              spare_blocks: int = 3) -> DecodeCase:
+    """Decode batch whose rows start with the same physical pages, as BlockManager hands out for
+    prefix-cache hits (reference engine/block_manager.py:41-71). `shared_pages`: int (every row
+    shares that many leading pages with row 0) or a per-row list (rows with fewer shared pages
+    diverge earlier; 0 = unrelated row). A row shares at most the pages it has."""
+    lens = list(ctx)
+    batch = len(lens)
+    sp = [shared_pages] * batch if isinstance(shared_pages, int) else list(shared_pages)
+    assert len(sp) == batch and all(c >= 1 for c in lens)
+    rng = random.Random(seed)
+    gen = torch.Generator(device=device).manual_seed(seed)
+    need = [(c + block_size - 1) // block_size for c in lens]
+    sp = [min(s, n) for s, n in zip(sp, need)]
+    n_shared = max(sp) if sp else 0
+    own = [n - s for n, s in zip(need, sp)]
+    num_blocks = n_shared + sum(own) + spare_blocks
+    ids = _alloc_blocks(n_shared + sum(own), num_blocks, rng)
+    shared_ids, at = ids[:n_shared], n_shared
+    seqs = []
+    for c, s, o in zip(lens, sp, own):
+        seqs.append(md.SeqState(num_tokens=c, block_table=shared_ids[:s] + ids[at:at + o]))
+        at += o
+    shape = (num_blocks, block_size, Hkv, D)
+    k_cache, v_cache = _randn(shape, gen, device), _randn(shape, gen, device)
+    q, k, v = _qkv(batch, Hq, Hkv, D, gen, device)
+    return DecodeCase(q, k, v, k_cache, v_cache, md.prepare_decode(seqs, block_size), seqs,
+                      float(D) ** -0.5)
+
+
 def prefill_case(lens, Hq: int, Hkv: int, cached=None, D: int = 128, block_size: int = 256,
                  seed: int = 0, device="cpu", spare_blocks: int = 3) -> PrefillCase:
     """`lens`: full lengths; `cached`: per-sequence cached prefix tokens (multiples of block_size,
