@@ -263,8 +263,8 @@ int b200attn_store_decode_cascade(const void* q, const void* key, int64_t key_ro
                                   int32_t num_splits, const int32_t* plan, int32_t prefix_chunks,
                                   int32_t dtype, void* stream) {
     if (int rc = check_attn_shape(num_q_heads, num_kv_heads, head_dim, block_size, dtype)) return rc;
-    if (prefix_chunks < 0 || prefix_chunks > 64 || (prefix_chunks > 0) != (plan != nullptr))
-        return fail(B200ATTN_E_BADARG, "plan and prefix_chunks (0..64) must be given together");
+    if (prefix_chunks < 0 || prefix_chunks > 32 || (prefix_chunks > 0) != (plan != nullptr))
+        return fail(B200ATTN_E_BADARG, "plan and prefix_chunks (0..32) must be given together");
     if (prefix_chunks > 0 && (block_size % 128 != 0 || 128 % (num_q_heads / num_kv_heads) != 0))
         return fail(B200ATTN_E_UNSUPPORTED,
                     "cascade needs block_size %% 128 == 0 and a GQA group dividing 128");
@@ -272,6 +272,7 @@ int b200attn_store_decode_cascade(const void* q, const void* key, int64_t key_ro
         return fail(B200ATTN_E_BADARG, "negative or zero size");
     if (batch == 0) return 0;
     if (batch > 65535) return fail(B200ATTN_E_UNSUPPORTED, "batch %d > 65535", batch);
+    if (num_splits > 64) return fail(B200ATTN_E_UNSUPPORTED, "num_splits %d > 64", num_splits);
     if (!q || !k_cache || !v_cache || !block_tables || !context_lens || !out)
         return fail(B200ATTN_E_BADARG, "null pointer");
     if (!std::isfinite(scale)) return fail(B200ATTN_E_BADARG, "scale is not finite");

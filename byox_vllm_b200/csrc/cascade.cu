@@ -113,7 +113,9 @@ int cascade_pick_chunks(int32_t batch, int32_t num_q_heads, int32_t num_kv_heads
     if (table_width < 2) return 0;  // one page per row: nothing can lie before the newest token
     const int64_t row_tiles = (static_cast<int64_t>(batch) * group + 255) / 256;
     const int64_t ctas = row_tiles * num_kv_heads;
-    int64_t chunks = (sm_count + ctas / 2) / ctas;  // about one CTA per SM
+    // The prefix CTAs run one per SM: the largest chunk count that still fits ONE wave (a second,
+    // partly filled wave costs more than shorter chunks save; profiles/r01_cascade_chunks.log).
+    int64_t chunks = sm_count / ctas;
     const int64_t max_tiles = (capacity - 1) / 128;
     if (chunks > max_tiles) chunks = max_tiles;
     if (chunks > 16) chunks = 16;

@@ -35,6 +35,12 @@ constexpr int kSubTileBytes = kTile * 128;  // [64 tok][64 dims] bf16 = 8 KiB, 1
 constexpr int kStageBytes = 4 * kSubTileBytes;  // K lo/hi + V lo/hi = 32 KiB
 constexpr int kMergeStride = 132;           // padded fp32 row (bank-conflict-free transposed writes)
 
+// Programmatic dependent launch: block until the primary grid (the cascade prefix pass) has
+// completed and its global writes are visible. A no-op when launched without the attribute.
+__device__ __forceinline__ void grid_dependency_wait() {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 __device__ __forceinline__ void consumer_bar_sync() {
     asm volatile("bar.sync 1, %0;" ::"n"(kConsumerWarps * 32) : "memory");
 }
@@ -303,48 +309,86 @@ decode_split_kernel(const __grid_constant__ CUtensorMap k_map,
         }
     consumer_bar_sync();
 
-    const int d = threadIdx.x;  // 128 consumer threads <-> 128 dims
+    // Final reduction: warp w owns heads w, w+4; lane owns dims 4*lane..4*lane+3 (float4 smem
+    // reads, 8-byte bf16 / 16-byte fp32 global stores, a head row is one coalesced line).
     const int n_prefix =
         shared_pages > 0 ? prefix_chunks_of(shared_pages, p.block_size, p.prefix_chunks).valid : 0;
-    for (int h = 0; h < G; ++h) {
+    for (int h = warp; h < G; h += kConsumerWarps) {
         float m = -INFINITY;
 #pragma unroll
         for (int w = 0; w < kConsumerWarps; ++w) m = fmaxf(m, ml_smem[(w * 8 + h) * 2]);
-        float l = 0.f, acc = 0.f;
+        float l = 0.f;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
         for (int w = 0; w < kConsumerWarps; ++w) {
             const float mw = ml_smem[(w * 8 + h) * 2];
             l += mw == -INFINITY ? 0.f : ml_smem[(w * 8 + h) * 2 + 1] * fast_exp2(mw - m);
-            acc += osc[(w * 8 + h) * kMergeStride + d];
+            const float4 x =
+                *reinterpret_cast<const float4*>(&osc[(w * 8 + h) * kMergeStride + 4 * lane]);
+            acc.x += x.x;
+            acc.y += x.y;
+            acc.z += x.z;
+            acc.w += x.w;
         }
+        const int64_t row = q_row0 + h;
         if (S == 1) {
             if (n_prefix > 0) {
+                grid_dependency_wait();  // the prefix pass (PDL primary) has written its slots
                 // fold in the shared-prefix partials (normalised O_c, lse_c) of this row:
                 // out = (acc 2^(m-M) + sum_c O_c 2^(lse_c-M)) / (l 2^(m-M) + sum_c 2^(lse_c-M))
-                const float* lse_c = p.ws_lse + (q_row0 + h) * St + 1;
-                const float* o_c = p.ws_o + ((q_row0 + h) * St + 1) * kHeadDim + d;
-                float M = m;
-                for (int c = 0; c < n_prefix; ++c) M = fmaxf(M, lse_c[c]);
+                // lane c holds lse_c; the O_c loads are independent and unrolled so they overlap.
+                const float my_lse = lane < n_prefix ? p.ws_lse[row * St + 1 + lane] : -INFINITY;
+                float M = fmaxf(m, my_lse);
+#pragma unroll
+                for (int off = 16; off > 0; off >>= 1)
+                    M = fmaxf(M, __shfl_xor_sync(0xffffffffu, M, off));
                 const float f = m == -INFINITY ? 0.f : fast_exp2(m - M);
-                acc *= f;
+                const float my_w = my_lse == -INFINITY ? 0.f : fast_exp2(my_lse - M);
+                acc.x *= f;
+                acc.y *= f;
+                acc.z *= f;
+                acc.w *= f;
                 l *= f;
-                for (int c = 0; c < n_prefix; ++c) {
-                    const float ls = lse_c[c];
-                    if (ls == -INFINITY) continue;
-                    const float w = fast_exp2(ls - M);
-                    acc += w * o_c[c * kHeadDim];
-                    l += w;
+                const float4* o_c =
+                    reinterpret_cast<const float4*>(p.ws_o + (row * St + 1) * kHeadDim) + lane;
+                for (int c0 = 0; c0 < n_prefix; c0 += 8) {
+                    float4 x[8];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u)
+                        x[u] = c0 + u < n_prefix ? o_c[(c0 + u) * (kHeadDim / 4)]
+                                                 : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) {
+                        const float w = __shfl_sync(0xffffffffu, my_w, (c0 + u) & 31);
+                        const float wu = c0 + u < n_prefix ? w : 0.f;
+                        acc.x += wu * x[u].x;
+                        acc.y += wu * x[u].y;
+                        acc.z += wu * x[u].z;
+                        acc.w += wu * x[u].w;
+                        l += wu;
+                    }
                 }
             }
-            const float val = l > 0.f ? acc / l : 0.f;
-            static_cast<__nv_bfloat16*>(p.out)[(q_row0 + h) * kHeadDim + d] = __float2bfloat16(val);
+            const bool live = l > 0.f;
+            uint2 pk;
+            pk.x = pack_bf16x2(live ? acc.x / l : 0.f, live ? acc.y / l : 0.f);
+            pk.y = pack_bf16x2(live ? acc.z / l : 0.f, live ? acc.w / l : 0.f);
+            *reinterpret_cast<uint2*>(static_cast<__nv_bfloat16*>(p.out) + row * kHeadDim +
+                                      4 * lane) = pk;
         } else {
-            const float val = l > 0.f ? acc / l : 0.f;
-            p.ws_o[((q_row0 + h) * St + split) * kHeadDim + d] = val;
-            if (d == 0) p.ws_lse[(q_row0 + h) * St + split] = l > 0.f ? m + log2f(l) : -INFINITY;
+            const bool live = l > 0.f;
+            acc.x = live ? acc.x / l : 0.f;
+            acc.y = live ? acc.y / l : 0.f;
+            acc.z = live ? acc.z / l : 0.f;
+            acc.w = live ? acc.w / l : 0.f;
+            *reinterpret_cast<float4*>(p.ws_o + (row * St + split) * kHeadDim + 4 * lane) = acc;
+            if (lane == 0) p.ws_lse[row * St + split] = l > 0.f ? m + log2f(l) : -INFINITY;
         }
     }
     (void)mg;
+    // With the cascade armed this grid is a programmatic dependent of the prefix pass: make sure
+    // it cannot finish before its primary did (the merge kernel that follows reads both).
+    if (p.plan != nullptr) grid_dependency_wait();
 }
 
 // Combine num_splits normalised partials per (b, q-head) row: one warp per row, 4 dims per lane.
@@ -363,24 +407,47 @@ decode_merge_kernel(const float* __restrict__ ws_o, const float* __restrict__ ws
     if (plan != nullptr && context_lens[row / num_q_heads] > 0)
         S += prefix_chunks_of(plan[0], block_size, prefix_chunks).valid;
     const float* lse = ws_lse + static_cast<int64_t>(row) * St;
+    // lane s (and s + 32) holds the weight of slot s; the partial loads of 8 slots are issued
+    // together so their latencies overlap (S <= 64 + 32 slots).
+    float my_lse[3], my_w[3];
     float mx = -INFINITY;
-    for (int s = lane; s < S; s += 32) mx = fmaxf(mx, lse[s]);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        my_lse[i] = lane + 32 * i < S ? lse[lane + 32 * i] : -INFINITY;
+        mx = fmaxf(mx, my_lse[i]);
+    }
 #pragma unroll
     for (int off = 16; off > 0; off >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, off));
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     float wsum = 0.f;
-    if (mx != -INFINITY) {
-        for (int s = 0; s < S; ++s) {
-            const float ls = lse[s];
-            if (ls == -INFINITY) continue;  // empty split: its partial was never written
-            const float w = fast_exp2(ls - mx);
-            const float4 v = *reinterpret_cast<const float4*>(
-                ws_o + (static_cast<int64_t>(row) * St + s) * kHeadDim + lane * 4);
-            acc.x += w * v.x;
-            acc.y += w * v.y;
-            acc.z += w * v.z;
-            acc.w += w * v.w;
-            wsum += w;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        my_w[i] = my_lse[i] == -INFINITY ? 0.f : fast_exp2(my_lse[i] - mx);  // empty: weight 0
+        wsum += my_w[i];
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) wsum += __shfl_xor_sync(0xffffffffu, wsum, off);
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    const float4* po =
+        reinterpret_cast<const float4*>(ws_o + static_cast<int64_t>(row) * St * kHeadDim) + lane;
+    for (int s0 = 0; s0 < S; s0 += 8) {
+        float4 x[8];
+        float w[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int sl = s0 + u;
+            const float wa = __shfl_sync(0xffffffffu, my_w[0], sl & 31);
+            const float wb = __shfl_sync(0xffffffffu, my_w[1], sl & 31);
+            const float wc = __shfl_sync(0xffffffffu, my_w[2], sl & 31);
+            w[u] = sl < S ? (sl < 32 ? wa : (sl < 64 ? wb : wc)) : 0.f;
+            // an empty slot (weight 0) was never written: do not read it
+            x[u] = w[u] != 0.f ? po[sl * (kHeadDim / 4)] : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            acc.x += w[u] * x[u].x;
+            acc.y += w[u] * x[u].y;
+            acc.z += w[u] * x[u].z;
+            acc.w += w[u] * x[u].w;
         }
     }
     const float inv = wsum > 0.f ? 1.f / wsum : 0.f;
@@ -409,6 +476,26 @@ cudaError_t launch_split(const DecodeParams& p, const CUtensorMap& k_map, const 
         configured = true;
     }
     dim3 grid(p.num_kv_heads, p.num_splits, p.batch);
+    if (p.plan != nullptr) {
+        // Programmatic dependent launch behind the prefix pass: this grid may start while the
+        // prefix CTAs are still running (they signal launch_dependents at once) and only waits
+        // (griddepcontrol.wait) where it consumes their partials. It touches nothing the prefix
+        // pass reads or writes before that point: the fused scatter writes token ctx-1, which
+        // lies after the shared pages, and the split partials go to other workspace slots.
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = grid;
+        cfg.blockDim = dim3(kDecodeThreads);
+        cfg.dynamicSmemBytes = smem;
+        cfg.stream = stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        cudaError_t e = cudaLaunchKernelEx(&cfg, decode_split_kernel<kStages>, k_map, v_map, p);
+        count_launch();
+        return e != cudaSuccess ? e : cudaGetLastError();
+    }
     decode_split_kernel<kStages><<<grid, kDecodeThreads, smem, stream>>>(k_map, v_map, p);
     count_launch();
     return cudaGetLastError();

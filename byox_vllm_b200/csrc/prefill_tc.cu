@@ -87,6 +87,10 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
     int q_c1 = 0;     // TMA head coordinate of the Q boxes
     int row0[2], n_kv[2], q_c2[2];
     if constexpr (kCascade) {
+        // Let the dependent grid (the streaming decode over the per-row remainders, launched
+        // with programmatic stream serialization) start now; it waits on this grid only where it
+        // reads the partials written below.
+        asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
         const PrefixChunks pc = prefix_chunks_of(p.plan[0], p.block_size, p.prefix_chunks);
         chunk = blockIdx.y;
         if (chunk >= pc.valid) return;  // uniform for the whole CTA (also: no shared prefix)

@@ -160,6 +160,7 @@ def test_cascade_chunks_heuristic_is_host_only(lib):
     c4 = pick(256, 8, 1, 40, 256, sm)              # config 4 per rank: 8 row-tile pairs x 1 head
     assert c4 == 16
     assert pick(256, 64, 8, 40, 256, sm) == 2      # 32B at TP=1: 8 pairs x 8 KV heads = 64 CTAs
+    assert pick(256, 32, 4, 40, 256, sm) == 4      # 32 CTAs: 4 chunks = 128 CTAs, one wave
     assert 1 <= pick(512, 32, 8, 64, 256, 0) <= 16  # unknown SM count -> 148
     assert pick(0, 8, 1, 40, 256, sm) == 0 and pick(256, 8, 1, 0, 256, sm) == 0
 

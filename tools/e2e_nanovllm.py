@@ -155,6 +155,9 @@ def main():
     ap.add_argument("--max-out", type=int, default=1024)
     ap.add_argument("--fixed-in", type=int, default=0, help="every prompt has exactly this length")
     ap.add_argument("--fixed-out", type=int, default=0, help="every request decodes this many")
+    ap.add_argument("--shared-prefix", type=int, default=0,
+                    help="the first N tokens of every prompt are identical (prefix-cache hits: "
+                         "BlockManager hands every sequence the same leading block ids)")
     ap.add_argument("--max-model-len", type=int, default=4096)
     ap.add_argument("--max-batched", type=int, default=16384)
     ap.add_argument("--util", type=float, default=0.9)
@@ -204,6 +207,10 @@ def main():
     seed(0)
     prompts = [[randint(0, 10000) for _ in range(args.fixed_in or randint(100, args.max_in))]
                for _ in range(args.num_seqs)]
+    if args.shared_prefix:
+        head = [randint(0, 10000) for _ in range(args.shared_prefix)]
+        prompts = [head + p[args.shared_prefix:] for p in prompts]
+        assert all(len(p) > args.shared_prefix for p in prompts), "prompts must outgrow the prefix"
     sps = [SamplingParams(temperature=0.6, ignore_eos=True,
                           max_tokens=args.fixed_out or randint(100, args.max_out))
            for _ in range(args.num_seqs)]
@@ -240,6 +247,7 @@ def main():
         "tool": "e2e_nanovllm", "impl": args.impl, "model": f"Qwen3-{args.model} (random init)",
         "tp": args.tp, "num_seqs": args.num_seqs, "in": args.fixed_in or [100, args.max_in],
         "out": args.fixed_out or [100, args.max_out], "max_model_len": args.max_model_len,
+        "shared_prefix": args.shared_prefix, "cascade_env": os.environ.get("B200ATTN_CASCADE"),
         "cuda_graphs": not args.eager, "total_output_tokens": total, "seconds": t,
         "tokens_per_s": total / t, "init_s": t_init,
         "decode_tokens_per_s": phase["decode_tokens"] / max(phase["decode_s"], 1e-9),

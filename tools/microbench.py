@@ -159,6 +159,8 @@ def bench_sweep(out, quick):
 CASCADE_SHAPES = [  # (B, ctx, shared tokens, Hq, Hkv)  -- BASELINE config 4 per rank first
     (256, 8192, 7680, 8, 1), (256, 8192, 7680, 64, 8), (128, 4096, 3840, 32, 8),
     (64, 8192, 4096, 8, 1), (256, 8192, 0, 8, 1), (256, 2048, 1024, 16, 8),
+    (256, 8192, 7680, 16, 2), (256, 8192, 7680, 32, 4), (64, 4096, 2048, 32, 8),
+    (512, 2048, 1536, 32, 8), (32, 16384, 15360, 32, 8), (256, 1024, 512, 16, 8),
 ]
 
 
@@ -207,7 +209,7 @@ def bench_cascade(out, quick):
                    logical_bytes=logical, flops=flops, plain_us=p_med * 1e3,
                    plain_logical_gbs=logical / p_med / 1e6, plan_us=pl_med * 1e3)
         best = None
-        for chunks in sorted({max(auto, 1), 2, 4, 8, 16}):
+        for chunks in sorted({max(auto, 1), 1, 2, 3, 4, 5, 6, 8, 10, 12, 16, 24, 32}):
             c_min, c_med = timed(lambda: paged_decode(q, kc, vc, lens, bt, scale, out=o, plan=plan,
                                                       prefix_chunks=chunks))
             rec[f"cascade_us_c{chunks}"] = c_med * 1e3
