@@ -25,6 +25,8 @@
 #include "ptx.cuh"
 #include "tcgen05.cuh"
 
+#include <cstdlib>
+
 namespace b200 {
 
 namespace {
@@ -76,7 +78,9 @@ __device__ __forceinline__ void wait_bar(uint64_t* bar, uint32_t parity) {
 //   q [B, Hq, 128] lands in shared memory in exactly that order. Keys are the tiles of this
 //   chunk of the P shared pages (block ids from row b0's table), all visible: no masking. The
 //   epilogue writes normalised fp32 partials + log2-sum-exp for the decode merge.
-template <bool kCascade>
+// kEmu of every 4 exponential pairs are evaluated on the FMA pipe (tc::exp2_fma_pipe), the rest on
+// the MUFU.
+template <bool kCascade, int kEmu>
 __global__ void __launch_bounds__(kTcThreads, 1)
 prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
                   const __grid_constant__ CUtensorMap k_map,
@@ -356,8 +360,12 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
                     const int e = hh * 64 + 2 * t;
                     float2 x = make_float2(__uint_as_float(sr[e]), __uint_as_float(sr[e + 1]));
                     x = __ffma2_rn(x, c2, nmu2);
-                    x.x = fast_exp2(x.x);
-                    x.y = fast_exp2(x.y);
+                    if ((t & 3) < kEmu) {
+                        x = tc::exp2_fma_pipe(x);
+                    } else {
+                        x.x = fast_exp2(x.x);
+                        x.y = fast_exp2(x.y);
+                    }
                     ls[t & 1] = __fadd2_rn(ls[t & 1], x);
                     pr[t] = pack_bf16x2(x.x, x.y);
                 }
@@ -449,38 +457,66 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
 
 }  // namespace
 
-cudaError_t launch_prefill_tc(const PrefillParams& p, const CUtensorMap& q_map,
-                              const CUtensorMap& k_map, const CUtensorMap& v_map,
-                              cudaStream_t stream) {
+namespace {
+
+// B200ATTN_EXP_EMU=0..3 overrides how many of every 4 exponential pairs leave the MUFU.
+int exp_emu_from_env(int dflt) {
+    static int v = [] {
+        const char* e = std::getenv("B200ATTN_EXP_EMU");
+        return (e && e[0] >= '0' && e[0] <= '3') ? e[0] - '0' : -1;
+    }();
+    return v < 0 ? dflt : v;
+}
+
+template <bool kCascade, int kEmu>
+cudaError_t launch_tc(dim3 grid, const PrefillParams& p, const CUtensorMap& q_map,
+                      const CUtensorMap& k_map, const CUtensorMap& v_map, cudaStream_t stream) {
     static bool configured = false;
     if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(
-            prefill_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes);
+        cudaError_t e = cudaFuncSetAttribute(prefill_tc_kernel<kCascade, kEmu>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             kTcSmemBytes);
         if (e != cudaSuccess) return e;
         configured = true;
     }
-    const int pairs = (p.max_seqlen_q + 2 * kTM - 1) / (2 * kTM);
-    dim3 grid(pairs, p.num_q_heads, p.num_seqs);
-    prefill_tc_kernel<false><<<grid, kTcThreads, kTcSmemBytes, stream>>>(q_map, k_map, v_map, p);
+    prefill_tc_kernel<kCascade, kEmu><<<grid, kTcThreads, kTcSmemBytes, stream>>>(q_map, k_map,
+                                                                                  v_map, p);
     count_launch();
     return cudaGetLastError();
+}
+
+template <bool kCascade>
+cudaError_t launch_tc_emu(int emu, dim3 grid, const PrefillParams& p, const CUtensorMap& q_map,
+                          const CUtensorMap& k_map, const CUtensorMap& v_map,
+                          cudaStream_t stream) {
+    switch (emu) {
+        case 0: return launch_tc<kCascade, 0>(grid, p, q_map, k_map, v_map, stream);
+        case 1: return launch_tc<kCascade, 1>(grid, p, q_map, k_map, v_map, stream);
+        case 3: return launch_tc<kCascade, 3>(grid, p, q_map, k_map, v_map, stream);
+        default: return launch_tc<kCascade, 2>(grid, p, q_map, k_map, v_map, stream);
+    }
+}
+
+}  // namespace
+
+constexpr int kDefaultExpEmu = 0;
+
+cudaError_t launch_prefill_tc(const PrefillParams& p, const CUtensorMap& q_map,
+                              const CUtensorMap& k_map, const CUtensorMap& v_map,
+                              cudaStream_t stream) {
+    const int pairs = (p.max_seqlen_q + 2 * kTM - 1) / (2 * kTM);
+    dim3 grid(pairs, p.num_q_heads, p.num_seqs);
+    return launch_tc_emu<false>(exp_emu_from_env(kDefaultExpEmu), grid, p, q_map, k_map, v_map,
+                                stream);
 }
 
 cudaError_t launch_cascade_prefix(const PrefillParams& p, const CUtensorMap& q_map,
                                   const CUtensorMap& k_map, const CUtensorMap& v_map,
                                   cudaStream_t stream) {
-    static bool configured = false;
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(
-            prefill_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes);
-        if (e != cudaSuccess) return e;
-        configured = true;
-    }
     const int rows = p.batch * p.group;  // query rows per KV head
     dim3 grid((rows + 2 * kTM - 1) / (2 * kTM), p.prefix_chunks, p.num_kv_heads);
-    prefill_tc_kernel<true><<<grid, kTcThreads, kTcSmemBytes, stream>>>(q_map, k_map, v_map, p);
-    count_launch();
-    return cudaGetLastError();
+    return launch_tc_emu<true>(exp_emu_from_env(kDefaultExpEmu), grid, p, q_map, k_map, v_map,
+                               stream);
 }
 
 }  // namespace b200

@@ -167,6 +167,36 @@ template <int N>
 __device__ __forceinline__ void reg_dec() {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N));
 }
+// 2^x for a pair of fp32 values WITHOUT the MUFU: Cody-Waite split x = floor(x) + f, a cubic for
+// 2^f on [0, 1) (max relative error ~1e-4, far below the bf16 rounding P gets anyway), and the
+// integer part added straight into the exponent field. The round-down add against 1.5 * 2^23
+// leaves floor(x) in the low mantissa bits of `xr`, so (bits(xr) << 23) is floor(x) << 23.
+// The softmax of the tcgen05 prefill is MUFU-bound (16 ex2/clk/SM against 8192 MMA flop/clk/SM);
+// moving a fraction of the exponentials to the FMA pipe takes the MUFU off the critical path.
+// x must be <= 127; values below -127 are clamped (result ~2^-127, i.e. 0 after bf16 rounding).
+__device__ __forceinline__ float2 exp2_fma_pipe(float2 x) {
+    const float kMagic = 12582912.f;  // 2^23 + 2^22
+    x.x = fmaxf(x.x, -127.f);
+    x.y = fmaxf(x.y, -127.f);
+    float2 xr;
+    asm("{\n\t.reg .b64 ra, rb, rd;\n\t"
+        "mov.b64 ra, {%2, %3};\n\tmov.b64 rb, {%4, %4};\n\t"
+        "add.rm.ftz.f32x2 rd, ra, rb;\n\t"
+        "mov.b64 {%0, %1}, rd;\n\t}"
+        : "=f"(xr.x), "=f"(xr.y)
+        : "f"(x.x), "f"(x.y), "f"(kMagic));
+    const float2 fl = __fadd2_rn(xr, make_float2(-kMagic, -kMagic));     // floor(x), exact
+    const float2 f = __ffma2_rn(fl, make_float2(-1.f, -1.f), x);         // x - floor(x) in [0, 1)
+    float2 p = __ffma2_rn(make_float2(0.077119089663028717f, 0.077119089663028717f), f,
+                          make_float2(0.227564394474029541f, 0.227564394474029541f));
+    p = __ffma2_rn(p, f, make_float2(0.695146143436431885f, 0.695146143436431885f));
+    p = __ffma2_rn(p, f, make_float2(1.f, 1.f));
+    float2 r;
+    r.x = __int_as_float(__float_as_int(p.x) + (__float_as_int(xr.x) << 23));
+    r.y = __int_as_float(__float_as_int(p.y) + (__float_as_int(xr.y) << 23));
+    return r;
+}
+
 __device__ __forceinline__ float fmax3(float a, float b, float c) {
     float d;
     asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
