@@ -458,12 +458,16 @@ int b200attn_prefill_varlen(const void* q, const void* key, int64_t key_row_stri
     p.group = num_q_heads / num_kv_heads;
     p.block_size = block_size;
     p.scale_log2 = scale * 1.4426950408889634f;
-    // Kernel choice from host-visible sizes only. The tcgen05 kernel works on 256-row query
-    // tile pairs and 128-token KV tiles: it needs pages that are multiples of 128 tokens.
+    // Kernel choice from host-visible sizes only. The tcgen05 kernel works on pairs of 128-row
+    // tiles of (token, group head) rows and 128-token KV tiles: it needs pages that are multiples
+    // of 128 tokens and a GQA group that divides 128.
     const int mode = prefill_mode_from_env();
-    const bool tc_ok = scale > 0.f && (!paged || block_size % 128 == 0) &&
+    const int group = num_q_heads / num_kv_heads;
+    const bool tc_ok = scale > 0.f && (!paged || block_size % 128 == 0) && 128 % group == 0 &&
                        static_cast<int64_t>(num_blocks) * block_size < (1LL << 31);
-    bool use_tc = tc_ok && max_seqlen_q >= 256;
+    // With GQA-packed rows the tcgen05 kernel wins at every measured shape, short query blocks
+    // included (profiles/r01_microbench_prefill_v4.log); mma.sync is the shape fallback only.
+    bool use_tc = tc_ok;
     if (mode == 1) {
         if (!tc_ok) return fail(B200ATTN_E_UNSUPPORTED, "B200ATTN_PREFILL=tc: shape unsupported");
         use_tc = true;
@@ -473,8 +477,10 @@ int b200attn_prefill_varlen(const void* q, const void* key, int64_t key_row_stri
     cudaError_t e;
     if (use_tc) {
         CUtensorMap q_map, k_map, v_map;
+        // GQA-packed query tiles: box = 64 dims x G heads x 128/G tokens
         if (int rc = encode_rows_map(q, num_q_heads, total_q,
-                                     static_cast<int64_t>(num_q_heads) * head_dim, 128, &q_map))
+                                     static_cast<int64_t>(num_q_heads) * head_dim, 128 / group,
+                                     &q_map, group))
             return rc;
         if (paged) {
             const int64_t num_slots = num_blocks * block_size;

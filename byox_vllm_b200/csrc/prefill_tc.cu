@@ -71,7 +71,8 @@ __device__ __forceinline__ void wait_bar(uint64_t* bar, uint32_t parity) {
     }
 }
 
-// kCascade = false: varlen causal prefill, CTA = (query-row pair, q-head, sequence).
+// kCascade = false: varlen causal prefill, CTA = (pair of 128-row tiles, KV head, sequence);
+//   a tile row is (query token r / G, group head r % G).
 // kCascade = true:  shared-prefix pass of the cascade decode (cascade.cu). CTA = (pair of 128-row
 //   tiles of the B*G query rows of one KV head, prefix chunk, KV head). A tile row r is
 //   (batch row r / G, group head r % G): the TMA box 64 dims x G heads x 128/G batch rows of
@@ -111,27 +112,32 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
         }
         q_c1 = kvh * p.group;
     } else {
+        // GQA packing: a 128-row sub-tile = 128/G query tokens x the G heads of one KV head
+        // (row r = token r / G, head r % G; one TMA box 64 dims x G heads x 128/G tokens), so a
+        // K/V tile is loaded once per KV head and short query blocks still fill the tile.
         seq = blockIdx.z;
-        h = blockIdx.y;
+        kvh = blockIdx.y;
         q_begin = p.cu_seqlens_q[seq];
         Lq = p.cu_seqlens_q[seq + 1] - q_begin;
         k_begin = p.cu_seqlens_k[seq];
         Lk = p.cu_seqlens_k[seq + 1] - k_begin;
-        const int n_pairs = (Lq + 2 * kTM - 1) / (2 * kTM);
+        const int toks_per_sub = kTM / p.group;
+        const int n_pairs = (Lq + 2 * toks_per_sub - 1) / (2 * toks_per_sub);
         if (static_cast<int>(blockIdx.x) >= n_pairs) return;  // uniform for the whole CTA
-        const int pair = n_pairs - 1 - blockIdx.x;            // heaviest (last) rows first
-        offset = Lk - Lq;                                     // row i sees keys j <= i + offset
-        kvh = h / p.group;
+        const int pair = n_pairs - 1 - blockIdx.x;            // heaviest (last) tokens first
+        offset = Lk - Lq;                                     // token i sees keys j <= i + offset
 #pragma unroll
         for (int i = 0; i < 2; ++i) {
-            row0[i] = pair * 2 * kTM + i * kTM;
-            const int rows_end = min(Lq, row0[i] + kTM);
-            const int vis = row0[i] < Lq ? min(Lk, rows_end + offset) : 0;  // visible keys [0, vis)
+            row0[i] = (pair * 2 + i) * toks_per_sub;          // first query token of the sub-tile
+            const int toks_end = min(Lq, row0[i] + toks_per_sub);
+            const int vis = row0[i] < Lq ? min(Lk, toks_end + offset) : 0;  // visible keys [0, vis)
             n_kv[i] = vis > 0 ? (vis + kTN - 1) / kTN : 0;
             q_c2[i] = q_begin + row0[i];
         }
-        q_c1 = h;
+        q_c1 = kvh * p.group;
     }
+    const int g_shift = __ffs(p.group) - 1;  // G is a power of two (128 % G == 0)
+    (void)h;
     const int n_max = max(n_kv[0], n_kv[1]);
 
     extern __shared__ uint8_t smem_raw[];
@@ -297,7 +303,8 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
         const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
         const uint32_t s_tmem = tmem + lane_base + i * kTN;
         const uint32_t o_tmem = tmem + lane_base + 2 * kTN + i * kHeadDim;
-        const int row = row0[i] + r;                   // row inside the sequence
+        const int row = row0[i] + (r >> g_shift);      // query token (cascade: batch row)
+        const int head = kvh * p.group + (r & (p.group - 1));
         const int n = n_kv[i];
         const float c = p.scale_log2;
         float m_ref = -INFINITY;  // scaled (log2-domain) reference maximum of this row
@@ -379,12 +386,12 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
 
         if constexpr (kCascade) {
             // ---- epilogue: normalised fp32 partial + log2-sum-exp of this prefix chunk ----
-            const int b = row0[i] + r / p.group;
+            const int b = row;
             if (n > 0) {  // warp-uniform: n depends on the sub-tile only
                 wait_bar(&bar->o_full[i], 0);
                 tc::fence_after_sync();
                 const int64_t qrow =
-                    static_cast<int64_t>(b) * p.num_q_heads + kvh * p.group + r % p.group;
+                    static_cast<int64_t>(b) * p.num_q_heads + head;
                 const int64_t slot = qrow * p.ws_slots + p.ws_slot0 + chunk;
                 const float inv = l > 0.f ? 1.f / l : 0.f;
                 float* og = p.ws_o + slot * kHeadDim;
@@ -410,7 +417,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
         // ---- epilogue: O / l -> bf16 -> global (row-predicated 16-byte stores) ----
         const bool row_ok = row < Lq;
         uint8_t* orow_g = static_cast<uint8_t*>(p.out) +
-                          ((static_cast<int64_t>(q_begin) + row) * p.num_q_heads + h) * 256;
+                          ((static_cast<int64_t>(q_begin) + row) * p.num_q_heads + head) * 256;
         if (n > 0) {
             wait_bar(&bar->o_full[i], 0);
             tc::fence_after_sync();
@@ -504,8 +511,8 @@ constexpr int kDefaultExpEmu = 0;
 cudaError_t launch_prefill_tc(const PrefillParams& p, const CUtensorMap& q_map,
                               const CUtensorMap& k_map, const CUtensorMap& v_map,
                               cudaStream_t stream) {
-    const int pairs = (p.max_seqlen_q + 2 * kTM - 1) / (2 * kTM);
-    dim3 grid(pairs, p.num_q_heads, p.num_seqs);
+    const int rows = p.max_seqlen_q * p.group;  // query rows per KV head of the longest sequence
+    dim3 grid((rows + 2 * kTM - 1) / (2 * kTM), p.num_kv_heads, p.num_seqs);
     return launch_tc_emu<false>(exp_emu_from_env(kDefaultExpEmu), grid, p, q_map, k_map, v_map,
                                 stream);
 }

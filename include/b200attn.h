@@ -171,8 +171,9 @@ int b200attn_store_decode_cascade(const void* q, const void* key, int64_t key_ro
  *          b200attn_decode; key/value ignored.
  *   q [total_q, num_q_heads, head_dim] contiguous; out same. Rows with no visible key get zeros.
  *   total_k = number of rows of key/value (dense; bounds the TMA tensor map), ignored when paged.
- * Kernel choice depends on host-visible sizes only: sequences of >= 256 query rows run on the
- * tcgen05/TMEM kernel, shorter batches on the mma.sync kernel (B200ATTN_PREFILL=tc|mma forces one).
+ * Kernel choice depends on host-visible sizes only: the tcgen05/TMEM kernel (rows = query token x
+ * GQA group head) whenever pages are multiples of 128 tokens and the group divides 128, else the
+ * mma.sync kernel (B200ATTN_PREFILL=tc|mma forces one).
  */
 int b200attn_prefill_varlen(const void* q, const void* key, int64_t key_row_stride,
                             const void* value, int64_t value_row_stride, const void* k_cache,

@@ -296,6 +296,14 @@ PREFILL_SHAPES = [  # (lens list spec, cached, Hq, Hkv)
     ("16x1024", [1024] * 16, None, 16, 8), ("1x16384", [16384], None, 32, 8),
     ("2x8192", [8192] * 2, None, 8, 1), ("bench24", None, None, 16, 8),
     ("32x(7680+512)", [8192] * 32, [7680] * 32, 8, 1), ("8x(3840+256)", [4096] * 8, [3840] * 8, 32, 8),
+    # short query blocks (max_seqlen_q < 256): remainders behind a cached prefix, short prompts
+    ("short32x(1024+100)", [1124] * 32, [1024] * 32, 16, 8), ("short64x128", [128] * 64, None, 16, 8),
+    ("short16x(2048+200)", [2248] * 16, [2048] * 16, 32, 8), ("short64x(256+60)", [316] * 64, [256] * 64, 16, 8),
+    ("short128x200", [200] * 128, None, 16, 8),
+    ("short64x(512+100)", [612] * 64, [512] * 64, 16, 8), ("short64x(512+60)", [572] * 64, [512] * 64, 16, 8),
+    ("short64x(1024+30)", [1054] * 64, [1024] * 64, 16, 8), ("short128x(512+16)", [528] * 128, [512] * 128, 32, 8),
+    ("short32x(768+150)", [918] * 32, [768] * 32, 32, 8), ("short256x(256+20)", [276] * 256, [256] * 256, 16, 8),
+    ("short64x160", [160] * 64, None, 32, 8), ("short8x100", [100] * 8, None, 16, 8),
 ]
 
 
