@@ -4,6 +4,8 @@
 #include "../../include/b200attn.h"
 #include "common.h"
 
+#include <cuda_bf16.h>
+
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -157,6 +159,149 @@ int check_attn_shape(int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim
 
 }  // namespace
 
+// Shared body of every decode entry point. `nr` != nullptr: q / key are raw QKV-projection rows
+// (q rows q_row_stride elements apart) and the kernel applies q/k RMSNorm + RoPE itself.
+static int store_decode_impl(const void* q, int64_t q_row_stride, const void* key,
+                             int64_t key_row_stride, const void* value, int64_t value_row_stride,
+                             const int32_t* slot_mapping, void* k_cache, void* v_cache,
+                             const int32_t* block_tables, int64_t table_row_stride,
+                             int32_t table_width, const int32_t* context_lens, void* out,
+                             void* workspace, size_t workspace_bytes, int32_t batch,
+                             int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim,
+                             int32_t block_size, int64_t num_blocks, float scale,
+                             int32_t num_splits, const int32_t* plan, int32_t prefix_chunks,
+                             int32_t dtype, void* stream, const b200::NormRopeArgs* nr) {
+    if (int rc = check_attn_shape(num_q_heads, num_kv_heads, head_dim, block_size, dtype)) return rc;
+    if (prefix_chunks < 0 || prefix_chunks > 32 || (prefix_chunks > 0) != (plan != nullptr))
+        return fail(B200ATTN_E_BADARG, "plan and prefix_chunks (0..32) must be given together");
+    if (nr && prefix_chunks > 0)
+        return fail(B200ATTN_E_UNSUPPORTED,
+                    "qkv_decode cannot be combined with the cascade (run qk_norm_rope_store first)");
+    if (prefix_chunks > 0 && (block_size % 128 != 0 || 128 % (num_q_heads / num_kv_heads) != 0))
+        return fail(B200ATTN_E_UNSUPPORTED,
+                    "cascade needs block_size %% 128 == 0 and a GQA group dividing 128");
+    if (batch < 0 || num_blocks <= 0 || table_width < 0 || num_splits < 1)
+        return fail(B200ATTN_E_BADARG, "negative or zero size");
+    if (batch == 0) return 0;
+    if (batch > 65535) return fail(B200ATTN_E_UNSUPPORTED, "batch %d > 65535", batch);
+    if (num_splits > 64) return fail(B200ATTN_E_UNSUPPORTED, "num_splits %d > 64", num_splits);
+    if (!q || !k_cache || !v_cache || !block_tables || !context_lens || !out)
+        return fail(B200ATTN_E_BADARG, "null pointer");
+    if (!std::isfinite(scale)) return fail(B200ATTN_E_BADARG, "scale is not finite");
+    const int64_t num_slots = num_blocks * block_size;
+    if (num_slots >= (1LL << 31))
+        return fail(B200ATTN_E_UNSUPPORTED, "cache of %lld slots exceeds int32 TMA coordinates",
+                    static_cast<long long>(num_slots));
+    if (!aligned16(q) || !aligned16(out) || !aligned16(k_cache) || !aligned16(v_cache))
+        return fail(B200ATTN_E_BADARG, "pointers must be 16-byte aligned");
+    const int32_t ws_slots = num_splits + prefix_chunks;
+    if (ws_slots > 1) {
+        const size_t need = b200::decode_workspace_bytes(batch, num_q_heads, ws_slots);
+        if (!workspace || workspace_bytes < need || !aligned16(workspace))
+            return fail(B200ATTN_E_WORKSPACE,
+                        "workspace %zu B < %zu B needed for %d splits + %d prefix chunks",
+                        workspace_bytes, need, num_splits, prefix_chunks);
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const bool with_store = key || value || slot_mapping;
+    // One launch: the decode kernel scatters the new rows itself (B200ATTN_FUSED_STORE=0 keeps the
+    // two-launch sequence for A/B runs).
+    static const bool fused_store = [] {
+        const char* e = std::getenv("B200ATTN_FUSED_STORE");
+        return !(e && e[0] == '0');
+    }();
+    if (with_store) {
+        if (!key || !value || !slot_mapping)
+            return fail(B200ATTN_E_BADARG, "store_decode needs key, value and slot_mapping");
+        if (key_row_stride % 8 != 0 || value_row_stride % 8 != 0 || !aligned16(key) ||
+            !aligned16(value))
+            return fail(B200ATTN_E_UNSUPPORTED, "key/value rows must be 16-byte aligned");
+        if (key_row_stride < num_kv_heads * head_dim || value_row_stride < num_kv_heads * head_dim)
+            return fail(B200ATTN_E_BADARG, "row stride smaller than the row");
+        if (nr && !fused_store)
+            return fail(B200ATTN_E_UNSUPPORTED, "qkv_decode needs the fused store");
+        if (!fused_store) {
+            if (int rc = b200attn_store_kvcache(key, key_row_stride, value, value_row_stride,
+                                                k_cache, v_cache, slot_mapping, batch,
+                                                num_kv_heads * head_dim, num_slots, dtype, stream))
+                return rc;
+        }
+    }
+    CUtensorMap k_map, v_map;
+    if (int rc = get_cache_map(k_cache, num_kv_heads, num_slots, 64, &k_map)) return rc;
+    if (int rc = get_cache_map(v_cache, num_kv_heads, num_slots, 64, &v_map)) return rc;
+
+    b200::DecodeParams p{};
+    p.q = q;
+    p.q_row_stride = q_row_stride;
+    if (nr) p.nr = *nr;
+    p.out = out;
+    p.block_tables = block_tables;
+    p.context_lens = context_lens;
+    p.table_row_stride = table_row_stride;
+    p.table_width = table_width;
+    p.batch = batch;
+    p.num_q_heads = num_q_heads;
+    p.num_kv_heads = num_kv_heads;
+    p.group = num_q_heads / num_kv_heads;
+    p.block_size = block_size;
+    p.num_splits = num_splits;
+    p.scale_log2 = scale * 1.4426950408889634f;
+    if (with_store && fused_store) {
+        p.new_key = key;
+        p.new_value = value;
+        p.slot_mapping = slot_mapping;
+        p.k_cache = k_cache;
+        p.v_cache = v_cache;
+        p.key_row_stride = key_row_stride;
+        p.value_row_stride = value_row_stride;
+        p.num_slots = num_slots;
+    }
+    if (ws_slots > 1) {
+        p.ws_o = static_cast<float*>(workspace);
+        p.ws_lse = p.ws_o + static_cast<size_t>(batch) * num_q_heads * ws_slots * b200::kHeadDim;
+    }
+    p.plan = plan;
+    p.prefix_chunks = prefix_chunks;
+    if (prefix_chunks > 0) {
+        // Shared-prefix pass first (tcgen05): B*G query rows of every KV head against the P
+        // shared pages, partials into workspace slots [num_splits, num_splits + prefix_chunks).
+        // It never touches the slot the fused scatter writes (that token lies after the prefix).
+        const int group = num_q_heads / num_kv_heads;
+        CUtensorMap q_map, k_map128, v_map128;
+        if (int rc = encode_rows_map(q, num_q_heads, batch,
+                                     static_cast<int64_t>(num_q_heads) * head_dim, 128 / group,
+                                     &q_map, group))
+            return rc;
+        if (int rc = get_cache_map(k_cache, num_kv_heads, num_slots, 128, &k_map128)) return rc;
+        if (int rc = get_cache_map(v_cache, num_kv_heads, num_slots, 128, &v_map128)) return rc;
+        b200::PrefillParams pp{};
+        pp.q = q;
+        pp.k_cache = k_cache;
+        pp.v_cache = v_cache;
+        pp.block_tables = block_tables;
+        pp.table_row_stride = table_row_stride;
+        pp.table_width = table_width;
+        pp.num_q_heads = num_q_heads;
+        pp.num_kv_heads = num_kv_heads;
+        pp.group = group;
+        pp.block_size = block_size;
+        pp.scale_log2 = p.scale_log2;
+        pp.plan = plan;
+        pp.ws_o = p.ws_o;
+        pp.ws_lse = p.ws_lse;
+        pp.batch = batch;
+        pp.prefix_chunks = prefix_chunks;
+        pp.ws_slot0 = num_splits;
+        pp.ws_slots = ws_slots;
+        cudaError_t e0 = b200::launch_cascade_prefix(pp, q_map, k_map128, v_map128, st);
+        if (e0 != cudaSuccess) return cuda_fail(e0, "cascade prefix launch");
+    }
+    cudaError_t e = b200::launch_decode(p, k_map, v_map, st);
+    return e == cudaSuccess ? 0 : cuda_fail(e, "decode launch");
+}
+
+
 extern "C" {
 
 int b200attn_abi_version(void) { return B200ATTN_ABI_VERSION; }
@@ -262,127 +407,12 @@ int b200attn_store_decode_cascade(const void* q, const void* key, int64_t key_ro
                                   int32_t block_size, int64_t num_blocks, float scale,
                                   int32_t num_splits, const int32_t* plan, int32_t prefix_chunks,
                                   int32_t dtype, void* stream) {
-    if (int rc = check_attn_shape(num_q_heads, num_kv_heads, head_dim, block_size, dtype)) return rc;
-    if (prefix_chunks < 0 || prefix_chunks > 32 || (prefix_chunks > 0) != (plan != nullptr))
-        return fail(B200ATTN_E_BADARG, "plan and prefix_chunks (0..32) must be given together");
-    if (prefix_chunks > 0 && (block_size % 128 != 0 || 128 % (num_q_heads / num_kv_heads) != 0))
-        return fail(B200ATTN_E_UNSUPPORTED,
-                    "cascade needs block_size %% 128 == 0 and a GQA group dividing 128");
-    if (batch < 0 || num_blocks <= 0 || table_width < 0 || num_splits < 1)
-        return fail(B200ATTN_E_BADARG, "negative or zero size");
-    if (batch == 0) return 0;
-    if (batch > 65535) return fail(B200ATTN_E_UNSUPPORTED, "batch %d > 65535", batch);
-    if (num_splits > 64) return fail(B200ATTN_E_UNSUPPORTED, "num_splits %d > 64", num_splits);
-    if (!q || !k_cache || !v_cache || !block_tables || !context_lens || !out)
-        return fail(B200ATTN_E_BADARG, "null pointer");
-    if (!std::isfinite(scale)) return fail(B200ATTN_E_BADARG, "scale is not finite");
-    const int64_t num_slots = num_blocks * block_size;
-    if (num_slots >= (1LL << 31))
-        return fail(B200ATTN_E_UNSUPPORTED, "cache of %lld slots exceeds int32 TMA coordinates",
-                    static_cast<long long>(num_slots));
-    if (!aligned16(q) || !aligned16(out) || !aligned16(k_cache) || !aligned16(v_cache))
-        return fail(B200ATTN_E_BADARG, "pointers must be 16-byte aligned");
-    const int32_t ws_slots = num_splits + prefix_chunks;
-    if (ws_slots > 1) {
-        const size_t need = b200::decode_workspace_bytes(batch, num_q_heads, ws_slots);
-        if (!workspace || workspace_bytes < need || !aligned16(workspace))
-            return fail(B200ATTN_E_WORKSPACE,
-                        "workspace %zu B < %zu B needed for %d splits + %d prefix chunks",
-                        workspace_bytes, need, num_splits, prefix_chunks);
-    }
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
-    const bool with_store = key || value || slot_mapping;
-    // One launch: the decode kernel scatters the new rows itself (B200ATTN_FUSED_STORE=0 keeps the
-    // two-launch sequence for A/B runs).
-    static const bool fused_store = [] {
-        const char* e = std::getenv("B200ATTN_FUSED_STORE");
-        return !(e && e[0] == '0');
-    }();
-    if (with_store) {
-        if (!key || !value || !slot_mapping)
-            return fail(B200ATTN_E_BADARG, "store_decode needs key, value and slot_mapping");
-        if (key_row_stride % 8 != 0 || value_row_stride % 8 != 0 || !aligned16(key) ||
-            !aligned16(value))
-            return fail(B200ATTN_E_UNSUPPORTED, "key/value rows must be 16-byte aligned");
-        if (key_row_stride < num_kv_heads * head_dim || value_row_stride < num_kv_heads * head_dim)
-            return fail(B200ATTN_E_BADARG, "row stride smaller than the row");
-        if (!fused_store) {
-            if (int rc = b200attn_store_kvcache(key, key_row_stride, value, value_row_stride,
-                                                k_cache, v_cache, slot_mapping, batch,
-                                                num_kv_heads * head_dim, num_slots, dtype, stream))
-                return rc;
-        }
-    }
-    CUtensorMap k_map, v_map;
-    if (int rc = get_cache_map(k_cache, num_kv_heads, num_slots, 64, &k_map)) return rc;
-    if (int rc = get_cache_map(v_cache, num_kv_heads, num_slots, 64, &v_map)) return rc;
-
-    b200::DecodeParams p{};
-    p.q = q;
-    p.out = out;
-    p.block_tables = block_tables;
-    p.context_lens = context_lens;
-    p.table_row_stride = table_row_stride;
-    p.table_width = table_width;
-    p.batch = batch;
-    p.num_q_heads = num_q_heads;
-    p.num_kv_heads = num_kv_heads;
-    p.group = num_q_heads / num_kv_heads;
-    p.block_size = block_size;
-    p.num_splits = num_splits;
-    p.scale_log2 = scale * 1.4426950408889634f;
-    if (with_store && fused_store) {
-        p.new_key = key;
-        p.new_value = value;
-        p.slot_mapping = slot_mapping;
-        p.k_cache = k_cache;
-        p.v_cache = v_cache;
-        p.key_row_stride = key_row_stride;
-        p.value_row_stride = value_row_stride;
-        p.num_slots = num_slots;
-    }
-    if (ws_slots > 1) {
-        p.ws_o = static_cast<float*>(workspace);
-        p.ws_lse = p.ws_o + static_cast<size_t>(batch) * num_q_heads * ws_slots * b200::kHeadDim;
-    }
-    p.plan = plan;
-    p.prefix_chunks = prefix_chunks;
-    if (prefix_chunks > 0) {
-        // Shared-prefix pass first (tcgen05): B*G query rows of every KV head against the P
-        // shared pages, partials into workspace slots [num_splits, num_splits + prefix_chunks).
-        // It never touches the slot the fused scatter writes (that token lies after the prefix).
-        const int group = num_q_heads / num_kv_heads;
-        CUtensorMap q_map, k_map128, v_map128;
-        if (int rc = encode_rows_map(q, num_q_heads, batch,
-                                     static_cast<int64_t>(num_q_heads) * head_dim, 128 / group,
-                                     &q_map, group))
-            return rc;
-        if (int rc = get_cache_map(k_cache, num_kv_heads, num_slots, 128, &k_map128)) return rc;
-        if (int rc = get_cache_map(v_cache, num_kv_heads, num_slots, 128, &v_map128)) return rc;
-        b200::PrefillParams pp{};
-        pp.q = q;
-        pp.k_cache = k_cache;
-        pp.v_cache = v_cache;
-        pp.block_tables = block_tables;
-        pp.table_row_stride = table_row_stride;
-        pp.table_width = table_width;
-        pp.num_q_heads = num_q_heads;
-        pp.num_kv_heads = num_kv_heads;
-        pp.group = group;
-        pp.block_size = block_size;
-        pp.scale_log2 = p.scale_log2;
-        pp.plan = plan;
-        pp.ws_o = p.ws_o;
-        pp.ws_lse = p.ws_lse;
-        pp.batch = batch;
-        pp.prefix_chunks = prefix_chunks;
-        pp.ws_slot0 = num_splits;
-        pp.ws_slots = ws_slots;
-        cudaError_t e0 = b200::launch_cascade_prefix(pp, q_map, k_map128, v_map128, st);
-        if (e0 != cudaSuccess) return cuda_fail(e0, "cascade prefix launch");
-    }
-    cudaError_t e = b200::launch_decode(p, k_map, v_map, st);
-    return e == cudaSuccess ? 0 : cuda_fail(e, "decode launch");
+    return store_decode_impl(q, static_cast<int64_t>(num_q_heads) * head_dim, key, key_row_stride,
+                             value, value_row_stride, slot_mapping, k_cache, v_cache, block_tables,
+                             table_row_stride, table_width, context_lens, out, workspace,
+                             workspace_bytes, batch, num_q_heads, num_kv_heads, head_dim,
+                             block_size, num_blocks, scale, num_splits, plan, prefix_chunks, dtype,
+                             stream, nullptr);
 }
 
 int b200attn_decode(const void* q, const void* k_cache, const void* v_cache,
@@ -498,6 +528,104 @@ int b200attn_prefill_varlen(const void* q, const void* key, int64_t key_row_stri
         e = b200::launch_prefill(p, static_cast<cudaStream_t>(stream));
     }
     return e == cudaSuccess ? 0 : cuda_fail(e, "prefill launch");
+}
+
+// Validates the q/k-norm + RoPE arguments shared by the two fused entry points.
+static int check_norm_rope(const int64_t* positions, const void* q_weight, const void* k_weight,
+                           float eps, const float* cos_sin_cache, int32_t max_position,
+                           b200::NormRopeArgs* out) {
+    if (!positions || !cos_sin_cache) return fail(B200ATTN_E_BADARG, "null positions/cos_sin_cache");
+    if ((q_weight == nullptr) != (k_weight == nullptr))
+        return fail(B200ATTN_E_BADARG, "q_norm_weight and k_norm_weight must be given together");
+    if (max_position <= 0) return fail(B200ATTN_E_BADARG, "max_position must be positive");
+    if (!(eps >= 0.f) || !std::isfinite(eps)) return fail(B200ATTN_E_BADARG, "bad eps");
+    if (!aligned16(cos_sin_cache) || (q_weight && (!aligned16(q_weight) || !aligned16(k_weight))))
+        return fail(B200ATTN_E_BADARG, "weights / cos_sin_cache must be 16-byte aligned");
+    out->positions = positions;
+    out->q_weight = q_weight;
+    out->k_weight = k_weight;
+    out->cos_sin = cos_sin_cache;
+    out->max_position = max_position;
+    out->eps = eps;
+    return 0;
+}
+
+int b200attn_qk_norm_rope_store(const void* qkv, int64_t qkv_row_stride, const int64_t* positions,
+                                const void* q_norm_weight, const void* k_norm_weight, float eps,
+                                const float* cos_sin_cache, int32_t max_position, void* q_out,
+                                void* k_out, int64_t k_out_row_stride, void* k_cache,
+                                void* v_cache, const int32_t* slot_mapping, int32_t n_tokens,
+                                int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim,
+                                int64_t num_slots, int32_t dtype, void* stream) {
+    if (dtype != B200ATTN_DTYPE_BF16)
+        return fail(B200ATTN_E_UNSUPPORTED, "dtype %d unsupported (bf16 only)", dtype);
+    if (head_dim != b200::kHeadDim)
+        return fail(B200ATTN_E_UNSUPPORTED, "head_dim %d unsupported (128 only)", head_dim);
+    if (n_tokens < 0 || num_q_heads <= 0 || num_kv_heads <= 0 || num_slots < 0)
+        return fail(B200ATTN_E_BADARG, "negative or zero size");
+    if (n_tokens == 0) return 0;
+    b200::QkNormRopeParams p{};
+    if (int rc = check_norm_rope(positions, q_norm_weight, k_norm_weight, eps, cos_sin_cache,
+                                 max_position, &p.nr))
+        return rc;
+    if (!qkv || !q_out) return fail(B200ATTN_E_BADARG, "null qkv/q_out");
+    const int64_t row = static_cast<int64_t>(num_q_heads + 2 * num_kv_heads) * head_dim;
+    if (qkv_row_stride < row || qkv_row_stride % 8 != 0)
+        return fail(B200ATTN_E_BADARG, "qkv_row_stride %lld < row of %lld elements or not 16-byte",
+                    static_cast<long long>(qkv_row_stride), static_cast<long long>(row));
+    if (k_out && (k_out_row_stride < num_kv_heads * head_dim || k_out_row_stride % 8 != 0))
+        return fail(B200ATTN_E_BADARG, "bad k_out_row_stride");
+    if (slot_mapping && (!k_cache || !v_cache))
+        return fail(B200ATTN_E_BADARG, "slot_mapping given without caches");
+    if (!aligned16(qkv) || !aligned16(q_out) || !aligned16(k_out) || !aligned16(k_cache) ||
+        !aligned16(v_cache))
+        return fail(B200ATTN_E_BADARG, "pointers must be 16-byte aligned");
+    p.qkv = qkv;
+    p.qkv_row_stride = qkv_row_stride;
+    p.q_out = q_out;
+    p.k_out = k_out;
+    p.k_out_row_stride = k_out_row_stride;
+    p.k_cache = k_cache;
+    p.v_cache = v_cache;
+    p.slot_mapping = slot_mapping;
+    p.num_slots = num_slots;
+    p.n_tokens = n_tokens;
+    p.num_q_heads = num_q_heads;
+    p.num_kv_heads = num_kv_heads;
+    cudaError_t e = b200::launch_qk_norm_rope_store(p, static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? 0 : cuda_fail(e, "qk_norm_rope_store launch");
+}
+
+int b200attn_qkv_decode(const void* qkv, int64_t qkv_row_stride, const int64_t* positions,
+                        const void* q_norm_weight, const void* k_norm_weight, float eps,
+                        const float* cos_sin_cache, int32_t max_position,
+                        const int32_t* slot_mapping, void* k_cache, void* v_cache,
+                        const int32_t* block_tables, int64_t table_row_stride, int32_t table_width,
+                        const int32_t* context_lens, void* out, void* workspace,
+                        size_t workspace_bytes, int32_t batch, int32_t num_q_heads,
+                        int32_t num_kv_heads, int32_t head_dim, int32_t block_size,
+                        int64_t num_blocks, float scale, int32_t num_splits, int32_t dtype,
+                        void* stream) {
+    if (batch == 0) return 0;
+    b200::NormRopeArgs nr{};
+    if (int rc = check_norm_rope(positions, q_norm_weight, k_norm_weight, eps, cos_sin_cache,
+                                 max_position, &nr))
+        return rc;
+    if (!qkv || !slot_mapping) return fail(B200ATTN_E_BADARG, "null qkv/slot_mapping");
+    if (num_q_heads <= 0 || num_kv_heads <= 0 || head_dim <= 0)
+        return fail(B200ATTN_E_BADARG, "bad head counts");
+    const int64_t row = static_cast<int64_t>(num_q_heads + 2 * num_kv_heads) * head_dim;
+    if (qkv_row_stride < row || qkv_row_stride % 8 != 0)
+        return fail(B200ATTN_E_BADARG, "qkv_row_stride %lld < row of %lld elements or not 16-byte",
+                    static_cast<long long>(qkv_row_stride), static_cast<long long>(row));
+    const __nv_bfloat16* base = static_cast<const __nv_bfloat16*>(qkv);
+    const void* key = base + static_cast<int64_t>(num_q_heads) * head_dim;
+    const void* value = base + static_cast<int64_t>(num_q_heads + num_kv_heads) * head_dim;
+    return store_decode_impl(qkv, qkv_row_stride, key, qkv_row_stride, value, qkv_row_stride,
+                             slot_mapping, k_cache, v_cache, block_tables, table_row_stride,
+                             table_width, context_lens, out, workspace, workspace_bytes, batch,
+                             num_q_heads, num_kv_heads, head_dim, block_size, num_blocks, scale,
+                             num_splits, nullptr, 0, dtype, stream, &nr);
 }
 
 }  // extern "C"

@@ -5,6 +5,8 @@
 #include <cstddef>
 #include <cstdint>
 
+#include "norm_rope.cuh"
+
 namespace b200 {
 
 constexpr int kHeadDim = 128;  // every BASELINE model (Qwen3 0.6B / 8B / 32B) has head_dim 128
@@ -17,6 +19,24 @@ cudaError_t launch_store_kvcache(const void* key, int64_t key_row_stride, const 
                                  int64_t value_row_stride, void* k_cache, void* v_cache,
                                  const int32_t* slot_mapping, int32_t n_tokens, int32_t row_elems,
                                  int64_t num_slots, cudaStream_t stream);
+
+// ---- qk_norm_rope.cu -------------------------------------------------------------------------
+struct QkNormRopeParams {
+    const void* qkv;         // [n_tokens, (Hq + 2 Hkv) * 128] bf16 rows: q heads | k heads | v heads
+    int64_t qkv_row_stride;  // elements
+    NormRopeArgs nr;
+    void* q_out;             // [n_tokens, Hq, 128] contiguous
+    void* k_out;             // nullable; rows [n_tokens, Hkv, 128], may alias the k part of qkv
+    int64_t k_out_row_stride;
+    void* k_cache;           // [num_slots, Hkv, 128]
+    void* v_cache;
+    const int32_t* slot_mapping;  // nullable => no cache scatter
+    int64_t num_slots;
+    int32_t n_tokens;
+    int32_t num_q_heads;
+    int32_t num_kv_heads;
+};
+cudaError_t launch_qk_norm_rope_store(const QkNormRopeParams& p, cudaStream_t stream);
 
 // ---- decode_attn.cu --------------------------------------------------------------------------
 struct DecodeParams {
@@ -49,6 +69,11 @@ struct DecodeParams {
     // prefix kernel into workspace slots [num_splits, num_splits + prefix_chunks).
     const int32_t* plan;
     int32_t prefix_chunks;  // 0 => no cascade
+    // optional fused q/k RMSNorm + RoPE (norm_rope.cuh): with nr.positions set, q
+    // and new_key are raw QKV-projection outputs; q rows are normalised + rotated while they are
+    // loaded into registers, the new K row while it is scattered (needs new_key / slot_mapping).
+    int64_t q_row_stride;  // elements between q rows of consecutive sequences
+    NormRopeArgs nr;
 };
 cudaError_t launch_decode(const DecodeParams& p, const CUtensorMap& k_map, const CUtensorMap& v_map,
                           cudaStream_t stream);

@@ -119,7 +119,8 @@ decode_split_kernel(const __grid_constant__ CUtensorMap k_map,
         // CTAs never read the slot: it is token ctx-1 of sequence b, private to this split.
         if (p.new_key != nullptr && t_end == tiles_total) {
             const int64_t slot = p.slot_mapping[b];
-            if (slot >= 0 && slot < p.num_slots) {
+            const bool ok = slot >= 0 && slot < p.num_slots;  // warp-uniform
+            if (ok) {
                 const bool is_v = lane >= 16;
                 const int c = lane & 15;  // 16-byte chunk of the 256-byte head row
                 const uint8_t* src =
@@ -128,7 +129,21 @@ decode_split_kernel(const __grid_constant__ CUtensorMap k_map,
                     kvh * 256 + c * 16;
                 uint8_t* dst = static_cast<uint8_t*>(is_v ? p.v_cache : p.k_cache) +
                                (slot * p.num_kv_heads + kvh) * 256 + c * 16;
-                st_v4(dst, ld_nc_v4(src));
+                int4 row = ld_nc_v4(src);
+                if (p.nr.positions != nullptr) {
+                    // fused k_norm + RoPE of the raw K row (lanes 16-31 hold the V row: they run
+                    // the same shuffles and drop the result)
+                    const bool has_norm = p.nr.k_weight != nullptr;
+                    uint4 wv = make_uint4(0, 0, 0, 0);
+                    if (has_norm)
+                        wv = *reinterpret_cast<const uint4*>(
+                            static_cast<const uint8_t*>(p.nr.k_weight) + c * 16);
+                    const uint4 rot = norm_rope_row16(
+                        make_uint4(row.x, row.y, row.z, row.w), wv, has_norm, p.nr.eps,
+                        cos_sin_row(p.nr, b), c);
+                    if (!is_v) row = make_int4(rot.x, rot.y, rot.z, rot.w);
+                }
+                st_v4(dst, row);
                 asm volatile("fence.proxy.async.global;" ::: "memory");
             }
             __syncwarp();
@@ -166,17 +181,75 @@ decode_split_kernel(const __grid_constant__ CUtensorMap k_map,
     uint32_t qf[8][2];
     {
         const int head = lane >> 2;
-        const __nv_bfloat16* qrow =
-            static_cast<const __nv_bfloat16*>(p.q) + (q_row0 + head) * kHeadDim + 2 * (lane & 3);
+        const int hl = head < G ? head : 0;  // heads >= G: load row 0 (convergent), zeroed below
+        const __nv_bfloat16* qrow = static_cast<const __nv_bfloat16*>(p.q) +
+                                    static_cast<int64_t>(b) * p.q_row_stride +
+                                    (static_cast<int64_t>(kvh) * G + hl) * kHeadDim +
+                                    2 * (lane & 3);
 #pragma unroll
         for (int ks = 0; ks < 8; ++ks) {
-            if (head < G) {
-                qf[ks][0] = *reinterpret_cast<const uint32_t*>(qrow + ks * 16);
-                qf[ks][1] = *reinterpret_cast<const uint32_t*>(qrow + ks * 16 + 8);
-            } else {
-                qf[ks][0] = 0u;
-                qf[ks][1] = 0u;
+            qf[ks][0] = *reinterpret_cast<const uint32_t*>(qrow + ks * 16);
+            qf[ks][1] = *reinterpret_cast<const uint32_t*>(qrow + ks * 16 + 8);
+        }
+        if (p.nr.positions != nullptr) {
+            // Fused q_norm + RoPE (norm_rope.cuh) in the fragment layout: the 4 lanes of a head
+            // hold its whole row, lane (lane&3) the dims ks*16 + 2*(lane&3) + {0, 1, 8, 9}; the
+            // rotation partner (dim +- 64) is register ks +- 4 of the same thread.
+            const float* cs = cos_sin_row(p.nr, b) + 2 * (lane & 3);
+            float x[8][4];
+#pragma unroll
+            for (int ks = 0; ks < 8; ++ks) {
+                x[ks][0] = bf16_lo(qf[ks][0]);
+                x[ks][1] = bf16_hi(qf[ks][0]);
+                x[ks][2] = bf16_lo(qf[ks][1]);
+                x[ks][3] = bf16_hi(qf[ks][1]);
             }
+            if (p.nr.q_weight != nullptr) {
+                float ss = 0.f;
+#pragma unroll
+                for (int ks = 0; ks < 8; ++ks)
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) ss += x[ks][i] * x[ks][i];
+                ss += __shfl_xor_sync(0xffffffffu, ss, 1);
+                ss += __shfl_xor_sync(0xffffffffu, ss, 2);
+                const float r = 1.0f / sqrtf(ss * (1.0f / 128.0f) + p.nr.eps);
+                const __nv_bfloat16* wrow =
+                    static_cast<const __nv_bfloat16*>(p.nr.q_weight) + 2 * (lane & 3);
+#pragma unroll
+                for (int ks = 0; ks < 8; ++ks) {
+                    const uint32_t w0 = *reinterpret_cast<const uint32_t*>(wrow + ks * 16);
+                    const uint32_t w1 = *reinterpret_cast<const uint32_t*>(wrow + ks * 16 + 8);
+                    const float w[4] = {bf16_lo(w0), bf16_hi(w0), bf16_lo(w1), bf16_hi(w1)};
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+                        x[ks][i] = bf16_round(__fmul_rn(bf16_round(__fmul_rn(x[ks][i], r)), w[i]));
+                }
+            }
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks) {
+                // rotation index j = ks*16 + 2*(lane&3) + {0, 1, 8, 9}
+                const float2 c01 = *reinterpret_cast<const float2*>(cs + ks * 16);
+                const float2 c89 = *reinterpret_cast<const float2*>(cs + ks * 16 + 8);
+                const float2 s01 = *reinterpret_cast<const float2*>(cs + 64 + ks * 16);
+                const float2 s89 = *reinterpret_cast<const float2*>(cs + 64 + ks * 16 + 8);
+                const float cv[4] = {c01.x, c01.y, c89.x, c89.y};
+                const float sv[4] = {s01.x, s01.y, s89.x, s89.y};
+                float y1[4], y2[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const float x1 = x[ks][i], x2 = x[ks + 4][i];
+                    y1[i] = __fsub_rn(__fmul_rn(x1, cv[i]), __fmul_rn(x2, sv[i]));
+                    y2[i] = __fadd_rn(__fmul_rn(x2, cv[i]), __fmul_rn(x1, sv[i]));
+                }
+                qf[ks][0] = bf16_pack(y1[0], y1[1]);
+                qf[ks][1] = bf16_pack(y1[2], y1[3]);
+                qf[ks + 4][0] = bf16_pack(y2[0], y2[1]);
+                qf[ks + 4][1] = bf16_pack(y2[2], y2[3]);
+            }
+        }
+        if (head >= G) {
+#pragma unroll
+            for (int ks = 0; ks < 8; ++ks) qf[ks][0] = qf[ks][1] = 0u;
         }
     }
 

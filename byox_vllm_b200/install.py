@@ -9,6 +9,10 @@ The reference binds the op by name: `from nanovllm.layers.attention import Atten
      nanovllm.models.qwen3 is imported, so neither triton nor flash_attn is ever imported;
   3. if nanovllm.models.qwen3 was already imported, rebinds its `Attention` name and swaps the
      class of existing instances' constructor target.
+  4. (`fuse_qkv`, default on; B200ATTN_FUSE_QKV=0 or fuse_qkv=False keeps the
+     frozen Attention.forward boundary) rebinds Qwen3Attention.forward (models/qwen3.py:70-86) to
+     qkv_attention.qwen3_attention_forward: q/k RMSNorm + RoPE + KV scatter (+ the paged decode)
+     become one library call on the raw qkv_proj output.
 For tensor parallel runs nanovllm spawns ranks with multiprocessing "spawn"
 (engine/llm_engine.py:24-31): call install() at module top level of the launcher script so each
 spawned rank re-applies it on import of __main__.
@@ -16,11 +20,17 @@ spawned rank re-applies it on import of __main__.
 from __future__ import annotations
 
 import importlib
+import os
 import sys
 
+_ORIG_QWEN3_FORWARD = None
 
-def install(verbose: bool = False) -> None:
+
+def install(verbose: bool = False, fuse_qkv: bool | None = None) -> None:
     from . import attention as ours
+
+    if fuse_qkv is None:
+        fuse_qkv = os.environ.get("B200ATTN_FUSE_QKV", "1") != "0"
 
     ref_ctx = importlib.import_module("nanovllm.utils.context")
     ours.get_context = ref_ctx.get_context
@@ -31,9 +41,20 @@ def install(verbose: bool = False) -> None:
     qwen3 = sys.modules.get("nanovllm.models.qwen3")
     if qwen3 is not None:
         qwen3.Attention = ours.Attention
+    if fuse_qkv:
+        global _ORIG_QWEN3_FORWARD
+        from . import qkv_attention as fused
+
+        qwen3 = importlib.import_module("nanovllm.models.qwen3")  # binds OUR Attention (step 2)
+        cls = getattr(qwen3, "Qwen3Attention", None)
+        if cls is None:
+            fuse_qkv = False
+        elif cls.forward is not fused.qwen3_attention_forward:
+            _ORIG_QWEN3_FORWARD = cls.forward
+            cls.forward = fused.qwen3_attention_forward
     if verbose:
-        print("[byox_vllm_b200] nanovllm.layers.attention -> byox_vllm_b200.attention",
-              file=sys.stderr)
+        print("[byox_vllm_b200] nanovllm.layers.attention -> byox_vllm_b200.attention"
+              + (" (+ fused qkv path)" if fuse_qkv else ""), file=sys.stderr)
 
 
 def uninstall() -> None:
@@ -41,5 +62,10 @@ def uninstall() -> None:
     from . import context as own
 
     ours.get_context = own.get_context
+    global _ORIG_QWEN3_FORWARD
+    qwen3 = sys.modules.get("nanovllm.models.qwen3")
+    if qwen3 is not None and _ORIG_QWEN3_FORWARD is not None and hasattr(qwen3, "Qwen3Attention"):
+        qwen3.Qwen3Attention.forward = _ORIG_QWEN3_FORWARD
+        _ORIG_QWEN3_FORWARD = None
     if sys.modules.get("nanovllm.layers.attention") is ours:
         del sys.modules["nanovllm.layers.attention"]

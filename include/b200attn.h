@@ -14,6 +14,11 @@
  *   b200attn_cascade_*,        same decode call site (:87-96) for batches whose block tables
  *   b200attn_store_decode_cascade   start with identical block ids — the prefix-cache hits
  *                              nanovllm/engine/block_manager.py:41-71 produces
+ *   b200attn_qk_norm_rope_store  nanovllm/models/qwen3.py:80-83 + layers/attention.py:70-71:
+ *                              q_norm / k_norm (layers/layernorm.py:16-26), rotary_emb
+ *                              (layers/rotary_embedding.py:37-48) and store_kvcache in one pass
+ *                              over the QKV projection output
+ *   b200attn_qkv_decode        the same four steps + the paged decode (:87-96) in ONE launch
  *
  * Conventions
  *   - Plain pointers and sizes only; all buffers are DEVICE pointers owned by the caller (torch
@@ -37,7 +42,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 3
+#define B200ATTN_ABI_VERSION 4
 
 #define B200ATTN_DTYPE_BF16 0
 
@@ -184,6 +189,51 @@ int b200attn_prefill_varlen(const void* q, const void* key, int64_t key_row_stri
                             int32_t max_seqlen_q, int32_t max_seqlen_k, void* out,
                             int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim, int32_t block_size,
                             int64_t num_blocks, float scale, int32_t dtype, void* stream);
+
+/*
+ * Fused q/k RMSNorm + neox RoPE + KV scatter over the raw QKV projection output (the steps of
+ * nanovllm/models/qwen3.py:75-84 that precede the attention call). Row i of `qkv` holds
+ * num_q_heads q heads, then num_kv_heads k heads, then num_kv_heads v heads of head_dim bf16.
+ * For every token i and head row x of 128 elements:
+ *     q/k rows:  x32 = float(x) / sqrt(mean(x32^2) + eps); xw = bf16(bf16(x32) * weight)
+ *                (skipped when both weights are NULL: models with qkv_bias, qwen3.py:66-68,80-82)
+ *                y[j]      = xw[j] * cos[j] - xw[j + 64] * sin[j]
+ *                y[j + 64] = xw[j + 64] * cos[j] + xw[j] * sin[j]      j < 64, fp32, then bf16
+ *                with cos[j] = cos_sin_cache[positions[i] * 128 + j], sin[j] = ...[... + 64 + j]
+ *                (the layout RotaryEmbedding builds: rotary_embedding.py:27-35)
+ *     q -> q_out[i, h, :]  (contiguous [n_tokens, num_q_heads, 128])
+ *     k -> k_out[i * k_out_row_stride + h * 128 ...] when k_out != NULL (may alias the k part of
+ *          qkv: dense prefill reads K/V through strided views of qkv), and, when slot_mapping !=
+ *          NULL and slot_mapping[i] in [0, num_slots), -> k_cache[slot, h, :]
+ *     v -> v_cache[slot, h, :] (bit-exact copy) under the same slot condition
+ * positions are clamped to [0, max_position). Strides are in elements.
+ */
+int b200attn_qk_norm_rope_store(const void* qkv, int64_t qkv_row_stride, const int64_t* positions,
+                                const void* q_norm_weight, const void* k_norm_weight, float eps,
+                                const float* cos_sin_cache, int32_t max_position, void* q_out,
+                                void* k_out, int64_t k_out_row_stride, void* k_cache,
+                                void* v_cache, const int32_t* slot_mapping, int32_t n_tokens,
+                                int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim,
+                                int64_t num_slots, int32_t dtype, void* stream);
+
+/*
+ * Whole decode step of one layer between qkv_proj and o_proj in ONE launch: the decode kernel of
+ * b200attn_store_decode reads q and this step's K/V rows straight from `qkv` (batch rows, layout
+ * as above), applies q_norm + RoPE to the q heads while loading them into registers and k_norm +
+ * RoPE to the new K row while scattering it, then attends over the updated cache. Equal to
+ * b200attn_qk_norm_rope_store followed by b200attn_decode. Same precondition on slot_mapping as
+ * b200attn_store_decode. Not combinable with the cascade (run the two-call sequence instead).
+ */
+int b200attn_qkv_decode(const void* qkv, int64_t qkv_row_stride, const int64_t* positions,
+                        const void* q_norm_weight, const void* k_norm_weight, float eps,
+                        const float* cos_sin_cache, int32_t max_position,
+                        const int32_t* slot_mapping, void* k_cache, void* v_cache,
+                        const int32_t* block_tables, int64_t table_row_stride, int32_t table_width,
+                        const int32_t* context_lens, void* out, void* workspace,
+                        size_t workspace_bytes, int32_t batch, int32_t num_q_heads,
+                        int32_t num_kv_heads, int32_t head_dim, int32_t block_size,
+                        int64_t num_blocks, float scale, int32_t num_splits, int32_t dtype,
+                        void* stream);
 
 #ifdef __cplusplus
 }

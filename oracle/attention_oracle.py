@@ -9,6 +9,9 @@ What it restates (paths relative to the reference tree /root/reference):
   paged_decode_ref       nanovllm/layers/attention.py:87-96 -> flash_attn_with_kvcache
   prefill_varlen_ref     nanovllm/layers/attention.py:72-86 -> flash_attn_varlen_func
   attention_forward_ref  nanovllm/layers/attention.py:67-97 (dispatch on the Context)
+  qk_norm_rope_ref       nanovllm/models/qwen3.py:75-83 (split, q_norm/k_norm, rotary_emb) with
+                         layers/layernorm.py:16-26 and layers/rotary_embedding.py:7-16,27-48
+  qkv_attention_ref      qwen3.py:75-84: the steps above followed by attention_forward_ref
 
 The attention arithmetic itself lives in a third-party dependency that is NOT in the reference
 tree: flash-attn (unpinned in the reference's pyproject.toml:18; this image carries 2.8.3). Its
@@ -25,6 +28,9 @@ Parity pins (see DESIGN.md "Oracle"):
   * decode / prefill: against flash-attn 2.8.3 executed on a B200 through the reference's exact
     call sites — fixtures tests/golden/fa_*.npz made by tools/make_golden_flashattn.py
     (tolerance 2e-2 abs + 1e-2 rel, the bound north_star states for bf16).
+  * q/k norm + RoPE: bit-exact against the reference's own RMSNorm / RotaryEmbedding modules run
+    on CPU (eager: TORCHDYNAMO_DISABLE=1) — fixtures tests/golden/normrope_*.npz made by
+    tools/make_golden_normrope.py.
 """
 from __future__ import annotations
 
@@ -181,3 +187,57 @@ def within_tolerance(got: torch.Tensor, want: torch.Tensor, atol: float = 2e-2,
     ratio = ((got - want).abs() / (atol + rtol * want.abs())).max().item()
     ok = bool(torch.isfinite(got).all()) and ratio <= 1.0
     return ok, ratio
+
+
+def rope_cos_sin_cache(head_dim: int, max_position: int, base: float) -> torch.Tensor:
+    """[max_position, head_dim] fp32 = cos(head_dim/2) | sin(head_dim/2), the table
+    RotaryEmbedding.__init__ builds (rotary_embedding.py:27-35, without its unsqueeze)."""
+    inv_freq = 1.0 / (base ** (torch.arange(0, head_dim, 2, dtype=torch.float) / head_dim))
+    t = torch.arange(max_position, dtype=torch.float)
+    freqs = torch.einsum("i,j -> ij", t, inv_freq)
+    return torch.cat((freqs.cos(), freqs.sin()), dim=-1)
+
+
+def _rms_norm_ref(x: torch.Tensor, weight: torch.Tensor, eps: float) -> torch.Tensor:
+    """layers/layernorm.py:16-26 (rms_forward), eager rounding points."""
+    orig = x.dtype
+    assert weight.dtype == orig, "the reference builds RMSNorm weights in the model dtype"
+    x = x.float()
+    var = x.pow(2).mean(dim=-1, keepdim=True)
+    x = x * torch.rsqrt(var + eps)
+    return x.to(orig) * weight
+
+
+def _rope_ref(x: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor) -> torch.Tensor:
+    """layers/rotary_embedding.py:7-16 (apply_rotary_emb)."""
+    x1, x2 = torch.chunk(x.float(), 2, dim=-1)
+    y1 = x1 * cos - x2 * sin
+    y2 = x2 * cos + x1 * sin
+    return torch.cat((y1, y2), dim=-1).to(x.dtype)
+
+
+def qk_norm_rope_ref(qkv: torch.Tensor, positions: torch.Tensor, q_weight, k_weight, eps: float,
+                     cos_sin_cache: torch.Tensor, num_q_heads: int, num_kv_heads: int,
+                     head_dim: int = 128):
+    """qwen3.py:75-83: split qkv rows into heads, per-head RMSNorm of q and k (skipped when the
+    weights are None: qkv_bias models), neox RoPE at `positions`. Returns (q, k, v) with v a
+    strided view of qkv as in the reference."""
+    q_size, kv_size = num_q_heads * head_dim, num_kv_heads * head_dim
+    q, k, v = qkv.split([q_size, kv_size, kv_size], dim=-1)
+    q = q.reshape(-1, num_q_heads, head_dim)
+    k = k.reshape(-1, num_kv_heads, head_dim)
+    v = v.view(-1, num_kv_heads, head_dim)
+    if q_weight is not None:
+        q = _rms_norm_ref(q, q_weight, eps)
+        k = _rms_norm_ref(k, k_weight, eps)
+    cos_sin = cos_sin_cache[positions.long()].unsqueeze(1)
+    cos, sin = cos_sin.chunk(2, dim=-1)
+    return _rope_ref(q, cos, sin), _rope_ref(k, cos, sin), v
+
+
+def qkv_attention_ref(qkv, positions, q_weight, k_weight, eps, cos_sin_cache, k_cache, v_cache,
+                      context, scale, num_q_heads, num_kv_heads):
+    """qwen3.py:75-84 up to (not including) o_proj; caches updated in place."""
+    q, k, v = qk_norm_rope_ref(qkv, positions, q_weight, k_weight, eps, cos_sin_cache,
+                               num_q_heads, num_kv_heads)
+    return attention_forward_ref(q, k, v, k_cache, v_cache, context, scale)

@@ -86,3 +86,20 @@ def test_oracle_edge_cases():
     before = kc.clone()
     orc.store_kvcache_ref(k, v, kc, vc, torch.full_like(slots, -1))
     assert torch.equal(kc, before)
+
+
+@pytest.mark.parametrize("case", gc.NORMROPE_CASES, ids=[c[0] for c in gc.NORMROPE_CASES])
+def test_normrope_oracle_matches_reference_modules(case):
+    """Bit-exact against the reference's RMSNorm / RotaryEmbedding (eager) called as
+    models/qwen3.py:75-83 calls them (tools/make_golden_normrope.py)."""
+    name, n, Hq, Hkv, has_norm, max_pos, base, seed = case
+    g = _load(f"normrope_{name}.npz")
+    qkv, positions, q_w, k_w = gc.normrope_inputs(n, Hq, Hkv, has_norm, max_pos, seed)
+    assert synth.checksum(qkv, positions, *([q_w, k_w] if has_norm else [])) == str(g["input_sha"])
+    cache = orc.rope_cos_sin_cache(128, max_pos, base)
+    assert synth.checksum(cache) == str(g["cos_sin_sha"])
+    q, k, v = orc.qk_norm_rope_ref(qkv, positions, q_w, k_w, gc.NORMROPE_EPS, cache, Hq, Hkv)
+    assert np.array_equal(q.contiguous().view(torch.int16).numpy(), g["q"])
+    assert np.array_equal(k.contiguous().view(torch.int16).numpy(), g["k"])
+    # v is the untouched strided view of qkv (qwen3.py:79)
+    assert v.data_ptr() == qkv.data_ptr() + (Hq + Hkv) * 128 * 2

@@ -59,3 +59,31 @@ PREFILL_CASES = [
     ("paged_prefix_8_4", [280, 600, 40], [256, 512, 0], 8, 4, 24),
     ("paged_prefix_4_1", [1000, 257], [768, 256], 4, 1, 25),
 ]
+
+
+# ---- q/k RMSNorm + RoPE: (name, n_tokens, Hq, Hkv, has_norm, max_position, rope_base, seed) -----
+NORMROPE_CASES = [
+    ("n1_16_8", 1, 16, 8, True, 4096, 1000000.0, 11),
+    ("n37_16_8", 37, 16, 8, True, 4096, 1000000.0, 12),
+    ("n64_32_8", 64, 32, 8, True, 40960, 1000000.0, 13),
+    ("n19_8_1", 19, 8, 1, True, 40960, 1000000.0, 14),
+    ("n23_4_1_nonorm", 23, 4, 1, False, 4096, 10000.0, 15),
+]
+NORMROPE_EPS = 1e-6
+
+
+def normrope_inputs(n, Hq, Hkv, has_norm, max_position, seed, D=128):
+    """qkv [n, (Hq + 2 Hkv) * D] bf16 ~ N(0, 2^2) (so the norm has work to do), positions int64 in
+    [0, max_position) including both ends, bf16 norm weights ~ 1 + 0.25 N(0,1) (None without
+    norm: the qkv_bias models of qwen3.py:66-68)."""
+    gen = torch.Generator().manual_seed(seed)
+    qkv = (2.0 * torch.randn(n, (Hq + 2 * Hkv) * D, generator=gen)).to(torch.bfloat16)
+    positions = torch.randint(0, max_position, (n,), generator=gen, dtype=torch.int64)
+    positions[0] = max_position - 1
+    if n > 1:
+        positions[1] = 0
+    q_w = k_w = None
+    if has_norm:
+        q_w = (1.0 + 0.25 * torch.randn(D, generator=gen)).to(torch.bfloat16)
+        k_w = (1.0 + 0.25 * torch.randn(D, generator=gen)).to(torch.bfloat16)
+    return qkv, positions, q_w, k_w
