@@ -564,6 +564,8 @@ int b200attn_qk_norm_rope_store(const void* qkv, int64_t qkv_row_stride, const i
     if (n_tokens < 0 || num_q_heads <= 0 || num_kv_heads <= 0 || num_slots < 0)
         return fail(B200ATTN_E_BADARG, "negative or zero size");
     if (n_tokens == 0) return 0;
+    if (static_cast<int64_t>(n_tokens) * (num_q_heads + 2 * num_kv_heads) >= (1LL << 31))
+        return fail(B200ATTN_E_UNSUPPORTED, "n_tokens * heads exceeds 32-bit row indexing");
     b200::QkNormRopeParams p{};
     if (int rc = check_norm_rope(positions, q_norm_weight, k_norm_weight, eps, cos_sin_cache,
                                  max_position, &p.nr))

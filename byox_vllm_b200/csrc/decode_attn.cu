@@ -130,9 +130,8 @@ decode_split_kernel(const __grid_constant__ CUtensorMap k_map,
                 uint8_t* dst = static_cast<uint8_t*>(is_v ? p.v_cache : p.k_cache) +
                                (slot * p.num_kv_heads + kvh) * 256 + c * 16;
                 int4 row = ld_nc_v4(src);
-                if (p.nr.positions != nullptr) {
-                    // fused k_norm + RoPE of the raw K row (lanes 16-31 hold the V row: they run
-                    // the same shuffles and drop the result)
+                if (p.nr.positions != nullptr && !is_v) {
+                    // fused k_norm + RoPE of the raw K row: lanes 0-15 only (half-warp shuffles)
                     const bool has_norm = p.nr.k_weight != nullptr;
                     uint4 wv = make_uint4(0, 0, 0, 0);
                     if (has_norm)
@@ -140,8 +139,8 @@ decode_split_kernel(const __grid_constant__ CUtensorMap k_map,
                             static_cast<const uint8_t*>(p.nr.k_weight) + c * 16);
                     const uint4 rot = norm_rope_row16(
                         make_uint4(row.x, row.y, row.z, row.w), wv, has_norm, p.nr.eps,
-                        cos_sin_row(p.nr, b), c);
-                    if (!is_v) row = make_int4(rot.x, rot.y, rot.z, rot.w);
+                        load_cos_sin8(cos_sin_row(p.nr, b), c), c, 0x0000ffffu);
+                    row = make_int4(rot.x, rot.y, rot.z, rot.w);
                 }
                 st_v4(dst, row);
                 asm volatile("fence.proxy.async.global;" ::: "memory");
@@ -212,7 +211,7 @@ decode_split_kernel(const __grid_constant__ CUtensorMap k_map,
                     for (int i = 0; i < 4; ++i) ss += x[ks][i] * x[ks][i];
                 ss += __shfl_xor_sync(0xffffffffu, ss, 1);
                 ss += __shfl_xor_sync(0xffffffffu, ss, 2);
-                const float r = 1.0f / sqrtf(ss * (1.0f / 128.0f) + p.nr.eps);
+                const float r = rsqrtf(ss * (1.0f / 128.0f) + p.nr.eps);
                 const __nv_bfloat16* wrow =
                     static_cast<const __nv_bfloat16*>(p.nr.q_weight) + 2 * (lane & 3);
 #pragma unroll

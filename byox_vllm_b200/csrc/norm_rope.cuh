@@ -3,7 +3,7 @@
 //     q = q_norm(q); k = k_norm(k)            layers/layernorm.py:16-26  (rms_forward)
 //     q, k = rotary_emb(positions, q, k)      layers/rotary_embedding.py:7-16, 44-47
 // Rounding points follow the reference's eager arithmetic so results agree to the bf16 bit except
-// where the fp32 sum of squares rounds differently (different summation order):
+// where the fp32 sum of squares / rsqrt round differently (summation order, MUFU.RSQ):
 //     x32 = float(x);  x32 *= 1/sqrt(mean(x32^2) + eps);  xb = bf16(x32);  xw = bf16(xb * w)
 //     y1 = xw1*cos - xw2*sin;  y2 = xw2*cos + xw1*sin   (fp32 mul, mul, add/sub: no FMA);  bf16(y)
 // where (xw1, xw2) = elements (j, j + 64) and cos/sin = cos_sin_cache[pos][j], [pos][64 + j].
@@ -33,65 +33,79 @@ __device__ __forceinline__ uint32_t bf16_pack(float lo, float hi) {
     return *reinterpret_cast<uint32_t*>(&v);
 }
 
-// Row spread over a half-warp: lane c = (lane & 15) holds elements 8c .. 8c+7 as one 16-byte
-// vector `raw`; `wv` = weight[8c .. 8c+7] (ignored when !has_norm); cs_row = cos_sin_cache row of
-// this token. MUST be called by all 32 lanes of the warp (full-mask shuffles with xor <= 8 stay
-// inside each half-warp, so the two halves may work on different rows).
-__device__ __forceinline__ uint4 norm_rope_row16(uint4 raw, uint4 wv, bool has_norm, float eps,
-                                                 const float* __restrict__ cs_row, int c) {
-    float x[8];
-    const uint32_t rw[4] = {raw.x, raw.y, raw.z, raw.w};
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        x[2 * i] = bf16_lo(rw[i]);
-        x[2 * i + 1] = bf16_hi(rw[i]);
-    }
-    // cos/sin of rotation index j = 8*(c&7) + i; issued early so they overlap the reduction
+// cos / sin of one token for the 8 rotation indices j = 8*(c&7) .. +7 a lane works on. The sine
+// carries the sign of the lane's half (first half: y1 = x1 cos - x2 sin; second: y2 = x2 cos +
+// x1 sin), so the rotation is mul, mul, add for every lane: a - b == a + (-b) exactly in IEEE.
+struct CosSin8 {
+    float c[8], s[8];
+};
+__device__ __forceinline__ CosSin8 load_cos_sin8(const float* __restrict__ cs_row, int c) {
     const int j0 = 8 * (c & 7);
     const float4 c0 = *reinterpret_cast<const float4*>(cs_row + j0);
     const float4 c1 = *reinterpret_cast<const float4*>(cs_row + j0 + 4);
     const float4 s0 = *reinterpret_cast<const float4*>(cs_row + 64 + j0);
     const float4 s1 = *reinterpret_cast<const float4*>(cs_row + 64 + j0 + 4);
+    CosSin8 r;
+    r.c[0] = c0.x, r.c[1] = c0.y, r.c[2] = c0.z, r.c[3] = c0.w;
+    r.c[4] = c1.x, r.c[5] = c1.y, r.c[6] = c1.z, r.c[7] = c1.w;
+    r.s[0] = s0.x, r.s[1] = s0.y, r.s[2] = s0.z, r.s[3] = s0.w;
+    r.s[4] = s1.x, r.s[5] = s1.y, r.s[6] = s1.z, r.s[7] = s1.w;
+    if (c < 8) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) r.s[i] = -r.s[i];
+    }
+    return r;
+}
+
+// bf16(bf16(a) * bf16(b)) for two packed pairs: one HMUL2.BF16 (the product of two bf16 values is
+// exact in fp32, so the single rounding of the packed multiply equals torch's float-then-round).
+__device__ __forceinline__ uint32_t bf16x2_mul(uint32_t a, uint32_t b) {
+    __nv_bfloat162 r = __hmul2(*reinterpret_cast<__nv_bfloat162*>(&a),
+                               *reinterpret_cast<__nv_bfloat162*>(&b));
+    return *reinterpret_cast<uint32_t*>(&r);
+}
+
+// Row spread over a half-warp: lane c = (lane & 15) holds elements 8c .. 8c+7 as one 16-byte
+// vector `raw`; `wv` = weight[8c .. 8c+7] (ignored when !has_norm); cs = cos/sin of this token.
+// Must be called by all 16 lanes of the half-warp named by `hmask` (0xffff or 0xffff0000): the
+// shuffles use xor <= 8, so the two halves of a warp may work on different rows or diverge.
+__device__ __forceinline__ uint4 norm_rope_row16(uint4 raw, uint4 wv, bool has_norm, float eps,
+                                                 const CosSin8& cs, int c, uint32_t hmask) {
+    uint32_t xw[4] = {raw.x, raw.y, raw.z, raw.w};
     if (has_norm) {
+        float x[8];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            x[2 * i] = bf16_lo(xw[i]);
+            x[2 * i + 1] = bf16_hi(xw[i]);
+        }
         float ss = 0.f;
 #pragma unroll
         for (int i = 0; i < 8; ++i) ss += x[i] * x[i];
 #pragma unroll
-        for (int off = 1; off < 16; off <<= 1) ss += __shfl_xor_sync(0xffffffffu, ss, off);
-        const float r = 1.0f / sqrtf(ss * (1.0f / 128.0f) + eps);  // IEEE div/sqrt, as torch CPU
+        for (int off = 1; off < 16; off <<= 1) ss += __shfl_xor_sync(hmask, ss, off);
+        // rsqrtf (MUFU.RSQ, <= 2 ulp) is what torch.rsqrt executes on a GPU, eager or compiled;
+        // an IEEE 1/sqrt (what torch does on the CPU) costs ~40 instructions per row and this pass is
+        // instruction-issue bound before it is HBM bound
+        const float r = rsqrtf(ss * (1.0f / 128.0f) + eps);
         const uint32_t ww[4] = {wv.x, wv.y, wv.z, wv.w};
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            x[2 * i] = bf16_round(__fmul_rn(bf16_round(__fmul_rn(x[2 * i], r)), bf16_lo(ww[i])));
-            x[2 * i + 1] =
-                bf16_round(__fmul_rn(bf16_round(__fmul_rn(x[2 * i + 1], r)), bf16_hi(ww[i])));
-        }
+        for (int i = 0; i < 4; ++i)
+            xw[i] = bf16x2_mul(bf16_pack(__fmul_rn(x[2 * i], r), __fmul_rn(x[2 * i + 1], r)),
+                               ww[i]);
     }
     // partner half of the rotation pair lives in lane c ^ 8 (elements +-64)
-    float y[8];
+    uint32_t ow[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-        const uint32_t mine = bf16_pack(x[2 * i], x[2 * i + 1]);  // exact: x is bf16-valued
-        const uint32_t other = __shfl_xor_sync(0xffffffffu, mine, 8);
-        y[2 * i] = bf16_lo(other);
-        y[2 * i + 1] = bf16_hi(other);
+        const uint32_t other = __shfl_xor_sync(hmask, xw[i], 8);
+        const float a0 = __fmul_rn(bf16_lo(xw[i]), cs.c[2 * i]);
+        const float a1 = __fmul_rn(bf16_hi(xw[i]), cs.c[2 * i + 1]);
+        const float b0 = __fmul_rn(bf16_lo(other), cs.s[2 * i]);
+        const float b1 = __fmul_rn(bf16_hi(other), cs.s[2 * i + 1]);
+        ow[i] = bf16_pack(__fadd_rn(a0, b0), __fadd_rn(a1, b1));
     }
-    const float cs[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
-    const float sn[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
-    const bool first_half = c < 8;
-    float o[8];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        const float a = __fmul_rn(x[i], cs[i]);
-        const float b = __fmul_rn(y[i], sn[i]);
-        o[i] = first_half ? __fsub_rn(a, b) : __fadd_rn(a, b);
-    }
-    uint4 out;
-    out.x = bf16_pack(o[0], o[1]);
-    out.y = bf16_pack(o[2], o[3]);
-    out.z = bf16_pack(o[4], o[5]);
-    out.w = bf16_pack(o[6], o[7]);
-    return out;
+    return make_uint4(ow[0], ow[1], ow[2], ow[3]);
 }
 
 // cos_sin_cache row of a token; positions outside [0, max_position) are clamped (the reference

@@ -4,10 +4,13 @@ comparisons with the oracle, equality of the one-launch decode with the two-call
 Context dispatch of qkv_attention, CUDA-graph replay and size-independent properties at full size.
 
 Tolerance for the normalised + rotated rows: the arithmetic follows the reference's rounding
-points, so results are bit-identical except where the fp32 sum of squares rounds differently
-(summation order) and flips a bf16 rounding: every element must be within ONE bf16 ulp
-(2^-7 of the head row's largest element) of the reference and at most 0.5 % of the elements may
-differ at all. Without
+points, so results are bit-identical except where the fp32 sum of squares or the reciprocal
+square root round differently (summation order; MUFU.RSQ on the GPU, as torch.rsqrt there, vs
+IEEE 1/sqrt in the CPU oracle) and flip a bf16 rounding of the normalised value. Such a flip is one ulp of
+xn, at most two ulps after the weight multiply and its rounding (|w| < 2), the rotation can shrink
+the row maximum by sqrt(2), and the final rounding adds one more: every element must be within
+FOUR bf16 ulps (4 * 2^-7) of the head row's largest element of the reference, and at most 0.5 %
+of the elements may differ at all. Without
 the norm (and for V rows) the result must be bit-exact. Attention outputs: north_star bound
 (2e-2 abs + 1e-2 rel)."""
 import numpy as np
@@ -33,10 +36,10 @@ def _ulp_check(got: torch.Tensor, want: torch.Tensor, what: str, exact: bool = F
         assert bool(same.all()), f"{what}: not bit-exact ({(~same).sum().item()} elements differ)"
         return 0.0
     g, w = got.float(), want.float()
-    # one bf16 ulp of the head row's largest element: a flipped rounding of x1 moves
-    # y = x1 cos - x2 sin by an ulp of x1 even where y itself is small
-    bound = w.abs().amax(dim=-1, keepdim=True) * 2.0 ** -7 + 1e-30
-    assert bool(((g - w).abs() <= bound).all()), f"{what}: more than one bf16 ulp off"
+    # ulps of the head row's largest element: a flipped rounding of x1 moves y = x1 cos - x2 sin
+    # by ulps of x1 even where y itself is small
+    bound = w.abs().amax(dim=-1, keepdim=True) * (4 * 2.0 ** -7) + 1e-30
+    assert bool(((g - w).abs() <= bound).all()), f"{what}: more than four bf16 ulps off"
     frac = 1.0 - same.float().mean().item()
     assert frac <= 5e-3, f"{what}: {frac:.4%} of the elements differ from the reference"
     return frac

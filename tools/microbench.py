@@ -384,6 +384,150 @@ def bench_prefill(out, quick):
         torch.cuda.empty_cache()
 
 
+def timed_graph(fn, iters=10, warm=3):
+    """Capture fn once into a CUDA graph and time replays (decode runs under graphs in the engine:
+    model_runner.py:242-254), L2 flushed before every replay."""
+    fn()
+    torch.cuda.synchronize()
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        fn()
+    torch.cuda.current_stream().wait_stream(s)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        fn()
+    return timed(g.replay, iters=iters, warm=warm)
+
+
+def bench_qkv(out, quick):
+    """the steps between qkv_proj and o_proj (models/qwen3.py:75-84). Ours: one pass
+    (prefill sizes) / one launch (decode). Reference chain: its own RMSNorm x2 + RotaryEmbedding
+    (torch.compile'd, from baseline/_ref) + Triton store_kvcache (+ flash_attn_with_kvcache)."""
+    sys.path.insert(0, str(ROOT / "baseline" / "_ref"))
+    from nanovllm.layers.attention import store_kvcache as ref_store
+    from nanovllm.layers.layernorm import RMSNorm
+    from nanovllm.layers.rotary_embedding import RotaryEmbedding
+    from flash_attn import flash_attn_with_kvcache
+
+    from byox_vllm_b200 import qkv_attention as fused
+    from byox_vllm_b200.attention import paged_decode
+
+    eps, max_pos = 1e-6, 40960
+    torch.set_default_device("cuda")
+    rope = RotaryEmbedding(D, D, max_pos, 1e6)
+    torch.set_default_dtype(torch.bfloat16)
+    qn, kn = RMSNorm(D, eps), RMSNorm(D, eps)
+    torch.set_default_dtype(torch.float32)
+    torch.set_default_device("cpu")
+    g = torch.Generator(device="cuda").manual_seed(0)
+    qn.weight.data.normal_(1.0, 0.25, generator=g)
+    kn.weight.data.normal_(1.0, 0.25, generator=g)
+    cache = rope.cos_sin_cache
+
+    def ref_prep(qkv, pos, Hq, Hkv):
+        q, k, v = qkv.split([Hq * D, Hkv * D, Hkv * D], dim=-1)
+        q, k, v = q.view(-1, Hq, D), k.view(-1, Hkv, D), v.view(-1, Hkv, D)
+        q, k = qn(q), kn(k)
+        q, k = rope(pos, q, k)
+        return q, k, v
+
+    # ---- prefill-size pass: norm + rope + scatter -------------------------------------------
+    for N, Hq, Hkv in ([(16384, 32, 8)] if quick else
+                       [(16384, 32, 8), (16384, 16, 8), (16384, 8, 1), (4096, 32, 8), (1024, 16, 8)]):
+        qkv = torch.empty(N, (Hq + 2 * Hkv) * D, dtype=torch.bfloat16,
+                          device="cuda").normal_(generator=g)
+        pos = torch.randint(0, max_pos, (N,), generator=g, device="cuda")
+        nb = (N + BLOCK - 1) // BLOCK * 2
+        kc = torch.zeros(nb, BLOCK, Hkv, D, dtype=torch.bfloat16, device="cuda")
+        vc, kc2, vc2 = torch.zeros_like(kc), torch.zeros_like(kc), torch.zeros_like(kc)
+        slots = torch.randperm(nb * BLOCK, generator=g, device="cuda")[:N].to(torch.int32)
+        work = qkv.clone()
+
+        def ours():
+            return fused.qk_norm_rope_store(work, pos, qn.weight, kn.weight, eps, cache, Hq, Hkv,
+                                            D, k_cache=kc, v_cache=vc, slot_mapping=slots)
+
+        def ref():
+            q, k, v = ref_prep(qkv, pos, Hq, Hkv)
+            ref_store(k, v, kc2, vc2, slots)
+            return q, k
+
+        work.copy_(qkv)
+        q1, k1, _ = ours()
+        q2, k2 = ref()
+        torch.cuda.synchronize()
+        dq = (q1.float() - q2.float()).abs().max().item()
+        mism = (q1.view(torch.int16) != q2.view(torch.int16)).float().mean().item()
+        v_same = torch.equal(vc, vc2)
+        # algorithmic bytes (k written in place too, as dense prefill needs it)
+        alg = N * ((Hq + 2 * Hkv) * 256 + Hq * 256 + Hkv * 256 + 2 * Hkv * 256 + 12)
+        t_min, t_med = timed(ours, iters=10)
+        f_min, f_med = timed(ref, iters=10)
+        rec = dict(kind="qkv_prep", N=N, Hq=Hq, Hkv=Hkv, alg_bytes=alg, ours_us=t_med * 1e3,
+                   ours_min_us=t_min * 1e3, ours_gbs=alg / t_med / 1e6,
+                   ours_frac=alg / t_med / 1e6 / PEAK, ref_us=f_med * 1e3, speedup=f_med / t_med,
+                   q_max_abs_diff=dq, q_mismatch_frac=mism, v_cache_equal=v_same)
+        out.write(json.dumps(rec) + "\n")
+        out.flush()
+        print(f"qkv_prep N={N:6d} {Hq}/{Hkv}: ours {t_med * 1e3:7.1f} us {rec['ours_gbs']:6.0f} GB/s"
+              f" ({rec['ours_frac']:.2f}) | ref chain {f_med * 1e3:7.1f} us | x{rec['speedup']:.2f}"
+              f" q diff {dq:.4f} mismatch {mism:.2e} v equal={v_same}", flush=True)
+        del qkv, work, kc, vc, kc2, vc2
+        torch.cuda.empty_cache()
+
+    # ---- decode step of one layer, graph-replayed -------------------------------------------
+    for B, ctx, Hq, Hkv in ([(256, 1024, 16, 8)] if quick else
+                            [(256, 1024, 16, 8), (128, 4096, 32, 8), (256, 8192, 8, 1),
+                             (64, 4096, 32, 8), (16, 2048, 16, 8), (1, 4096, 32, 8)]):
+        _, kc, vc, lens, bt, alg = decode_inputs(B, ctx, Hq, Hkv, ragged=True, seed=B)
+        qkv = torch.empty(B, (Hq + 2 * Hkv) * D, dtype=torch.bfloat16,
+                          device="cuda").normal_(generator=g)
+        pos = (lens - 1).long()
+        last = (lens - 1)
+        slots = (bt.gather(1, (last // BLOCK).long().unsqueeze(1)).squeeze(1) * BLOCK +
+                 last % BLOCK).to(torch.int32)
+        scale = D ** -0.5
+        o1 = torch.empty(B, Hq, D, dtype=torch.bfloat16, device="cuda")
+        o2 = torch.empty_like(o1)
+
+        def ours():
+            fused.qkv_decode(qkv, pos, qn.weight, kn.weight, eps, cache, kc, vc, lens, bt, slots,
+                             scale, Hq, Hkv, out=o1)
+
+        def ours_boundary():  # frozen Attention.forward boundary: reference prep + our fused call
+            q, k, v = ref_prep(qkv, pos, Hq, Hkv)
+            paged_decode(q, kc, vc, lens, bt, scale, key=k, value=v, slot_mapping=slots, out=o2)
+
+        def ref():
+            q, k, v = ref_prep(qkv, pos, Hq, Hkv)
+            ref_store(k, v, kc, vc, slots)
+            return flash_attn_with_kvcache(q.unsqueeze(1), kc, vc, cache_seqlens=lens,
+                                           block_table=bt, softmax_scale=scale, causal=True)
+
+        ours()
+        o_ref = ref()
+        torch.cuda.synchronize()
+        err = (o1.float() - o_ref.squeeze(1).float()).abs().max().item()
+        t_min, t_med = timed_graph(ours)
+        b_min, b_med = timed_graph(ours_boundary)
+        f_min, f_med = timed_graph(ref)
+        alg2 = alg + B * (Hq + 2 * Hkv) * 256  # decode bytes + the qkv rows
+        rec = dict(kind="qkv_decode", B=B, ctx=ctx, Hq=Hq, Hkv=Hkv, alg_bytes=alg2,
+                   ours_us=t_med * 1e3, ours_gbs=alg2 / t_med / 1e6,
+                   ours_frac=alg2 / t_med / 1e6 / PEAK, ours_boundary_us=b_med * 1e3,
+                   ref_us=f_med * 1e3, speedup_vs_ref=f_med / t_med,
+                   speedup_vs_boundary=b_med / t_med, max_abs_diff_vs_ref=err)
+        out.write(json.dumps(rec) + "\n")
+        out.flush()
+        print(f"qkv_decode B={B:4d} ctx={ctx:6d} {Hq}/{Hkv}: one launch {t_med * 1e3:7.1f} us "
+              f"{rec['ours_gbs']:6.0f} GB/s ({rec['ours_frac']:.2f}) | ref prep + ours "
+              f"{b_med * 1e3:7.1f} us | ref chain {f_med * 1e3:7.1f} us | x{rec['speedup_vs_ref']:.2f}"
+              f" err {err:.4f}", flush=True)
+        del kc, vc
+        torch.cuda.empty_cache()
+
+
 def main():
     args = [a for a in sys.argv[1:] if not a.startswith("--")]
     quick = "--quick" in sys.argv
@@ -396,7 +540,7 @@ def main():
                                   tf_peak=TF_PEAK, torch=torch.__version__)) + "\n")
         for k in kinds:
             {"decode": bench_decode, "store": bench_store, "prefill": bench_prefill,
-             "sweep": bench_sweep, "cascade": bench_cascade}[k](out, quick)
+             "sweep": bench_sweep, "cascade": bench_cascade, "qkv": bench_qkv}[k](out, quick)
 
 
 if __name__ == "__main__":
