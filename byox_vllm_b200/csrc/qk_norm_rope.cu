@@ -45,7 +45,7 @@ __device__ __forceinline__ void st_u4(void* p, const uint4& v) {
 // so the shuffles are full-mask and convergent); the remaining blocks copy the v heads into the
 // cache.
 template <bool kHasNorm>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 4)
 qk_norm_rope_store_kernel(const QkNormRopeParams p, uint32_t qk_blocks, uint32_t qk_groups,
                           uint32_t v_groups) {
     const int c = threadIdx.x & 15;
@@ -80,6 +80,8 @@ qk_norm_rope_store_kernel(const QkNormRopeParams p, uint32_t qk_blocks, uint32_t
     const uint32_t h0 = (item - tok * qk_groups) * kRows;
     const bool live = tok < static_cast<uint32_t>(p.n_tokens);
     if (!live) tok = 0;  // the other half of the warp still needs this half in its shuffles
+    // head of the only dependent load chain (position -> cos/sin row): issue it first
+    const float* cs_row = cos_sin_row(p.nr, tok);
     const uint8_t* src = static_cast<const uint8_t*>(p.qkv) +
                          static_cast<int64_t>(tok) * p.qkv_row_stride * 2 + c * 16;
 #pragma unroll
@@ -92,7 +94,7 @@ qk_norm_rope_store_kernel(const QkNormRopeParams p, uint32_t qk_blocks, uint32_t
         wq = *reinterpret_cast<const uint4*>(static_cast<const uint8_t*>(p.nr.q_weight) + c * 16);
         wk = *reinterpret_cast<const uint4*>(static_cast<const uint8_t*>(p.nr.k_weight) + c * 16);
     }
-    const CosSin8 cs = load_cos_sin8(cos_sin_row(p.nr, tok), c);
+    const CosSin8 cs = load_cos_sin8(cs_row, c);
     int64_t slot = p.slot_mapping != nullptr ? p.slot_mapping[tok] : -1;
     if (slot >= p.num_slots) slot = -1;
     uint8_t* q_dst = static_cast<uint8_t*>(p.q_out) + static_cast<int64_t>(tok) * Hq * 256 + c * 16;

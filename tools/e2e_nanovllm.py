@@ -166,6 +166,8 @@ def main():
     ap.add_argument("--check", action="store_true",
                     help="also dump near-greedy tokens of 8 short prompts for cross-arm comparison")
     ap.add_argument("--out", default=None)
+    ap.add_argument("--cprofile", action="store_true",
+                    help="run the timed generate under cProfile and print the host-side hot spots")
     ap.add_argument("--profile", action="store_true",
                     help="torch.profiler table of a short generate instead of the benchmark")
     args = ap.parse_args()
@@ -239,8 +241,19 @@ def main():
         phase[k] = 0 if isinstance(phase[k], int) else 0.0
     torch.cuda.synchronize()
     t = time.time()
-    llm.generate(prompts, sps, use_tqdm=False)
-    t = time.time() - t
+    if args.cprofile:
+        import cProfile
+        import pstats
+
+        prof = cProfile.Profile()
+        prof.runcall(llm.generate, prompts, sps, use_tqdm=False)
+        t = time.time() - t
+        for key in ("tottime", "cumulative"):
+            print(f"==== cProfile by {key} ====", flush=True)
+            pstats.Stats(prof).sort_stats(key).print_stats(28)
+    else:
+        llm.generate(prompts, sps, use_tqdm=False)
+        t = time.time() - t
     total = sum(sp.max_tokens for sp in sps)
 
     line = {
