@@ -19,7 +19,7 @@ BUILD_DIR = PKG_DIR / "_build"
 LIB_PATH = PKG_DIR / "libb200attn.so"
 
 SOURCES = ["store_kv.cu", "decode_attn.cu", "prefill_attn.cu", "prefill_tc.cu", "cascade.cu",
-           "qk_norm_rope.cu", "api.cu"]
+           "qk_norm_rope.cu", "prepare_meta.cu", "api.cu"]
 HEADERS = ["common.h", "ptx.cuh", "tcgen05.cuh", "norm_rope.cuh", "../../include/b200attn.h"]
 
 NVCC_FLAGS = [

@@ -630,4 +630,34 @@ int b200attn_qkv_decode(const void* qkv, int64_t qkv_row_stride, const int64_t* 
                              num_splits, nullptr, 0, dtype, stream, &nr);
 }
 
+int b200attn_prepare_decode(const int32_t* packed, int32_t batch, int32_t table_width,
+                            int32_t block_size, int64_t* input_ids, int64_t* positions,
+                            int32_t* slot_mapping, int32_t* context_lens, int32_t* block_tables,
+                            int64_t table_row_stride, int32_t capacity, void* stream) {
+    if (batch < 0 || capacity < batch || table_width < 0 || block_size <= 0)
+        return fail(B200ATTN_E_BADARG, "bad sizes (batch %d, capacity %d, table_width %d)", batch,
+                    capacity, table_width);
+    if (batch > 1024) return fail(B200ATTN_E_UNSUPPORTED, "batch %d > 1024", batch);
+    if (capacity == 0) return 0;
+    if (!slot_mapping || !context_lens) return fail(B200ATTN_E_BADARG, "null pointer");
+    if (batch > 0 && (!packed || !input_ids || !positions || !block_tables))
+        return fail(B200ATTN_E_BADARG, "null pointer");
+    if (table_row_stride < table_width)
+        return fail(B200ATTN_E_BADARG, "table_row_stride smaller than table_width");
+    b200::PrepareDecodeParams p{};
+    p.packed = packed;
+    p.input_ids = input_ids;
+    p.positions = positions;
+    p.slot_mapping = slot_mapping;
+    p.context_lens = context_lens;
+    p.block_tables = block_tables;
+    p.table_row_stride = table_row_stride;
+    p.batch = batch;
+    p.capacity = capacity;
+    p.table_width = table_width;
+    p.block_size = block_size;
+    cudaError_t e = b200::launch_prepare_decode(p, static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? 0 : cuda_fail(e, "prepare_decode launch");
+}
+
 }  // extern "C"

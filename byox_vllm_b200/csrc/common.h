@@ -38,6 +38,22 @@ struct QkNormRopeParams {
 };
 cudaError_t launch_qk_norm_rope_store(const QkNormRopeParams& p, cudaStream_t stream);
 
+// ---- prepare_meta.cu -------------------------------------------------------------------------
+struct PrepareDecodeParams {
+    const int32_t* packed;  // device: last_token[B] | num_tokens[B] | table_len[B] | blocks[sum]
+    int64_t* input_ids;     // [capacity]
+    int64_t* positions;     // [capacity]
+    int32_t* slot_mapping;  // [capacity]
+    int32_t* context_lens;  // [capacity]
+    int32_t* block_tables;  // [capacity, table_row_stride]
+    int64_t table_row_stride;
+    int32_t batch;
+    int32_t capacity;
+    int32_t table_width;
+    int32_t block_size;
+};
+cudaError_t launch_prepare_decode(const PrepareDecodeParams& p, cudaStream_t stream);
+
 // ---- decode_attn.cu --------------------------------------------------------------------------
 struct DecodeParams {
     const void* q;                // [B, Hq, 128] bf16

@@ -1,0 +1,162 @@
+"""decode-step metadata built on the device.
+
+The reference forms the decode metadata on the host every step — five Python lists, five pinned
+tensors, five H2D copies (engine/model_runner.py:206-226, :152-158) — and then refreshes the
+CUDA-graph input buffers with seven more small device ops (:242-254). Here the host packs ONE
+compact int32 record
+
+    last_token[B] | num_tokens[B] | table_len[B] | blocks[sum(table_len)]
+
+into a pinned staging buffer, copies it with one cudaMemcpyAsync, and one launch of
+b200attn_prepare_decode (csrc/prepare_meta.cu) writes input_ids / positions / slot_mapping /
+context_lens / block_tables straight into the graph input buffers, bit-identically.
+
+  pack_decode_record(...)      host packing (numpy), shared by the tests
+  DecodeMetaStager             pinned double buffer + device record + the launch
+  prepare_decode / run_model   drop-ins for ModelRunner._prepare_decode / _run_model
+                               (bound by install.install(fast_meta=True))
+"""
+from __future__ import annotations
+
+from itertools import chain
+
+import numpy as np
+import torch
+
+from . import _lib
+
+
+def pack_decode_record(last_tokens, num_tokens, block_tables, out: np.ndarray | None = None):
+    """-> (record int32[3B + sum(len)], table_width). `block_tables`: one list per sequence."""
+    B = len(last_tokens)
+    lens = [len(t) for t in block_tables]
+    total = 3 * B + sum(lens)
+    if out is None:
+        out = np.empty(total, dtype=np.int32)
+    assert out.dtype == np.int32 and out.size >= total
+    out[:B] = last_tokens
+    out[B:2 * B] = num_tokens
+    out[2 * B:3 * B] = lens
+    out[3 * B:total] = np.fromiter(chain.from_iterable(block_tables), dtype=np.int32,
+                                   count=total - 3 * B)
+    return out[:total], (max(lens) if lens else 0)
+
+
+class DecodeMetaStager:
+    """Owns the staging buffers for one set of graph input buffers (ModelRunner.graph_vars)."""
+
+    def __init__(self, input_ids: torch.Tensor, positions: torch.Tensor,
+                 slot_mapping: torch.Tensor, context_lens: torch.Tensor,
+                 block_tables: torch.Tensor, block_size: int):
+        for t in (input_ids, positions, slot_mapping, context_lens, block_tables):
+            if not t.is_cuda:
+                raise RuntimeError("DecodeMetaStager needs CUDA graph-input buffers; no CPU path")
+        assert input_ids.dtype == torch.int64 and positions.dtype == torch.int64
+        assert slot_mapping.dtype == torch.int32 and context_lens.dtype == torch.int32
+        assert block_tables.dtype == torch.int32 and block_tables.dim() == 2
+        assert block_tables.stride(1) == 1
+        self.capacity = min(input_ids.numel(), positions.numel(), slot_mapping.numel(),
+                            context_lens.numel(), block_tables.size(0))
+        self.max_width = block_tables.size(1)
+        self.block_size = block_size
+        self.bufs = (input_ids, positions, slot_mapping, context_lens, block_tables)
+        n = self.capacity * (3 + self.max_width)
+        self.device = input_ids.device
+        self._dev = torch.empty(n, dtype=torch.int32, device=self.device)
+        # two pinned buffers: the copy of step t may still be in flight while step t+1 is packed
+        self._pinned = [torch.empty(n, dtype=torch.int32, pin_memory=True) for _ in range(2)]
+        self._np = [p.numpy() for p in self._pinned]
+        self._events = [torch.cuda.Event(), torch.cuda.Event()]
+        self._used = [False, False]
+        self._turn = 0
+
+    def fits(self, batch: int, table_width: int) -> bool:
+        return 0 < batch <= min(self.capacity, 1024) and table_width <= self.max_width
+
+    def stage(self, last_tokens, num_tokens, block_tables) -> tuple[int, int]:
+        """Pack, copy and expand. Returns (batch, table_width). Asynchronous on the current
+        stream."""
+        i = self._turn
+        self._turn ^= 1
+        if self._used[i]:
+            self._events[i].synchronize()
+        rec, width = pack_decode_record(last_tokens, num_tokens, block_tables, self._np[i])
+        B = len(last_tokens)
+        if not self.fits(B, width):
+            raise ValueError(f"batch {B} x table width {width} exceeds the staged buffers")
+        n = rec.size
+        self._dev[:n].copy_(self._pinned[i][:n], non_blocking=True)
+        self._events[i].record()
+        self._used[i] = True
+        input_ids, positions, slot_mapping, context_lens, block_tables_d = self.bufs
+        lib = _lib.load()
+        rc = lib.b200attn_prepare_decode(
+            self._dev.data_ptr(), B, width, self.block_size, input_ids.data_ptr(),
+            positions.data_ptr(), slot_mapping.data_ptr(), context_lens.data_ptr(),
+            block_tables_d.data_ptr(), block_tables_d.stride(0), self.capacity,
+            torch.cuda.current_stream(self.device).cuda_stream)
+        _lib.check("b200attn_prepare_decode", rc)
+        return B, width
+
+
+# ---- drop-ins for the reference's ModelRunner (bound by install.py) ----------------------------
+_ORIG = {}
+
+
+def _stager_of(runner):
+    st = getattr(runner, "_b200_meta_stager", None)
+    if st is None and getattr(runner, "graph_vars", None) is not None:
+        gv = runner.graph_vars
+        st = DecodeMetaStager(gv["input_ids"], gv["positions"], gv["slot_mapping"],
+                              gv["context_lens"], gv["block_tables"], runner.block_size)
+        runner._b200_meta_stager = st
+    return st
+
+
+def prepare_decode(self, seqs):
+    """ModelRunner._prepare_decode (model_runner.py:206-226) writing the graph inputs directly."""
+    import sys
+
+    from . import attention as _attn
+
+    # the Context module install() bound (nanovllm.utils.context), else our standalone mirror
+    set_context = sys.modules[_attn.get_context.__module__].set_context
+    st = None if self.enforce_eager else _stager_of(self)
+    bs = len(seqs)
+    tables = [seq.block_table for seq in seqs]
+    if st is None or not st.fits(bs, max(map(len, tables))):
+        return _ORIG["_prepare_decode"](self, seqs)
+    _, width = st.stage([seq.last_token for seq in seqs], [seq.num_tokens for seq in seqs], tables)
+    gv = self.graph_vars
+    set_context(False, slot_mapping=gv["slot_mapping"][:bs], context_lens=gv["context_lens"][:bs],
+                block_tables=gv["block_tables"][:bs, :width])
+    self._b200_meta_staged = bs
+    return gv["input_ids"][:bs], gv["positions"][:bs]
+
+
+@torch.inference_mode()
+def run_model(self, input_ids, positions, is_prefill):
+    """ModelRunner._run_model (model_runner.py:228-254): when prepare_decode above already filled
+    the graph inputs, replay the graph without the seven refresh copies."""
+    staged = getattr(self, "_b200_meta_staged", 0)
+    self._b200_meta_staged = 0
+    if is_prefill or not staged or staged != input_ids.size(0):
+        return _ORIG["_run_model"](self, input_ids, positions, is_prefill)
+    bs = staged
+    graph = self.graphs[next(x for x in self.graph_bs if x >= bs)]
+    graph.replay()
+    return self.model.compute_logits(self.graph_vars["outputs"][:bs])
+
+
+def bind(model_runner_cls) -> None:
+    if "_prepare_decode" not in _ORIG:
+        _ORIG["_prepare_decode"] = model_runner_cls._prepare_decode
+        _ORIG["_run_model"] = model_runner_cls._run_model
+    model_runner_cls._prepare_decode = prepare_decode
+    model_runner_cls._run_model = run_model
+
+
+def unbind(model_runner_cls) -> None:
+    if "_prepare_decode" in _ORIG:
+        model_runner_cls._prepare_decode = _ORIG.pop("_prepare_decode")
+        model_runner_cls._run_model = _ORIG.pop("_run_model")

@@ -13,6 +13,10 @@ The reference binds the op by name: `from nanovllm.layers.attention import Atten
      frozen Attention.forward boundary) rebinds Qwen3Attention.forward (models/qwen3.py:70-86) to
      qkv_attention.qwen3_attention_forward: q/k RMSNorm + RoPE + KV scatter (+ the paged decode)
      become one library call on the raw qkv_proj output.
+  5. (`fast_meta`, default on; B200ATTN_FAST_META=0 or fast_meta=False disables)
+     rebinds ModelRunner._prepare_decode / _run_model (engine/model_runner.py:206-254) to
+     fast_meta.prepare_decode / run_model: the decode metadata is expanded on the device into the
+     CUDA-graph input buffers by one copy + one launch.
 For tensor parallel runs nanovllm spawns ranks with multiprocessing "spawn"
 (engine/llm_engine.py:24-31): call install() at module top level of the launcher script so each
 spawned rank re-applies it on import of __main__.
@@ -26,11 +30,14 @@ import sys
 _ORIG_QWEN3_FORWARD = None
 
 
-def install(verbose: bool = False, fuse_qkv: bool | None = None) -> None:
+def install(verbose: bool = False, fuse_qkv: bool | None = None,
+            fast_meta: bool | None = None) -> None:
     from . import attention as ours
 
     if fuse_qkv is None:
         fuse_qkv = os.environ.get("B200ATTN_FUSE_QKV", "1") != "0"
+    if fast_meta is None:
+        fast_meta = os.environ.get("B200ATTN_FAST_META", "1") != "0"
 
     ref_ctx = importlib.import_module("nanovllm.utils.context")
     ours.get_context = ref_ctx.get_context
@@ -52,9 +59,21 @@ def install(verbose: bool = False, fuse_qkv: bool | None = None) -> None:
         elif cls.forward is not fused.qwen3_attention_forward:
             _ORIG_QWEN3_FORWARD = cls.forward
             cls.forward = fused.qwen3_attention_forward
+    if fast_meta:
+        try:
+            mr = importlib.import_module("nanovllm.engine.model_runner")
+        except ImportError:
+            mr = None
+        if mr is not None and hasattr(mr, "ModelRunner"):
+            from . import fast_meta as fm
+
+            fm.bind(mr.ModelRunner)
+        else:
+            fast_meta = False
     if verbose:
         print("[byox_vllm_b200] nanovllm.layers.attention -> byox_vllm_b200.attention"
-              + (" (+ fused qkv path)" if fuse_qkv else ""), file=sys.stderr)
+              + (" (+ fused qkv path)" if fuse_qkv else "")
+              + (" (+ device-side decode metadata)" if fast_meta else ""), file=sys.stderr)
 
 
 def uninstall() -> None:
@@ -67,5 +86,10 @@ def uninstall() -> None:
     if qwen3 is not None and _ORIG_QWEN3_FORWARD is not None and hasattr(qwen3, "Qwen3Attention"):
         qwen3.Qwen3Attention.forward = _ORIG_QWEN3_FORWARD
         _ORIG_QWEN3_FORWARD = None
+    mr = sys.modules.get("nanovllm.engine.model_runner")
+    if mr is not None and hasattr(mr, "ModelRunner"):
+        from . import fast_meta as fm
+
+        fm.unbind(mr.ModelRunner)
     if sys.modules.get("nanovllm.layers.attention") is ours:
         del sys.modules["nanovllm.layers.attention"]

@@ -19,6 +19,9 @@
  *                              (layers/rotary_embedding.py:37-48) and store_kvcache in one pass
  *                              over the QKV projection output
  *   b200attn_qkv_decode        the same four steps + the paged decode (:87-96) in ONE launch
+ *   b200attn_prepare_decode    nanovllm/engine/model_runner.py:206-226 (_prepare_decode),
+ *                              :152-158 (_prepare_block_tables) and the graph-variable refresh of
+ *                              _run_model :242-254, expanded on the device
  *
  * Conventions
  *   - Plain pointers and sizes only; all buffers are DEVICE pointers owned by the caller (torch
@@ -42,7 +45,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 4
+#define B200ATTN_ABI_VERSION 5
 
 #define B200ATTN_DTYPE_BF16 0
 
@@ -234,6 +237,28 @@ int b200attn_qkv_decode(const void* qkv, int64_t qkv_row_stride, const int64_t* 
                         int32_t num_kv_heads, int32_t head_dim, int32_t block_size,
                         int64_t num_blocks, float scale, int32_t num_splits, int32_t dtype,
                         void* stream);
+
+/*
+ * Decode-step metadata expansion. `packed` is a DEVICE int32 array the caller
+ * filled with one host->device copy:
+ *     last_token[batch] | num_tokens[batch] | table_len[batch] | blocks[sum(table_len)]
+ * (blocks = every sequence's block_table back to back). One launch writes, bit-identically to
+ * what ModelRunner._prepare_decode + _run_model leave in the CUDA-graph input buffers:
+ *     input_ids[b]    = last_token[b]                       (int64)      b < batch
+ *     positions[b]    = num_tokens[b] - 1                   (int64)
+ *     context_lens[b] = num_tokens[b]
+ *     slot_mapping[b] = block_table_b[-1] * block_size + last_block_num_tokens_b - 1
+ *                       with last_block_num_tokens = num_tokens - (ceil(num_tokens / block_size)
+ *                       - 1) * block_size          (engine/sequence.py:62-68, model_runner.py:215)
+ *     block_tables[b, j] = block_table_b[j] for j < table_len[b], -1 for table_len[b] <= j <
+ *                       table_width; columns >= table_width are left untouched
+ *     slot_mapping[b] = -1, context_lens[b] = 0             batch <= b < capacity
+ * batch <= 1024, table_len[b] <= table_width. All output buffers hold `capacity` rows.
+ */
+int b200attn_prepare_decode(const int32_t* packed, int32_t batch, int32_t table_width,
+                            int32_t block_size, int64_t* input_ids, int64_t* positions,
+                            int32_t* slot_mapping, int32_t* context_lens, int32_t* block_tables,
+                            int64_t table_row_stride, int32_t capacity, void* stream);
 
 #ifdef __cplusplus
 }

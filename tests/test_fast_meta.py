@@ -1,0 +1,147 @@
+"""device-side decode metadata. CPU part: the host packing; GPU part: the kernel
+against the restated builders (byox_vllm_b200.metadata, pinned by the reference's own expectations
+in tests/test_prepare_funcs.py:83-143,169-206 — see tests/test_metadata.py) — bit-exact."""
+import random
+
+import numpy as np
+import pytest
+import torch
+
+from byox_vllm_b200 import fast_meta as fm, metadata as md
+
+
+def test_pack_decode_record_layout():
+    rec, width = fm.pack_decode_record([7, 9, 11], [5, 300, 17], [[3], [8, 2], [4]])
+    assert rec.dtype == np.int32 and width == 2
+    assert rec.tolist() == [7, 9, 11, 5, 300, 17, 1, 2, 1, 3, 8, 2, 4]
+    buf = np.full(64, -7, dtype=np.int32)
+    rec2, _ = fm.pack_decode_record([7, 9, 11], [5, 300, 17], [[3], [8, 2], [4]], buf)
+    assert rec2.tolist() == rec.tolist() and rec2.base is buf and buf[13] == -7
+    rec, width = fm.pack_decode_record([], [], [])
+    assert rec.size == 0 and width == 0
+
+
+def _run(dev, last, ntok, tables, block_size, capacity, max_width, stale=12345):
+    ids = torch.full((capacity,), stale, dtype=torch.int64, device=dev)
+    pos = torch.full((capacity,), stale, dtype=torch.int64, device=dev)
+    slot = torch.full((capacity,), stale, dtype=torch.int32, device=dev)
+    lens = torch.full((capacity,), stale, dtype=torch.int32, device=dev)
+    bt = torch.full((capacity, max_width), stale, dtype=torch.int32, device=dev)
+    st = fm.DecodeMetaStager(ids, pos, slot, lens, bt, block_size)
+    B, W = st.stage(last, ntok, tables)
+    torch.cuda.synchronize()
+    return ids.cpu(), pos.cpu(), slot.cpu(), lens.cpu(), bt.cpu(), B, W, st
+
+
+def _check(dev, last, ntok, tables, block_size, capacity, max_width):
+    stale = 12345
+    ids, pos, slot, lens, bt, B, W, _ = _run(dev, last, ntok, tables, block_size, capacity,
+                                             max_width, stale)
+    want = md.prepare_decode([md.SeqState(n, list(t)) for n, t in zip(ntok, tables)], block_size)
+    assert W == want["block_tables"].size(1)
+    assert torch.equal(ids[:B], torch.tensor(last, dtype=torch.int64))
+    assert torch.equal(pos[:B], want["positions"])
+    assert torch.equal(slot[:B], want["slot_mapping"])
+    assert torch.equal(lens[:B], want["context_lens"])
+    assert torch.equal(bt[:B, :W], want["block_tables"])
+    # what _run_model's fill_(-1) / zero_() leave in the padding rows (model_runner.py:248-251)
+    assert bool((slot[B:] == -1).all()) and bool((lens[B:] == 0).all())
+    # untouched: ids / positions of padding rows, table columns >= W and padding table rows
+    assert bool((ids[B:] == stale).all()) and bool((pos[B:] == stale).all())
+    assert bool((bt[:, W:] == stale).all()) and bool((bt[B:] == stale).all())
+
+
+@pytest.mark.gpu
+def test_reference_expectations_block16(cuda_dev):
+    """The cases of the reference's tests/test_prepare_funcs.py (block_size 16; its mocks leave -1
+    as the LAST table entry, which makes the slot negative: block_table[-1] is what counts)."""
+    _check(cuda_dev, [5], [5], [[0, -1, -1, -1]], 16, 8, 4)            # :83-101  slot -12
+    _check(cuda_dev, [3, 7], [3, 4], [[0, -1, -1, -1], [1, -1, -1, -1]], 16, 8, 6)  # :104-143
+    _check(cuda_dev, [4, 9], [4, 5], [[0, -1, -1, -1], [1, -1, -1, -1]], 16, 2, 4)  # :169-206
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("batch,block_size,max_len,capacity", [
+    (1, 256, 4096, 512), (3, 256, 1000, 16), (256, 256, 4096, 512), (512, 256, 4096, 512),
+    (511, 64, 40960, 512), (1000, 256, 2048, 1024)])
+def test_prepare_decode_matches_reference_builders(cuda_dev, batch, block_size, max_len, capacity):
+    rng = random.Random(batch)
+    ntok = [rng.randint(1, max_len) for _ in range(batch)]
+    # page-boundary rows: exactly full page, first token of a new page
+    for i, n in enumerate((block_size, block_size + 1, 1, max_len)):
+        if i < batch:
+            ntok[i] = n
+    tables = [[rng.randrange(1 << 22) for _ in range((n + block_size - 1) // block_size)]
+              for n in ntok]
+    last = [rng.randint(0, 151935) for _ in range(batch)]
+    _check(cuda_dev, last, ntok, tables, block_size, capacity,
+           (max_len + block_size - 1) // block_size + 2)
+
+
+@pytest.mark.gpu
+def test_stager_reuse_and_model_runner_dropins(cuda_dev):
+    """Two consecutive steps through the same stager (pinned double buffer), then the ModelRunner
+    drop-ins on a stand-in runner: the Context carries slices of the graph inputs, the graph is
+    replayed without the refresh copies, and an oversized batch falls back to the original."""
+    from byox_vllm_b200 import attention as attn_mod
+    from byox_vllm_b200.context import reset_context
+
+    dev = cuda_dev
+    cap, width = 16, 8
+    gv = dict(input_ids=torch.zeros(cap, dtype=torch.int64, device=dev),
+              positions=torch.zeros(cap, dtype=torch.int64, device=dev),
+              slot_mapping=torch.zeros(cap, dtype=torch.int32, device=dev),
+              context_lens=torch.zeros(cap, dtype=torch.int32, device=dev),
+              block_tables=torch.zeros(cap, width, dtype=torch.int32, device=dev),
+              outputs=torch.arange(cap, dtype=torch.float32, device=dev).view(cap, 1))
+
+    class Seq:
+        def __init__(self, n, table, tok):
+            self.num_tokens, self.block_table, self.last_token = n, table, tok
+
+    class Graph:
+        replays = 0
+
+        def replay(self):
+            Graph.replays += 1
+
+    class Runner:
+        enforce_eager = False
+        block_size = 256
+        graph_vars = gv
+        graph_bs = [1, 2, 4, 8, 16]
+        graphs = {b: Graph() for b in graph_bs}
+        model = type("M", (), {"compute_logits": staticmethod(lambda x: x)})()
+
+    calls = []
+    fm._ORIG["_prepare_decode"] = lambda self, seqs: calls.append("prepare") or ("ids", "pos")
+    fm._ORIG["_run_model"] = lambda self, i, p, pre: calls.append("run") or "orig"
+    try:
+        r = Runner()
+        for step in range(3):
+            seqs = [Seq(300 + step, [5, 9], 11 + step), Seq(256 + step, [7] + [3] * (step > 0), 4),
+                    Seq(17, [2], 6)]
+            ids, pos = fm.prepare_decode(r, seqs)
+            ctx = attn_mod.get_context()
+            torch.cuda.synchronize()
+            want = md.prepare_decode([md.SeqState(s.num_tokens, s.block_table) for s in seqs], 256)
+            assert ids.data_ptr() == gv["input_ids"].data_ptr() and ids.size(0) == 3
+            assert ids.tolist() == [s.last_token for s in seqs]
+            assert torch.equal(pos.cpu(), want["positions"])
+            assert not ctx.is_prefill
+            assert ctx.slot_mapping.data_ptr() == gv["slot_mapping"].data_ptr()
+            assert torch.equal(ctx.slot_mapping.cpu(), want["slot_mapping"])
+            assert torch.equal(ctx.context_lens.cpu(), want["context_lens"])
+            assert torch.equal(ctx.block_tables.cpu(), want["block_tables"])
+            assert gv["slot_mapping"][3:].tolist() == [-1] * (cap - 3)
+            out = fm.run_model(r, ids, pos, False)
+            assert Graph.replays == step + 1 and out.shape == (3, 1) and calls == []
+        # prefill and unstaged calls go to the original
+        assert fm.run_model(r, ids, pos, True) == "orig"
+        assert fm.run_model(r, ids, pos, False) == "orig"  # nothing staged any more
+        big = [Seq(5, [1], 2) for _ in range(cap + 1)]
+        assert fm.prepare_decode(r, big) == ("ids", "pos")
+        assert calls == ["run", "run", "prepare"]
+    finally:
+        fm._ORIG.clear()
+        reset_context()

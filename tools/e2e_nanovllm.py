@@ -262,6 +262,7 @@ def main():
         "out": args.fixed_out or [100, args.max_out], "max_model_len": args.max_model_len,
         "shared_prefix": args.shared_prefix, "cascade_env": os.environ.get("B200ATTN_CASCADE"),
         "fuse_qkv_env": os.environ.get("B200ATTN_FUSE_QKV"),
+        "fast_meta_env": os.environ.get("B200ATTN_FAST_META"),
         "cuda_graphs": not args.eager, "total_output_tokens": total, "seconds": t,
         "tokens_per_s": total / t, "init_s": t_init,
         "decode_tokens_per_s": phase["decode_tokens"] / max(phase["decode_s"], 1e-9),
