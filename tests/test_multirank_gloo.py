@@ -37,6 +37,25 @@ def _worker(rank, world, port, q):
         full = orc.paged_decode_ref(c.q, c.k_cache, c.v_cache, c.meta["context_lens"],
                                     c.meta["block_tables"], c.scale)
         ok = torch.allclose(torch.cat(parts, dim=1), full, atol=1e-6)
+        # the fused step before the path shards the same way: rank r's QKV rows hold
+        # its own q / k / v heads (QKVParallelLinear, linear.py:92-123), the norm weights and the
+        # cos/sin table are replicated, so the rank-local result is the head slice of the full one
+        gen = torch.Generator().manual_seed(3)
+        D, n = 128, 5
+        qf = torch.randn(n, Hq, D, generator=gen).to(torch.bfloat16)
+        kf = torch.randn(n, Hkv, D, generator=gen).to(torch.bfloat16)
+        vf = torch.randn(n, Hkv, D, generator=gen).to(torch.bfloat16)
+        wq = (1 + 0.2 * torch.randn(D, generator=gen)).to(torch.bfloat16)
+        wk = (1 + 0.2 * torch.randn(D, generator=gen)).to(torch.bfloat16)
+        pos = torch.tensor([0, 7, 4095, 300, 1])
+        cache = orc.rope_cos_sin_cache(D, 4096, 1e6)
+        pack = lambda a, b, c_: torch.cat([a.flatten(1), b.flatten(1), c_.flatten(1)], dim=1)
+        q_all, k_all, _ = orc.qk_norm_rope_ref(pack(qf, kf, vf), pos, wq, wk, 1e-6, cache, Hq, Hkv)
+        qs_, ks_ = slice(sh.q_head_start, sh.q_head_start + sh.num_q_heads), slice(
+            sh.kv_head_start, sh.kv_head_start + sh.num_kv_heads)
+        q_loc, k_loc, _ = orc.qk_norm_rope_ref(pack(qf[:, qs_], kf[:, ks_], vf[:, ks_]), pos, wq,
+                                               wk, 1e-6, cache, sh.num_q_heads, sh.num_kv_heads)
+        ok = ok and torch.equal(q_loc, q_all[:, qs_]) and torch.equal(k_loc, k_all[:, ks_])
         t = parallel.max_over_ranks(10.0 + rank)
         q.put((rank, bool(ok), t, sh.group))
     finally:
