@@ -73,6 +73,26 @@ def store_kvcache(key: torch.Tensor, value: torch.Tensor, k_cache: torch.Tensor,
     _lib.check("b200attn_store_kvcache", rc)
 
 
+_SPLIT_COUNTERS: dict[int, torch.Tensor] = {}
+_SPLIT_COUNTER_SLOTS = 1 << 16  # (sequence, KV head) pairs; 256 KiB per device
+
+
+def ensure_split_counters(device: torch.device) -> None:
+    """Register the zeroed arrival counters that let split-KV decode merge inside its own launch
+    (b200attn_set_split_counters). Allocated once per device, outside any graph capture (the
+    reference warms every batch size up eagerly before capturing it, model_runner.py:281), kept
+    alive for the life of the process; every launch leaves them zero."""
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    if idx in _SPLIT_COUNTERS or torch.cuda.is_current_stream_capturing():
+        return
+    with torch.cuda.device(idx):
+        buf = torch.zeros(_SPLIT_COUNTER_SLOTS, dtype=torch.int32, device=device)
+        torch.cuda.current_stream(device).synchronize()
+        rc = _lib.load().b200attn_set_split_counters(buf.data_ptr(), buf.numel())
+    _lib.check("b200attn_set_split_counters", rc)
+    _SPLIT_COUNTERS[idx] = buf
+
+
 def decode_num_splits(batch: int, num_kv_heads: int, table_width: int, block_size: int) -> int:
     """Host-only split heuristic (a function of host-visible sizes: graph-capture rule)."""
     lib = _lib.load()
@@ -151,6 +171,8 @@ def paged_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
     else:
         assert plan.dtype == torch.int32 and plan.numel() >= 4 and plan.is_cuda
     ws, ws_bytes = None, 0
+    if num_splits > 1:
+        ensure_split_counters(q.device)
     if num_splits + prefix_chunks > 1:
         ws_bytes = lib.b200attn_decode_workspace_bytes(B, Hq, D, num_splits + prefix_chunks)
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=q.device)

@@ -159,6 +159,30 @@ int check_attn_shape(int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim
 
 }  // namespace
 
+// Caller-registered arrival counters for the in-launch split merge, per device.
+struct SplitCounters {
+    int32_t* ptr = nullptr;
+    int64_t count = 0;
+};
+static SplitCounters g_split_counters[64];
+static std::mutex g_split_counters_mu;
+
+static int32_t* split_counters_for(int64_t need) {
+    static const bool enabled = [] {
+        const char* e = std::getenv("B200ATTN_FUSED_MERGE");
+        return !(e && e[0] == '0');
+    }();
+    if (!enabled) return nullptr;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
+        (void)cudaGetLastError();
+        return nullptr;
+    }
+    std::lock_guard<std::mutex> lock(g_split_counters_mu);
+    const SplitCounters& c = g_split_counters[dev];
+    return (c.ptr != nullptr && c.count >= need) ? c.ptr : nullptr;
+}
+
 // Shared body of every decode entry point. `nr` != nullptr: q / key are raw QKV-projection rows
 // (q rows q_row_stride elements apart) and the kernel applies q/k RMSNorm + RoPE itself.
 static int store_decode_impl(const void* q, int64_t q_row_stride, const void* key,
@@ -263,6 +287,8 @@ static int store_decode_impl(const void* q, int64_t q_row_stride, const void* ke
     }
     p.plan = plan;
     p.prefix_chunks = prefix_chunks;
+    if (num_splits > 1)
+        p.split_counters = split_counters_for(static_cast<int64_t>(batch) * num_kv_heads);
     if (prefix_chunks > 0) {
         // Shared-prefix pass first (tcgen05): B*G query rows of every KV head against the P
         // shared pages, partials into workspace slots [num_splits, num_splits + prefix_chunks).
@@ -658,6 +684,21 @@ int b200attn_prepare_decode(const int32_t* packed, int32_t batch, int32_t table_
     p.block_size = block_size;
     cudaError_t e = b200::launch_prepare_decode(p, static_cast<cudaStream_t>(stream));
     return e == cudaSuccess ? 0 : cuda_fail(e, "prepare_decode launch");
+}
+
+int b200attn_set_split_counters(void* counters, int64_t count) {
+    if (count < 0 || (counters == nullptr) != (count == 0))
+        return fail(B200ATTN_E_BADARG, "counters and count must be given together");
+    if (counters && (reinterpret_cast<uintptr_t>(counters) & 3u))
+        return fail(B200ATTN_E_BADARG, "counters must be 4-byte aligned");
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetDevice");
+    if (dev < 0 || dev >= 64) return fail(B200ATTN_E_UNSUPPORTED, "device %d out of range", dev);
+    std::lock_guard<std::mutex> lock(g_split_counters_mu);
+    g_split_counters[dev].ptr = static_cast<int32_t*>(counters);
+    g_split_counters[dev].count = count;
+    return 0;
 }
 
 }  // extern "C"

@@ -90,6 +90,10 @@ struct DecodeParams {
     // loaded into registers, the new K row while it is scattered (needs new_key / slot_mapping).
     int64_t q_row_stride;  // elements between q rows of consecutive sequences
     NormRopeArgs nr;
+    // optional in-launch merge (num_splits > 1): zeroed int32 arrival counters, one per
+    // (sequence, KV head); the split CTA that arrives last merges the partials itself and resets
+    // the counter, so no merge kernel is launched. nullptr => separate decode_merge_kernel.
+    int32_t* split_counters;
 };
 cudaError_t launch_decode(const DecodeParams& p, const CUtensorMap& k_map, const CUtensorMap& v_map,
                           cudaStream_t stream);

@@ -45,6 +45,84 @@ __device__ __forceinline__ void consumer_bar_sync() {
     asm volatile("bar.sync 1, %0;" ::"n"(kConsumerWarps * 32) : "memory");
 }
 
+// Combine S normalised partials (fp32 O_s, log2-domain lse_s) of one (b, q-head) row into out:
+// one warp per row, 4 dims per lane. lane s (and s + 32, s + 64) holds the weight of slot s; the
+// partial loads of 8 slots are issued together so their latencies overlap (S <= 64 + 32 slots).
+// Loads go through L2 (ld.global.cg): when the last-arriving split CTA merges in the same launch,
+// the partials were written by other SMs a moment ago.
+__device__ __forceinline__ void merge_row(const float* __restrict__ ws_o,
+                                          const float* __restrict__ ws_lse,
+                                          __nv_bfloat16* __restrict__ out, int64_t row, int S,
+                                          int St, int lane) {
+    const float* lse = ws_lse + row * St;
+    float my_lse[3], my_w[3];
+    float mx = -INFINITY;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        my_lse[i] = lane + 32 * i < S ? __ldcg(lse + lane + 32 * i) : -INFINITY;
+        mx = fmaxf(mx, my_lse[i]);
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+    float wsum = 0.f;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        my_w[i] = my_lse[i] == -INFINITY ? 0.f : fast_exp2(my_lse[i] - mx);  // empty: weight 0
+        wsum += my_w[i];
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) wsum += __shfl_xor_sync(0xffffffffu, wsum, off);
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    const float4* po = reinterpret_cast<const float4*>(ws_o + row * St * kHeadDim) + lane;
+    for (int s0 = 0; s0 < S; s0 += 8) {
+        float4 x[8];
+        float w[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int sl = s0 + u;
+            const float wa = __shfl_sync(0xffffffffu, my_w[0], sl & 31);
+            const float wb = __shfl_sync(0xffffffffu, my_w[1], sl & 31);
+            const float wc = __shfl_sync(0xffffffffu, my_w[2], sl & 31);
+            w[u] = sl < S ? (sl < 32 ? wa : (sl < 64 ? wb : wc)) : 0.f;
+            // an empty slot (weight 0) was never written: do not read it
+            x[u] = w[u] != 0.f ? __ldcg(po + sl * (kHeadDim / 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            acc.x += w[u] * x[u].x;
+            acc.y += w[u] * x[u].y;
+            acc.z += w[u] * x[u].z;
+            acc.w += w[u] * x[u].w;
+        }
+    }
+    const float inv = wsum > 0.f ? 1.f / wsum : 0.f;
+    uint2 pk;
+    pk.x = pack_bf16x2(acc.x * inv, acc.y * inv);
+    pk.y = pack_bf16x2(acc.z * inv, acc.w * inv);
+    *reinterpret_cast<uint2*>(out + row * kHeadDim + lane * 4) = pk;
+}
+
+// In-launch merge (DecodeParams::split_counters): every split CTA of a (sequence, KV head) calls
+// this after its partials are written (all `n_threads` threads of barrier `bar_id`). Returns true
+// in the CTA that arrived last - that one merges. Classic fence / atomic pattern: writers fence
+// before the counter increment, the last arriver fences after it; the counter is left at zero for
+// the next launch.
+__device__ __forceinline__ bool split_arrive_is_last(int32_t* counter, int n_splits, int bar_id,
+                                                     int n_threads, int* flag_smem) {
+    __threadfence();
+    asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "r"(n_threads) : "memory");
+    if (threadIdx.x == 0) {
+        const int old = atomicAdd(counter, 1);
+        const int last = old == n_splits - 1;
+        if (last) *counter = 0;
+        *flag_smem = last;
+    }
+    asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "r"(n_threads) : "memory");
+    const bool last = *flag_smem != 0;
+    if (last) __threadfence();
+    return last;
+}
+
 template <int kStages>
 __global__ void __launch_bounds__(kDecodeThreads, 2)
 decode_split_kernel(const __grid_constant__ CUtensorMap k_map,
@@ -55,6 +133,7 @@ decode_split_kernel(const __grid_constant__ CUtensorMap k_map,
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kStages * kStageBytes);
     uint64_t* empty_bar = full_bar + kStages;
     float* ml_smem = reinterpret_cast<float*>(empty_bar + kStages);  // [4 warps][8 heads][2]
+    __shared__ int last_flag;
 
     const int kvh = blockIdx.x;
     const int split = blockIdx.y;
@@ -85,9 +164,22 @@ decode_split_kernel(const __grid_constant__ CUtensorMap k_map,
             __nv_bfloat16* out = static_cast<__nv_bfloat16*>(p.out) + q_row0 * kHeadDim;
             for (int i = threadIdx.x; i < G * kHeadDim; i += kDecodeThreads)
                 out[i] = __float2bfloat16(0.f);
-        } else if (threadIdx.x < G) {
-            p.ws_lse[(q_row0 + threadIdx.x) * St + split] = -INFINITY;
+        } else {
+            if (threadIdx.x < G) p.ws_lse[(q_row0 + threadIdx.x) * St + split] = -INFINITY;
+            if (p.split_counters != nullptr &&
+                split_arrive_is_last(p.split_counters + b * p.num_kv_heads + kvh, S, 0,
+                                     kDecodeThreads, &last_flag)) {
+                // this empty split arrived last: it merges the row group
+                const int n_pre = shared_pages > 0 ? prefix_chunks_of(shared_pages, p.block_size,
+                                                                      p.prefix_chunks).valid
+                                                   : 0;
+                if (n_pre > 0) grid_dependency_wait();
+                for (int h = warp; h < G; h += kConsumerWarps + 1)
+                    merge_row(p.ws_o, p.ws_lse, static_cast<__nv_bfloat16*>(p.out), q_row0 + h,
+                              S + n_pre, St, lane);
+            }
         }
+        if (p.plan != nullptr) grid_dependency_wait();
         return;
     }
 
@@ -458,8 +550,17 @@ decode_split_kernel(const __grid_constant__ CUtensorMap k_map,
         }
     }
     (void)mg;
+    if (S > 1 && p.split_counters != nullptr &&
+        split_arrive_is_last(p.split_counters + b * p.num_kv_heads + kvh, S, 1,
+                             kConsumerWarps * 32, &last_flag)) {
+        // last split of this (sequence, KV head) to finish: merge its G rows here, no merge launch
+        if (n_prefix > 0) grid_dependency_wait();
+        for (int h = warp; h < G; h += kConsumerWarps)
+            merge_row(p.ws_o, p.ws_lse, static_cast<__nv_bfloat16*>(p.out), q_row0 + h,
+                      S + n_prefix, St, lane);
+    }
     // With the cascade armed this grid is a programmatic dependent of the prefix pass: make sure
-    // it cannot finish before its primary did (the merge kernel that follows reads both).
+    // it cannot finish before its primary did (a merge kernel that follows reads both).
     if (p.plan != nullptr) grid_dependency_wait();
 }
 
@@ -478,57 +579,7 @@ decode_merge_kernel(const float* __restrict__ ws_o, const float* __restrict__ ws
     int S = S_split;
     if (plan != nullptr && context_lens[row / num_q_heads] > 0)
         S += prefix_chunks_of(plan[0], block_size, prefix_chunks).valid;
-    const float* lse = ws_lse + static_cast<int64_t>(row) * St;
-    // lane s (and s + 32) holds the weight of slot s; the partial loads of 8 slots are issued
-    // together so their latencies overlap (S <= 64 + 32 slots).
-    float my_lse[3], my_w[3];
-    float mx = -INFINITY;
-#pragma unroll
-    for (int i = 0; i < 3; ++i) {
-        my_lse[i] = lane + 32 * i < S ? lse[lane + 32 * i] : -INFINITY;
-        mx = fmaxf(mx, my_lse[i]);
-    }
-#pragma unroll
-    for (int off = 16; off > 0; off >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, off));
-    float wsum = 0.f;
-#pragma unroll
-    for (int i = 0; i < 3; ++i) {
-        my_w[i] = my_lse[i] == -INFINITY ? 0.f : fast_exp2(my_lse[i] - mx);  // empty: weight 0
-        wsum += my_w[i];
-    }
-#pragma unroll
-    for (int off = 16; off > 0; off >>= 1) wsum += __shfl_xor_sync(0xffffffffu, wsum, off);
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    const float4* po =
-        reinterpret_cast<const float4*>(ws_o + static_cast<int64_t>(row) * St * kHeadDim) + lane;
-    for (int s0 = 0; s0 < S; s0 += 8) {
-        float4 x[8];
-        float w[8];
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {
-            const int sl = s0 + u;
-            const float wa = __shfl_sync(0xffffffffu, my_w[0], sl & 31);
-            const float wb = __shfl_sync(0xffffffffu, my_w[1], sl & 31);
-            const float wc = __shfl_sync(0xffffffffu, my_w[2], sl & 31);
-            w[u] = sl < S ? (sl < 32 ? wa : (sl < 64 ? wb : wc)) : 0.f;
-            // an empty slot (weight 0) was never written: do not read it
-            x[u] = w[u] != 0.f ? po[sl * (kHeadDim / 4)] : make_float4(0.f, 0.f, 0.f, 0.f);
-        }
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {
-            acc.x += w[u] * x[u].x;
-            acc.y += w[u] * x[u].y;
-            acc.z += w[u] * x[u].z;
-            acc.w += w[u] * x[u].w;
-        }
-    }
-    const float inv = wsum > 0.f ? 1.f / wsum : 0.f;
-    __nv_bfloat162 lo = __floats2bfloat162_rn(acc.x * inv, acc.y * inv);
-    __nv_bfloat162 hi = __floats2bfloat162_rn(acc.z * inv, acc.w * inv);
-    uint2 pk;
-    pk.x = *reinterpret_cast<uint32_t*>(&lo);
-    pk.y = *reinterpret_cast<uint32_t*>(&hi);
-    *reinterpret_cast<uint2*>(out + static_cast<int64_t>(row) * kHeadDim + lane * 4) = pk;
+    merge_row(ws_o, ws_lse, out, row, S, St, lane);
 }
 
 template <int kStages>
@@ -618,7 +669,7 @@ cudaError_t launch_decode(const DecodeParams& p, const CUtensorMap& k_map, const
         default: e = launch_split<3>(p, k_map, v_map, stream); break;
     }
     if (e != cudaSuccess) return e;
-    if (p.num_splits > 1) {
+    if (p.num_splits > 1 && p.split_counters == nullptr) {
         const int rows = p.batch * p.num_q_heads;
         decode_merge_kernel<<<(rows + 3) / 4, 128, 0, stream>>>(
             p.ws_o, p.ws_lse, static_cast<__nv_bfloat16*>(p.out), rows, p.num_splits,

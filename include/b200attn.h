@@ -45,7 +45,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 5
+#define B200ATTN_ABI_VERSION 6
 
 #define B200ATTN_DTYPE_BF16 0
 
@@ -259,6 +259,19 @@ int b200attn_prepare_decode(const int32_t* packed, int32_t batch, int32_t table_
                             int32_t block_size, int64_t* input_ids, int64_t* positions,
                             int32_t* slot_mapping, int32_t* context_lens, int32_t* block_tables,
                             int64_t table_row_stride, int32_t capacity, void* stream);
+
+/*
+ * In-launch split merge. With num_splits > 1 the decode entry points normally launch a second
+ * (merge) kernel. If the caller registers a ZEROED device buffer of `count` int32 for the current
+ * device, the split CTA of a (sequence, KV head) that finishes last merges the partials itself
+ * (fence + atomic arrival counter, reset to zero before the launch ends) whenever
+ * batch * num_kv_heads <= count: one launch instead of two, same arithmetic, bit-identical output.
+ * The buffer stays owned by the caller and must outlive every later decode call on that device
+ * (the library keeps the pointer: the one exception, besides cached TMA descriptors, to "keeps no
+ * pointers"); decode calls that use it must be stream-ordered with respect to each other.
+ * counters == NULL unregisters. B200ATTN_FUSED_MERGE=0 ignores the registration (A/B runs).
+ */
+int b200attn_set_split_counters(void* counters, int64_t count);
 
 #ifdef __cplusplus
 }

@@ -208,3 +208,45 @@ def test_decode_properties_at_baseline_sizes(cuda_dev, shape):
                                     c.meta["context_lens"][b:b + 1],
                                     c.meta["block_tables"][b:b + 1], c.scale)
         assert_close(o[b:b + 1], want, f"row {b} vs oracle")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("batch,ctx,Hq,Hkv,splits", [
+    (1, 4096, 32, 8, 8), (3, [5000, 1, 300], 16, 8, 5), (2, [700, 64], 8, 1, 64),
+    (7, 1000, 4, 1, 3), (16, 2048, 16, 4, 2)])
+def test_in_launch_merge_equals_merge_kernel(cuda_dev, batch, ctx, Hq, Hkv, splits):
+    """num_splits > 1 with registered arrival counters (the last split CTA merges in the same
+    launch) must give the merge kernel's output bit for bit, launch once instead of twice, leave
+    the counters at zero, and handle empty splits / padding rows (ctx 0) that arrive last."""
+    from byox_vllm_b200 import _lib, attention as A
+
+    lib = _lib.load()
+    c = synth.decode_case(batch, ctx, Hq, Hkv, seed=61)
+    d = to_dev(c, cuda_dev)
+    m = d["meta"]
+    lens = m["context_lens"].clone()
+    if batch >= 3:
+        lens[1] = 0  # padding row of a captured batch: every split of it is empty
+    args = (d["q"], d["k_cache"], d["v_cache"], lens, m["block_tables"], c.scale)
+    A.ensure_split_counters(cuda_dev)
+    counters = A._SPLIT_COUNTERS[cuda_dev.index or 0]
+    try:
+        assert lib.b200attn_set_split_counters(None, 0) == 0
+        n0 = lib.b200attn_launch_count()
+        want = A.paged_decode(*args, num_splits=splits)
+        torch.cuda.synchronize()
+        assert lib.b200attn_launch_count() - n0 == 2  # split + merge kernels
+    finally:
+        assert lib.b200attn_set_split_counters(counters.data_ptr(), counters.numel()) == 0
+    for _ in range(3):  # repeated launches: the counters must come back to zero every time
+        n0 = lib.b200attn_launch_count()
+        got = A.paged_decode(*args, num_splits=splits)
+        torch.cuda.synchronize()
+        assert lib.b200attn_launch_count() - n0 == 1
+        assert torch.equal(got, want)
+        assert int(counters.abs().sum()) == 0
+    if batch >= 3:
+        assert torch.count_nonzero(got[1]) == 0
+    ref = orc.paged_decode_ref(c.q, c.k_cache, c.v_cache, lens.cpu(), c.meta["block_tables"],
+                               c.scale)
+    assert_close(got, ref, "in-launch merge vs oracle")

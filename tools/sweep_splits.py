@@ -21,7 +21,7 @@ SHAPES = [(1, 1024, 32, 8), (1, 4096, 32, 8), (4, 4096, 32, 8), (8, 2048, 16, 8)
           (32, 2048, 16, 8), (64, 1024, 16, 8), (64, 4096, 32, 8), (128, 4096, 4, 1),
           (128, 4096, 8, 2), (8, 16384, 32, 8), (2, 32768, 32, 8), (1, 131072, 32, 8),
           (256, 8192, 8, 1), (48, 800, 16, 8), (16, 600, 16, 8)]
-CANDS = [1, 2, 3, 4, 5, 6, 8, 10, 12, 16, 20, 24, 32, 37, 48, 64, 74, 96, 128]
+CANDS = [1, 2, 3, 4, 5, 6, 8, 10, 12, 16, 20, 24, 32, 37, 48, 64]  # API limit: 64 splits
 
 
 def main():
