@@ -19,6 +19,8 @@
 #include "norm_rope.cuh"
 #include "ptx.cuh"
 
+#include <cstdlib>
+
 namespace b200 {
 
 namespace {
@@ -124,10 +126,172 @@ qk_norm_rope_store_kernel(const QkNormRopeParams p, uint32_t qk_blocks, uint32_t
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// Bulk-staged variant (default for prefill-size launches): the bytes in flight are bounded by
+// shared memory instead of registers. A persistent CTA walks tokens t = blockIdx.x, + gridDim.x,
+// ...; a producer thread runs kBulkStages tokens ahead: it reads the token's position and slot,
+// then issues two 1-D bulk copies through the TMA engine (cp.async.bulk, mbarrier completion):
+// the whole QKV row (Hq + 2 Hkv) * 256 B and the 512-byte cos/sin row of its position. Four
+// consumer warps normalise + rotate the q and k heads IN shared memory (a head row per half-warp,
+// 16 B per lane, conflict-free), then one thread writes everything back with bulk stores straight
+// from shared memory: q heads -> q_out, k heads -> k_out (in place) and the cache slot, v heads ->
+// the cache slot (never touched by a compute thread). A stage is handed back to the producer when
+// the bulk stores of the PREVIOUS token have finished reading it (cp.async.bulk.wait_group.read
+// 1). Measured and not adopted: 6 / 8 consumer warps (more registers, fewer CTAs per SM: slower)
+// and a separate store thread behind a `done` mbarrier (a second spinning warp per CTA: 16/8 rows
+// 62 -> 72 us).
+constexpr int kBulkStages = 4;
+
+template <bool kHasNorm, int kBulkConsumerWarps>
+__global__ void __launch_bounds__((kBulkConsumerWarps + 1) * 32)
+qk_norm_rope_bulk_kernel(const QkNormRopeParams p, uint32_t stage_bytes) {
+    extern __shared__ uint8_t bulk_smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>(
+        (reinterpret_cast<uintptr_t>(bulk_smem_raw) + 127) & ~static_cast<uintptr_t>(127));
+    // stage layout: [row: Htot * 256 B][cos/sin: 512 B]; after the stages: barriers, slots
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kBulkStages * stage_bytes);
+    uint64_t* empty_bar = full_bar + kBulkStages;
+    int64_t* slot_smem = reinterpret_cast<int64_t*>(empty_bar + kBulkStages);
+
+    const uint32_t Hq = p.num_q_heads, Hkv = p.num_kv_heads, Hqk = Hq + Hkv;
+    const uint32_t row_bytes = (Hq + 2 * Hkv) * 256;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n_tokens = p.n_tokens;
+
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int s = 0; s < kBulkStages; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        fence_mbar_init();
+    }
+    __syncthreads();
+
+    if (warp == kBulkConsumerWarps) {
+        // ===================== producer (one thread) =====================
+        if (lane != 0) return;
+        int it = 0;
+        for (int tok = blockIdx.x; tok < n_tokens; tok += gridDim.x, ++it) {
+            const int stage = it % kBulkStages;
+            const uint32_t phase = (it / kBulkStages) & 1u;
+            const float* cs_row = cos_sin_row(p.nr, tok);  // dependent load, hidden by the ring
+            int64_t slot = p.slot_mapping != nullptr ? p.slot_mapping[tok] : -1;
+            if (slot >= p.num_slots) slot = -1;
+            mbar_wait(&empty_bar[stage], phase ^ 1u);
+            uint8_t* dst = smem + stage * stage_bytes;
+            slot_smem[stage] = slot;
+            mbar_expect_tx(&full_bar[stage], row_bytes + 512);
+            bulk_load_1d(dst, static_cast<const uint8_t*>(p.qkv) +
+                                  static_cast<int64_t>(tok) * p.qkv_row_stride * 2,
+                         row_bytes, &full_bar[stage]);
+            bulk_load_1d(dst + row_bytes, cs_row, 512, &full_bar[stage]);
+        }
+        return;
+    }
+
+    // ===================== consumers =====================
+    const int c = lane & 15, half = lane >> 4;
+    uint4 wq = make_uint4(0, 0, 0, 0), wk = wq;
+    if (kHasNorm) {
+        wq = *reinterpret_cast<const uint4*>(static_cast<const uint8_t*>(p.nr.q_weight) + c * 16);
+        wk = *reinterpret_cast<const uint4*>(static_cast<const uint8_t*>(p.nr.k_weight) + c * 16);
+    }
+    int it = 0;
+    int prev_stage = -1;
+    for (int tok = blockIdx.x; tok < n_tokens; tok += gridDim.x, ++it) {
+        const int stage = it % kBulkStages;
+        const uint32_t phase = (it / kBulkStages) & 1u;
+        mbar_wait(&full_bar[stage], phase);
+        uint8_t* row = smem + stage * stage_bytes;
+        const CosSin8 cs = load_cos_sin8(reinterpret_cast<const float*>(row + row_bytes), c);
+        // rows (2*warp + half), + 8, ...: both halves of a warp run the same trip count
+        for (uint32_t base = 2 * warp; base < Hqk; base += 2 * kBulkConsumerWarps) {
+            const uint32_t h = base + half;
+            const bool valid = h < Hqk;
+            uint4* cell = reinterpret_cast<uint4*>(row + (valid ? h : base) * 256 + c * 16);
+            const uint4 rot = norm_rope_row16(*cell, h < Hq ? wq : wk, kHasNorm, p.nr.eps, cs, c,
+                                              0xffffffffu);
+            if (valid) *cell = rot;
+        }
+        fence_proxy_async();  // generic-proxy writes above -> visible to the bulk stores below
+        asm volatile("bar.sync 1, %0;" ::"n"(kBulkConsumerWarps * 32) : "memory");
+        if (threadIdx.x == 0) {
+            const int64_t slot = slot_smem[stage];
+            const int64_t t = tok;
+            bulk_store_1d(static_cast<uint8_t*>(p.q_out) + t * Hq * 256, row, Hq * 256);
+            if (p.k_out != nullptr)
+                bulk_store_1d(static_cast<uint8_t*>(p.k_out) + t * p.k_out_row_stride * 2,
+                              row + Hq * 256, Hkv * 256);
+            if (slot >= 0) {
+                bulk_store_1d(static_cast<uint8_t*>(p.k_cache) + slot * Hkv * 256, row + Hq * 256,
+                              Hkv * 256);
+                bulk_store_1d(static_cast<uint8_t*>(p.v_cache) + slot * Hkv * 256,
+                              row + Hqk * 256, Hkv * 256);
+            }
+            bulk_commit_group();
+            // the previous token's stores have finished READING their stage: hand it back
+            bulk_wait_group_read<1>();
+            if (prev_stage >= 0) mbar_arrive(&empty_bar[prev_stage]);
+        }
+        prev_stage = stage;
+    }
+    if (threadIdx.x == 0) bulk_wait_group<0>();  // shared memory must outlive the last stores
+}
+
 }  // namespace
+
+// B200ATTN_NORMROPE=bulk|direct forces one variant (A/B runs); default: bulk-staged for
+// prefill-size launches, the direct kernel for decode-size ones (latency bound, wide grid).
+static int normrope_mode_from_env() {
+    static int mode = [] {
+        const char* e = std::getenv("B200ATTN_NORMROPE");
+        if (!e) return 0;
+        return e[0] == 'b' ? 1 : (e[0] == 'd' ? 2 : 0);
+    }();
+    return mode;
+}
 
 cudaError_t launch_qk_norm_rope_store(const QkNormRopeParams& p, cudaStream_t stream) {
     if (p.n_tokens == 0) return cudaSuccess;
+    const int mode = normrope_mode_from_env();
+    const uint32_t row_bytes = static_cast<uint32_t>(p.num_q_heads + 2 * p.num_kv_heads) * 256;
+    const uint32_t stage_bytes = (row_bytes + 512 + 127) & ~127u;
+    const int smem = kBulkStages * stage_bytes + 2 * kBulkStages * 8 + kBulkStages * 8 + 128;
+    const bool bulk_ok = smem <= 200 * 1024;
+    // rows of >= 8 KiB per token amortise the per-token barrier / issue chain; below that
+    // (TP = 8 shards) and for short batches the direct kernel is faster (measured)
+    if (bulk_ok && (mode == 1 || (mode == 0 && p.n_tokens >= 2048 && row_bytes >= 8192))) {
+        static int sm_count = [] {
+            int dev = 0, n = 148;
+            cudaGetDevice(&dev);
+            cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+            return n > 0 ? n : 148;
+        }();
+        static const int warps = [] {
+            const char* e = std::getenv("B200ATTN_NORMROPE_WARPS");
+            const int w = e ? std::atoi(e) : 4;
+            return (w == 4 || w == 6 || w == 8) ? w : 4;
+        }();
+        const bool norm = p.nr.q_weight != nullptr;
+        auto kern = warps == 4   ? (norm ? qk_norm_rope_bulk_kernel<true, 4>
+                                         : qk_norm_rope_bulk_kernel<false, 4>)
+                    : warps == 6 ? (norm ? qk_norm_rope_bulk_kernel<true, 6>
+                                         : qk_norm_rope_bulk_kernel<false, 6>)
+                                 : (norm ? qk_norm_rope_bulk_kernel<true, 8>
+                                         : qk_norm_rope_bulk_kernel<false, 8>);
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             smem);
+        if (e != cudaSuccess) return e;
+        int per_sm = (220 * 1024) / (smem + 1024);
+        per_sm = per_sm < 1 ? 1 : (per_sm > 6 ? 6 : per_sm);
+        const int64_t want = static_cast<int64_t>(sm_count) * per_sm;
+        const unsigned grid = static_cast<unsigned>(p.n_tokens < want ? p.n_tokens : want);
+        kern<<<grid, (warps + 1) * 32, smem, stream>>>(p, stage_bytes);
+        count_launch();
+        return cudaGetLastError();
+    }
     const int64_t qk_groups = (p.num_q_heads + p.num_kv_heads + kRows - 1) / kRows;
     const int64_t v_groups = (p.num_kv_heads + kRows - 1) / kRows;
     const int64_t qk_items = static_cast<int64_t>(p.n_tokens) * qk_groups;

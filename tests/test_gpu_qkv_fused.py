@@ -74,10 +74,12 @@ def test_normrope_matches_reference_modules(cuda_dev, case):
 
 @pytest.mark.parametrize("n,Hq,Hkv,has_norm", [(1, 16, 8, True), (255, 16, 8, True),
                                                (4097, 32, 8, True), (333, 4, 1, True),
-                                               (130, 8, 2, False)])
+                                               (130, 8, 2, False), (2048, 8, 1, True),
+                                               (1500, 8, 2, False), (1024, 16, 8, True)])
 def test_normrope_store_vs_oracle(cuda_dev, n, Hq, Hkv, has_norm):
     """Seeded sizes the CPU oracle finishes in seconds; scatter with holes and out-of-range
-    slots; write_k on/off; untouched cache rows stay untouched."""
+    slots; write_k on/off; untouched cache rows stay untouched. n >= 1024 runs the bulk-staged
+    (TMA) kernel, smaller n the direct one."""
     max_pos, bs, nb = 8192, 256, 24
     qkv, positions, q_w, k_w = gc.normrope_inputs(n, Hq, Hkv, has_norm, max_pos, seed=n)
     cache = orc.rope_cos_sin_cache(D, max_pos, 1e6)
