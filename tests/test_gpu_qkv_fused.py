@@ -302,3 +302,44 @@ def test_qkv_decode_graph_replay(cuda_dev):
         assert_close(g_out[:n].unsqueeze(1), want, "graph replay")
         assert torch.count_nonzero(g_out[n:]) == 0, "padding rows must give zeros"
         _ulp_check(kc, kc_ref, "k_cache under replay")
+
+
+def test_qkv_attention_decode_with_cascade_armed(cuda_dev):
+    """A decode batch the size heuristic arms the shared-prefix cascade for (64 rows, tables of
+    32 pages): qkv_attention must run qk_norm_rope_store (q materialised for the prefix pass's
+    TMA map, K/V scattered) followed by the cascade decode, and still equal qwen3.py:75-84."""
+    from byox_vllm_b200 import _lib, qkv_attention as fused
+    from byox_vllm_b200.attention import Attention, cascade_chunks
+    from byox_vllm_b200.context import reset_context, set_context
+
+    dev = cuda_dev
+    Hq, Hkv, B, W = 8, 2, 64, 32
+    assert cascade_chunks(B, Hq, Hkv, W, 256) > 0
+    c = synth.shared_prefix_decode_case([1300 + 5 * i for i in range(B)], 5, Hq, Hkv, seed=71)
+    m = c.meta
+    gen = torch.Generator().manual_seed(72)
+    qkv = (1.5 * torch.randn(B, (Hq + 2 * Hkv) * D, generator=gen)).to(torch.bfloat16)
+    q_w = (1.0 + 0.25 * torch.randn(D, generator=gen)).to(torch.bfloat16)
+    k_w = (1.0 + 0.25 * torch.randn(D, generator=gen)).to(torch.bfloat16)
+    cache = orc.rope_cos_sin_cache(D, 4096, 1e6)
+    kc_ref, vc_ref = c.k_cache.clone(), c.v_cache.clone()
+    want = orc.qkv_attention_ref(qkv, m["positions"], q_w, k_w, EPS, cache, kc_ref, vc_ref,
+                                 type("Ctx", (), dict(m))(), c.scale, Hq, Hkv)
+    bt = torch.full((B, W), -1, dtype=torch.int32)
+    bt[:, :m["block_tables"].size(1)] = m["block_tables"]
+    attn = Attention(Hq, D, c.scale, Hkv)
+    attn.k_cache, attn.v_cache = c.k_cache.to(dev), c.v_cache.to(dev)
+    set_context(False, slot_mapping=m["slot_mapping"].to(dev),
+                context_lens=m["context_lens"].to(dev), block_tables=bt.to(dev))
+    try:
+        n0 = _lib.load().b200attn_launch_count()
+        got = fused.qkv_attention(attn, qkv.to(dev), m["positions"].to(dev), q_w.to(dev),
+                                  k_w.to(dev), EPS, cache.to(dev))
+        torch.cuda.synchronize()
+        launches = _lib.load().b200attn_launch_count() - n0
+    finally:
+        reset_context()
+    assert launches == 4, f"plan + norm/rope/store + prefix pass + decode, got {launches}"
+    assert_close(got.unsqueeze(1), want, "qkv_attention with the cascade armed")
+    _ulp_check(attn.k_cache, kc_ref, "k_cache")
+    assert torch.equal(attn.v_cache.cpu().view(torch.int16), vc_ref.view(torch.int16))
