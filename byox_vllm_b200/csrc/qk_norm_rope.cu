@@ -138,7 +138,10 @@ qk_norm_rope_store_kernel(const QkNormRopeParams p, uint32_t qk_blocks, uint32_t
 // from shared memory: q heads -> q_out, k heads -> k_out (in place) and the cache slot, v heads ->
 // the cache slot (never touched by a compute thread). A stage is handed back to the producer when
 // the bulk stores of the PREVIOUS token have finished reading it (cp.async.bulk.wait_group.read
-// 1). Measured and not adopted: 6 / 8 consumer warps (more registers, fewer CTAs per SM: slower)
+// 1). Measured and not adopted: several tokens per stage for narrow rows (one barrier round per
+// ~16 KiB; the extra index arithmetic and producer registers cost more than the rounds save:
+// 16/8 rows 61 -> 79 us, 8/1 rows 29 -> 51 us, so narrow rows stay on the direct kernel); 6 / 8
+// consumer warps (more registers, fewer CTAs per SM: slower)
 // and a separate store thread behind a `done` mbarrier (a second spinning warp per CTA: 16/8 rows
 // 62 -> 72 us).
 constexpr int kBulkStages = 4;
