@@ -12,7 +12,7 @@ from pathlib import Path
 
 LIB_PATH = Path(__file__).resolve().parent / "libb200attn.so"
 
-ABI_VERSION = 6
+ABI_VERSION = 7
 DTYPE_BF16 = 0
 
 E_BADARG = -1
@@ -52,6 +52,8 @@ PROTOTYPES = {
     "b200attn_prepare_decode": (
         _i32, [_vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _vp]),
     "b200attn_set_split_counters": (_i32, [_vp, _i64]),
+    "b200attn_prepare_prefill": (
+        _i32, [_vp, _i32, _i32, _vp, _i32, _vp, _i32, _vp, _vp, _vp]),
     "b200attn_qkv_decode": (
         _i32, [_vp, _i64, _vp, _vp, _vp, _f32, _vp, _i32, _vp, _vp, _vp, _vp, _i64, _i32, _vp,
                _vp, _vp, _sz, _i32, _i32, _i32, _i32, _i32, _i64, _f32, _i32, _i32, _vp]),

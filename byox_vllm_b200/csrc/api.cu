@@ -701,4 +701,28 @@ int b200attn_set_split_counters(void* counters, int64_t count) {
     return 0;
 }
 
+int b200attn_prepare_prefill(const int32_t* packed, int32_t num_seqs, int32_t block_size,
+                             int64_t* positions, int32_t total_q, int32_t* slot_mapping,
+                             int32_t total_slots, int32_t* cu_seqlens_q, int32_t* cu_seqlens_k,
+                             void* stream) {
+    if (num_seqs < 0 || block_size <= 0 || total_q < 0 || total_slots < 0)
+        return fail(B200ATTN_E_BADARG, "negative or zero size");
+    if (num_seqs > 1024) return fail(B200ATTN_E_UNSUPPORTED, "num_seqs %d > 1024", num_seqs);
+    if (!cu_seqlens_q || !cu_seqlens_k) return fail(B200ATTN_E_BADARG, "null cu_seqlens");
+    if (num_seqs > 0 && !packed) return fail(B200ATTN_E_BADARG, "null packed record");
+    if ((total_q > 0 && !positions) || (total_slots > 0 && !slot_mapping))
+        return fail(B200ATTN_E_BADARG, "null output");
+    b200::PreparePrefillParams p{};
+    p.packed = packed;
+    p.positions = positions;
+    p.slot_mapping = slot_mapping;
+    p.cu_seqlens_q = cu_seqlens_q;
+    p.cu_seqlens_k = cu_seqlens_k;
+    p.num_seqs = num_seqs;
+    p.block_size = block_size;
+    cudaError_t e = b200::launch_prepare_prefill(p, total_q > total_slots ? total_q : total_slots,
+                                                 static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? 0 : cuda_fail(e, "prepare_prefill launch");
+}
+
 }  // extern "C"

@@ -54,6 +54,18 @@ struct PrepareDecodeParams {
 };
 cudaError_t launch_prepare_decode(const PrepareDecodeParams& p, cudaStream_t stream);
 
+struct PreparePrefillParams {
+    const int32_t* packed;  // device: num_tokens[S] | num_cached[S] | table_len[S] | blocks[sum]
+    int64_t* positions;     // [sum(n - cached)]
+    int32_t* slot_mapping;  // [sum over sequences with a table of n - (cached / bs) * bs]
+    int32_t* cu_seqlens_q;  // [S + 1]
+    int32_t* cu_seqlens_k;  // [S + 1]
+    int32_t num_seqs;
+    int32_t block_size;
+};
+cudaError_t launch_prepare_prefill(const PreparePrefillParams& p, int32_t total_hint,
+                                   cudaStream_t stream);
+
 // ---- decode_attn.cu --------------------------------------------------------------------------
 struct DecodeParams {
     const void* q;                // [B, Hq, 128] bf16

@@ -13,8 +13,10 @@ context_lens / block_tables straight into the graph input buffers, bit-identical
 
   pack_decode_record(...)      host packing (numpy), shared by the tests
   DecodeMetaStager             pinned double buffer + device record + the launch
-  prepare_decode / run_model   drop-ins for ModelRunner._prepare_decode / _run_model
-                               (bound by install.install(fast_meta=True))
+  pack_prefill_record / PrefillMetaStager   the same for the per-token lists of a prefill step
+                               (b200attn_prepare_prefill: positions, slot_mapping, cu_seqlens)
+  prepare_decode / run_model / prepare_prefill   drop-ins for ModelRunner._prepare_decode /
+                               _run_model / _prepare_prefill (install.install(fast_meta=True))
 """
 from __future__ import annotations
 
@@ -64,7 +66,8 @@ class DecodeMetaStager:
         self.device = input_ids.device
         self._dev = torch.empty(n, dtype=torch.int32, device=self.device)
         # two pinned buffers: the copy of step t may still be in flight while step t+1 is packed
-        self._pinned = [torch.empty(n, dtype=torch.int32, pin_memory=True) for _ in range(2)]
+        self._pinned = [torch.empty(n, dtype=torch.int32, device="cpu", pin_memory=True)
+                        for _ in range(2)]
         self._np = [p.numpy() for p in self._pinned]
         self._events = [torch.cuda.Event(), torch.cuda.Event()]
         self._used = [False, False]
@@ -97,6 +100,90 @@ class DecodeMetaStager:
             torch.cuda.current_stream(self.device).cuda_stream)
         _lib.check("b200attn_prepare_decode", rc)
         return B, width
+
+
+def pack_prefill_record(num_tokens, num_cached, block_tables, out: np.ndarray | None = None):
+    """-> record int32[3S + sum(len)] = num_tokens | num_cached | table_len | blocks."""
+    S = len(num_tokens)
+    lens = [len(t) for t in block_tables]
+    total = 3 * S + sum(lens)
+    if out is None:
+        out = np.empty(total, dtype=np.int32)
+    assert out.dtype == np.int32 and out.size >= total
+    out[:S] = num_tokens
+    out[S:2 * S] = num_cached
+    out[2 * S:3 * S] = lens
+    out[3 * S:total] = np.fromiter(chain.from_iterable(block_tables), dtype=np.int32,
+                                   count=total - 3 * S)
+    return out[:total]
+
+
+class _PinnedRing:
+    """Two growable pinned staging buffers with a reuse event each (the H2D copy of step t may
+    still be in flight while step t+1 is being packed)."""
+
+    def __init__(self, dtype):
+        self.dtype = dtype
+        self.bufs = [None, None]
+        self.events = [None, None]
+        self.turn = 0
+
+    def next(self, n: int) -> torch.Tensor:
+        i = self.turn
+        self.turn ^= 1
+        if self.events[i] is not None:
+            self.events[i].synchronize()
+        if self.bufs[i] is None or self.bufs[i].numel() < n:
+            # explicit device: ModelRunner.__init__ warms up under torch.set_default_device("cuda")
+            self.bufs[i] = torch.empty(max(n, 4096), dtype=self.dtype, device="cpu",
+                                       pin_memory=True)
+        self._last = i
+        return self.bufs[i]
+
+    def mark(self) -> None:
+        if self.events[self._last] is None:
+            self.events[self._last] = torch.cuda.Event()
+        self.events[self._last].record()
+
+
+class PrefillMetaStager:
+    """ModelRunner._prepare_prefill's per-token lists (positions, slot_mapping, cu_seqlens) built
+    by b200attn_prepare_prefill from one compact record. Output tensors are fresh per step, as in
+    the reference (prefill is not graph-captured)."""
+
+    def __init__(self, device: torch.device, block_size: int):
+        if torch.device(device).type != "cuda":
+            raise RuntimeError("PrefillMetaStager needs a CUDA device; there is no CPU path")
+        self.device = torch.device(device)
+        self.block_size = block_size
+        self._rec = _PinnedRing(torch.int32)
+
+    def stage(self, num_tokens, num_cached, block_tables):
+        """-> (positions int64[Nq], slot_mapping int32[Ns], cu_seqlens_q, cu_seqlens_k) on the
+        device, asynchronous on the current stream."""
+        S, bs = len(num_tokens), self.block_size
+        if S > 1024:
+            raise ValueError(f"{S} sequences exceed the 1024 the device builder handles")
+        total_q = sum(num_tokens) - sum(num_cached)
+        total_slots = sum(n - (c // bs) * bs
+                          for n, c, t in zip(num_tokens, num_cached, block_tables) if t)
+        n_rec = 3 * S + sum(map(len, block_tables))
+        pinned = self._rec.next(n_rec)
+        pack_prefill_record(num_tokens, num_cached, block_tables, pinned.numpy())
+        dev = self.device
+        rec = torch.empty(n_rec, dtype=torch.int32, device=dev)
+        rec.copy_(pinned[:n_rec], non_blocking=True)
+        self._rec.mark()
+        positions = torch.empty(total_q, dtype=torch.int64, device=dev)
+        slot_mapping = torch.empty(total_slots, dtype=torch.int32, device=dev)
+        cu_q = torch.empty(S + 1, dtype=torch.int32, device=dev)
+        cu_k = torch.empty(S + 1, dtype=torch.int32, device=dev)
+        rc = _lib.load().b200attn_prepare_prefill(
+            rec.data_ptr(), S, bs, positions.data_ptr(), total_q, slot_mapping.data_ptr(),
+            total_slots, cu_q.data_ptr(), cu_k.data_ptr(),
+            torch.cuda.current_stream(dev).cuda_stream)
+        _lib.check("b200attn_prepare_prefill", rc)
+        return positions, slot_mapping, cu_q, cu_k
 
 
 # ---- drop-ins for the reference's ModelRunner (bound by install.py) ----------------------------
@@ -134,6 +221,45 @@ def prepare_decode(self, seqs):
     return gv["input_ids"][:bs], gv["positions"][:bs]
 
 
+def prepare_prefill(self, seqs):
+    """ModelRunner._prepare_prefill (model_runner.py:160-204): the per-token lists (positions,
+    slot_mapping) and the cu_seqlens come from one device launch; input_ids (the token ids
+    themselves), max_seqlen_q/k and the prefix-cache block tables are formed as the reference
+    forms them."""
+    import sys
+
+    from . import attention as _attn
+
+    set_context = sys.modules[_attn.get_context.__module__].set_context
+    if len(seqs) > 1024:
+        return _ORIG["_prepare_prefill"](self, seqs)
+    st = getattr(self, "_b200_prefill_stager", None)
+    if st is None:
+        st = PrefillMetaStager(torch.device("cuda", torch.cuda.current_device()), self.block_size)
+        self._b200_prefill_stager = st
+        self._b200_ids_ring = _PinnedRing(torch.int64)
+    num_tokens = [len(seq) for seq in seqs]
+    num_cached = [seq.num_cached_tokens for seq in seqs]
+    positions, slot_mapping, cu_q, cu_k = st.stage(num_tokens, num_cached,
+                                                   [seq.block_table for seq in seqs])
+    total_q = positions.numel()
+    ring = self._b200_ids_ring
+    pinned = ring.next(total_q)
+    pinned.numpy()[:total_q] = np.fromiter(
+        chain.from_iterable(seq[seq.num_cached_tokens:] for seq in seqs), dtype=np.int64,
+        count=total_q)
+    input_ids = torch.empty(total_q, dtype=torch.int64, device=positions.device)
+    input_ids.copy_(pinned[:total_q], non_blocking=True)
+    ring.mark()
+    max_q = max(n - c for n, c in zip(num_tokens, num_cached))
+    max_k = max(num_tokens)
+    block_tables = None
+    if sum(num_tokens) > total_q:  # prefix cache (model_runner.py:188-189)
+        block_tables = self._prepare_block_tables(seqs)
+    set_context(True, cu_q, cu_k, max_q, max_k, slot_mapping, None, block_tables)
+    return input_ids, positions
+
+
 @torch.inference_mode()
 def run_model(self, input_ids, positions, is_prefill):
     """ModelRunner._run_model (model_runner.py:228-254): when prepare_decode above already filled
@@ -152,11 +278,14 @@ def bind(model_runner_cls) -> None:
     if "_prepare_decode" not in _ORIG:
         _ORIG["_prepare_decode"] = model_runner_cls._prepare_decode
         _ORIG["_run_model"] = model_runner_cls._run_model
+        _ORIG["_prepare_prefill"] = model_runner_cls._prepare_prefill
     model_runner_cls._prepare_decode = prepare_decode
     model_runner_cls._run_model = run_model
+    model_runner_cls._prepare_prefill = prepare_prefill
 
 
 def unbind(model_runner_cls) -> None:
     if "_prepare_decode" in _ORIG:
         model_runner_cls._prepare_decode = _ORIG.pop("_prepare_decode")
         model_runner_cls._run_model = _ORIG.pop("_run_model")
+        model_runner_cls._prepare_prefill = _ORIG.pop("_prepare_prefill")

@@ -45,7 +45,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 6
+#define B200ATTN_ABI_VERSION 7
 
 #define B200ATTN_DTYPE_BF16 0
 
@@ -272,6 +272,27 @@ int b200attn_prepare_decode(const int32_t* packed, int32_t batch, int32_t table_
  * counters == NULL unregisters. B200ATTN_FUSED_MERGE=0 ignores the registration (A/B runs).
  */
 int b200attn_set_split_counters(void* counters, int64_t count);
+
+/*
+ * Prefill-step metadata expansion: the per-token part of
+ * ModelRunner._prepare_prefill (engine/model_runner.py:160-204) on the device. `packed` is a
+ * DEVICE int32 array  num_tokens[S] | num_cached_tokens[S] | table_len[S] | blocks[sum(table_len)].
+ * One launch writes, bit-identically to the reference's lists:
+ *     positions    (int64)  concat over s of range(num_cached[s], num_tokens[s])
+ *     cu_seqlens_q (int32)  [0, prefix sums of num_tokens - num_cached]      S + 1 entries
+ *     cu_seqlens_k (int32)  [0, prefix sums of num_tokens]                   S + 1 entries
+ *     slot_mapping (int32)  for every s with table_len[s] > 0 (warm-up sequences have no table,
+ *                           :179-180): block_table[i] * block_size + j over blocks i from
+ *                           num_cached[s] / block_size to the last one, j < block_size (or <
+ *                           last_block_num_tokens in the last block, engine/sequence.py:58-68)
+ * The caller sizes the outputs from host-visible sums: total_q = sum(num_tokens - num_cached),
+ * total_slots = sum over s with a table of num_tokens[s] - (num_cached[s] / block_size) *
+ * block_size. num_seqs <= 1024. max_seqlen_q / max_seqlen_k and input_ids stay on the host side.
+ */
+int b200attn_prepare_prefill(const int32_t* packed, int32_t num_seqs, int32_t block_size,
+                             int64_t* positions, int32_t total_q, int32_t* slot_mapping,
+                             int32_t total_slots, int32_t* cu_seqlens_q, int32_t* cu_seqlens_k,
+                             void* stream);
 
 #ifdef __cplusplus
 }

@@ -145,3 +145,56 @@ def test_stager_reuse_and_model_runner_dropins(cuda_dev):
     finally:
         fm._ORIG.clear()
         reset_context()
+
+
+def test_pack_prefill_record_layout():
+    rec = fm.pack_prefill_record([5, 300], [0, 256], [[3], [8, 2]])
+    assert rec.dtype == np.int32 and rec.tolist() == [5, 300, 0, 256, 1, 2, 3, 8, 2]
+    assert fm.pack_prefill_record([], [], []).size == 0
+
+
+def _check_prefill(dev, seqs, block_size):
+    st = fm.PrefillMetaStager(dev, block_size)
+    want = md.prepare_prefill(seqs, block_size)
+    for _ in range(3):  # the pinned ring is reused across steps
+        pos, slot, cu_q, cu_k = st.stage([s.num_tokens for s in seqs],
+                                         [s.num_cached_tokens for s in seqs],
+                                         [s.block_table for s in seqs])
+        torch.cuda.synchronize()
+        assert pos.dtype == torch.int64 and slot.dtype == torch.int32
+        assert torch.equal(pos.cpu(), want["positions"])
+        assert torch.equal(slot.cpu(), want["slot_mapping"])
+        assert torch.equal(cu_q.cpu(), want["cu_seqlens_q"])
+        assert torch.equal(cu_k.cpu(), want["cu_seqlens_k"])
+
+
+@pytest.mark.gpu
+def test_prepare_prefill_reference_expectations_block16(cuda_dev):
+    """The prefill cases of the reference's tests/test_prepare_funcs.py:17-80,146-166 (block 16),
+    including a cached prefix that is not a whole block (slots cover the block, positions do
+    not)."""
+    S = lambda n, t, c=0: md.SeqState(n, list(t), c)
+    _check_prefill(cuda_dev, [S(5, [0])], 16)
+    _check_prefill(cuda_dev, [S(3, [0]), S(5, [1])], 16)
+    _check_prefill(cuda_dev, [S(6, [0, 1], 3)], 16)
+    _check_prefill(cuda_dev, [S(5, [0], 2), S(6, [1], 1)], 16)
+
+
+@pytest.mark.gpu
+def test_prepare_prefill_block256_batches(cuda_dev):
+    S = lambda n, t, c=0: md.SeqState(n, list(t), c)
+    _check_prefill(cuda_dev, [S(600, [4, 6, 0], 512), S(300, [1, 2])], 256)
+    _check_prefill(cuda_dev, [S(4096, []), S(4096, [])], 256)  # warm-up: no tables, no slots
+    _check_prefill(cuda_dev, [S(256, [9]), S(257, [3, 5]), S(1, [7]), S(513, [2, 4, 6], 512)], 256)
+    rng = random.Random(3)
+    seqs = []
+    for _ in range(48):  # ~16k uncached tokens, some sequences with cached prefixes
+        n = rng.randint(1, 700)
+        cached = rng.choice([0, 0, 256, 512]) if n > 512 else (256 if n > 300 and rng.random() < .5
+                                                                else 0)
+        nb = (n + 255) // 256
+        seqs.append(S(n, [rng.randrange(1 << 20) for _ in range(nb)], cached))
+    _check_prefill(cuda_dev, seqs, 256)
+    _check_prefill(cuda_dev, [S(16384, [rng.randrange(1 << 20) for _ in range(64)])], 256)
+    many = [S(rng.randint(1, 40), [rng.randrange(1 << 20)]) for _ in range(1024)]
+    _check_prefill(cuda_dev, many, 256)
