@@ -14,8 +14,29 @@ Workloads (BASELINE.json configs):
 N > 1 (torchrun): tensor-parallel layout of the reference — every rank gets Hq/N and Hkv/N heads
 of every layer and the full (replicated) metadata; no data-path collective; strong scaling.
 
+What one line carries besides the contract's keys:
+  roofline      the decode kernel alone (CUDA events), algorithmic bytes / measured HBM peak
+  e2e           the same step from pinned HOST buffers: one slab per layer group host->device,
+                the group's captured graph, its outputs device->host; copies inside the timing
+  flash_attn    the reference's OWN attention module (nanovllm/layers/attention.py from
+                baseline/_ref: Triton store_kvcache + flash_attn_with_kvcache, flash-attn's own
+                split heuristic) on the SAME per-rank state, captured in a CUDA graph the same
+                way and timed after ours: the bar north_star names. `vs_flash_attn` =
+                flash-attn step time / ours. A comparison leg: never inside ours' timed region;
+                the product package never imports flash_attn.
+  extra         (N=1) kernel-level rooflines the headline shape does not show: c3 = batch 128 x
+                ctx 4096 (the "batch >= 64, ctx >= 4k" target), c4 per-rank shape with the shared
+                prefix (cascade), c5 corners, the TP=8 per-rank shape of c2, varlen prefill
+                (tensor pipe), store_kvcache (HBM), each beside flash-attn / the reference's
+                Triton scatter.
+  engine_e2e    (N=1) the unmodified reference engine (baseline/_ref) on BASELINE config 2 end to
+                end (tools/e2e_nanovllm.py): reference attention vs the drop-in at the frozen
+                Attention.forward boundary vs the drop-in with every (f) row enabled.
+  cpu_baseline  the CPU restatement (oracle/) on a bounded sample, same sample as --impl reference
+
 `--impl reference` times the CPU restatement of the same path (oracle/, the reference has no
 CPU attention path of its own and is pure Python + CUDA-only wheels) on the host cores.
+`--workload prefill|store|c4|c5|tp8` print the corresponding extra block alone.
 """
 from __future__ import annotations
 
@@ -26,6 +47,7 @@ import statistics
 import subprocess
 import sys
 import time
+import types
 from pathlib import Path
 
 ROOT = Path(__file__).resolve().parent
@@ -38,7 +60,10 @@ WORKLOADS = {
     "c2": dict(model="Qwen3-0.6B", layers=28, Hq=16, Hkv=8, batch=256, ctx="bench"),
     "c3": dict(model="Qwen3-8B", layers=36, Hq=32, Hkv=8, batch=128, ctx=4096),
 }
+EXTRA_ONLY = ("prefill", "store", "c4", "c5", "tp8")
 D, BLOCK = 128, 256
+GROUP_LAYERS = 4          # layers per host->device slab / captured graph of the e2e leg
+CPU_SAMPLE_SEQS = 64      # sequences of the CPU legs' sample (both legs use the same one)
 
 
 def context_lengths(w) -> list[int]:
@@ -59,13 +84,16 @@ def algorithmic_bytes(lens, Hq, Hkv) -> int:
     return toks * Hkv * D * 2 * 2 + 2 * B * Hq * D * 2 + 4 * pages + 4 * B
 
 
-def measured_traffic(workload: str, world: int):
-    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the decode kernel from the
-    committed `ncu --set full` capture of this workload (profiles/traffic.json), else None."""
+def measured_traffic(key: str):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the kernel from the COMMITTED
+    `ncu --set full` capture named in profiles/traffic.json (not re-measured by this run)."""
     p = ROOT / "profiles" / "traffic.json"
     if not p.exists():
-        return None
-    return json.loads(p.read_text()).get(f"{workload}_tp{world}")
+        return None, None
+    v = json.loads(p.read_text()).get(key)
+    if isinstance(v, dict):
+        return v.get("bytes"), v.get("source")
+    return v, ("profiles/traffic.json" if v is not None else None)
 
 
 def peaks():
@@ -116,13 +144,54 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
+# ------------------------------------------------------------------------------------------------
+# the reference's own attention module, loaded from baseline/_ref without the rest of the engine
+# ------------------------------------------------------------------------------------------------
+def load_reference_attention():
+    """((nanovllm.layers.attention, nanovllm.utils.context), None) of the UNMODIFIED reference
+    under baseline/_ref, or (None, reason). Only the two files of the hot path are executed:
+    `nanovllm` / `nanovllm.layers` / `nanovllm.utils` are registered as bare packages so that
+    nanovllm/__init__.py (the whole engine, transformers, ...) is not imported."""
+    ref = ROOT / "baseline" / "_ref" / "nanovllm"
+    if not (ref / "layers" / "attention.py").exists():
+        return None, ("baseline/_ref is not installed (run __graft_entry__.build() where "
+                      "/root/reference exists)")
+    try:
+        import importlib
+
+        if "nanovllm" not in sys.modules:
+            for name, sub in (("nanovllm", ref), ("nanovllm.layers", ref / "layers"),
+                              ("nanovllm.utils", ref / "utils")):
+                pkg = types.ModuleType(name)
+                pkg.__path__ = [str(sub)]
+                sys.modules[name] = pkg
+        ctx = importlib.import_module("nanovllm.utils.context")
+        att = importlib.import_module("nanovllm.layers.attention")
+        return (att, ctx), None
+    except Exception as e:  # flash_attn / triton missing on this box
+        return None, f"reference attention not importable: {type(e).__name__}: {e}"
+
+
+def flash_attn_version():
+    try:
+        import flash_attn
+
+        return getattr(flash_attn, "__version__", "unknown")
+    except Exception:
+        return None
+
+
+# ------------------------------------------------------------------------------------------------
+# per-rank state
+# ------------------------------------------------------------------------------------------------
 def build_state(w, shard, lens, dev):
     """Per-rank device state: KV cache [2, L, nb, 256, Hkv_local, 128], metadata, Attention
-    modules with their cache views injected like ModelRunner._allocate_kv_cache does."""
+    modules with their cache views injected like ModelRunner._allocate_kv_cache does, and ONE
+    pinned host slab with every layer's inputs: layer l = q [B,Hq,D] | fused k|v rows [B,2*Hkv*D]."""
     import random
 
-    from byox_vllm_b200 import metadata as md
     from byox_vllm_b200.attention import Attention
+    from tools import metadata_ref as md
 
     L, Hq, Hkv = w["layers"], shard.num_q_heads, shard.num_kv_heads
     rng = random.Random(0)
@@ -145,17 +214,49 @@ def build_state(w, shard, lens, dev):
         a.k_cache, a.v_cache = kv_cache[0, layer], kv_cache[1, layer]
         layers.append(a)
     B = len(lens)
-    # pinned host inputs of one step: per layer q [B,Hq,D] and the fused qkv rows for k / v
-    host_q = torch.randn(L, B, Hq, D).to(torch.bfloat16).pin_memory()
-    host_kv = torch.randn(L, B, 2 * Hkv * D).to(torch.bfloat16).pin_memory()
-    return dict(meta=meta, kv_cache=kv_cache, layers=layers, host_q=host_q, host_kv=host_kv,
-                seqs=seqs, nb=nb)
+    row = B * (Hq + 2 * Hkv) * D
+    host_slab = torch.randn(L, row).to(torch.bfloat16).pin_memory()
+    return dict(meta=meta, kv_cache=kv_cache, layers=layers, host_slab=host_slab, seqs=seqs,
+                nb=nb)
+
+
+def slab_views(slab_layer, B, Hq, Hkv):
+    """q [B,Hq,D] contiguous, k [B,Hkv,D] / v [B,Hkv,D] strided views of the fused k|v rows (as
+    qkv.split gives the reference: models/qwen3.py:76-79)."""
+    q = slab_layer[:B * Hq * D].view(B, Hq, D)
+    kv = slab_layer[B * Hq * D:].view(B, 2 * Hkv * D)
+    return q, kv[:, :Hkv * D].view(B, Hkv, D), kv[:, Hkv * D:].view(B, Hkv, D)
+
+
+def capture(fn):
+    """Eager warm-up (lazy module state, descriptor caches, Triton JIT), then capture."""
+    fn()
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        fn()
+    torch.cuda.synchronize()
+    return g
+
+
+def time_replays(graph, steps, warmup, barrier):
+    for _ in range(warmup):
+        graph.replay()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        graph.replay()
+    e1.record()
+    barrier()
+    return e0.elapsed_time(e1) / steps
 
 
 def run_ours(args, w, rank, world, dev):
-    from byox_vllm_b200 import _lib, metadata as md, parallel
+    from byox_vllm_b200 import _lib, parallel
     from byox_vllm_b200.attention import paged_decode
     from byox_vllm_b200.context import reset_context, set_context
+    from tools import metadata_ref as md
 
     lib = _lib.load()
     shard = parallel.shard_heads(w["Hq"], w["Hkv"], world, rank)
@@ -164,21 +265,24 @@ def run_ours(args, w, rank, world, dev):
     B = len(lens)
     st = build_state(w, shard, lens, dev)
     meta, layers = st["meta"], st["layers"]
-    dq = st["host_q"].to(dev)
-    dkv = st["host_kv"].to(dev)
+    dslab = st["host_slab"].to(dev)
     dmeta = md.context_kwargs(meta, dev)
+    warmup = max(args.warmup, 3)
+
+    def barrier():
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize()
 
     def step_device():
         o = None
         for layer in range(L):
-            kv = dkv[layer]
-            k = kv[:, :Hkv * D].view(B, Hkv, D)
-            v = kv[:, Hkv * D:].view(B, Hkv, D)
-            o = layers[layer](dq[layer], k, v)  # consumed by o_proj in the model
+            q, k, v = slab_views(dslab[layer], B, Hq, Hkv)
+            o = layers[layer](q, k, v)  # consumed by o_proj in the model
         return o
 
     set_context(**dmeta)
-    step_device()  # eager warm-up (descriptor cache, func attributes) before capture
+    step_device()  # eager warm-up (descriptor cache, func attributes, counters) before capture
     torch.cuda.synchronize()
     n0 = lib.b200attn_launch_count()
     graph = torch.cuda.CUDAGraph()
@@ -187,89 +291,71 @@ def run_ours(args, w, rank, world, dev):
     launches_per_step = lib.b200attn_launch_count() - n0
     torch.cuda.synchronize()
 
-    def barrier():
-        if world > 1:
-            torch.distributed.barrier()
-        torch.cuda.synchronize()
-
-    for _ in range(max(args.warmup, 3)):
-        graph.replay()
-    barrier()
     sampler = ClockSampler(dev.index or 0) if rank == 0 else None
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(args.steps):
-        graph.replay()
-    e1.record()
-    barrier()
-    ms_step = parallel.max_over_ranks(e0.elapsed_time(e1) / args.steps)
+    ms_step = parallel.max_over_ranks(time_replays(graph, args.steps, warmup, barrier))
 
     # ---- roofline leg: the decode kernel alone, one launch per layer, CUDA events on the stream
-    splits = lib.b200attn_decode_pick_splits(B, Hkv, dmeta["block_tables"].size(1), BLOCK,
+    n_ctas = lib.b200attn_decode_pick_splits(B, Hkv, dmeta["block_tables"].size(1), BLOCK,
                                              lib.b200attn_sm_count())
     scratch = torch.empty(B, Hq, D, dtype=torch.bfloat16, device=dev)
 
     def decode_only():
         for layer in range(L):
-            paged_decode(dq[layer], layers[layer].k_cache, layers[layer].v_cache,
+            q, _, _ = slab_views(dslab[layer], B, Hq, Hkv)
+            paged_decode(q, layers[layer].k_cache, layers[layer].v_cache,
                          dmeta["context_lens"], dmeta["block_tables"], D ** -0.5, out=scratch)
 
-    decode_only()
-    torch.cuda.synchronize()
-    k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    g_dec = capture(decode_only)
     reps = max(2, min(args.steps, 10))
-    k0.record()
-    for _ in range(reps):
-        decode_only()
-    k1.record()
-    torch.cuda.synchronize()
-    ms_kernel = k0.elapsed_time(k1) / (reps * L)
+    ms_kernel = time_replays(g_dec, reps, 2, torch.cuda.synchronize) / L
     clocks = sampler.stop() if sampler else None
 
-    # ---- e2e leg: the user-facing call with HOST buffers; H2D of metadata + q/k/v and D2H of
-    # the outputs inside the timed region, every step
+    # ---- e2e leg: the user-facing call with HOST buffers. Per step: metadata H2D, then per group
+    # of GROUP_LAYERS layers ONE pinned slab H2D on a copy stream, the group's captured graph
+    # (Attention.forward per layer + its output gathered into an output slab) once its slab has
+    # landed, ONE D2H of the group's outputs on a second copy stream. The step ends when the last
+    # output is on the host.
+    groups = [(g0, min(g0 + GROUP_LAYERS, L)) for g0 in range(0, L, GROUP_LAYERS)]
+    eslab = torch.empty_like(dslab)                       # device staging of the host inputs
+    dout = torch.empty(L, B, 1, Hq, D, dtype=torch.bfloat16, device=dev)
     host_out = torch.empty(L, B, 1, Hq, D, dtype=torch.bfloat16).pin_memory()
-    h2d = d2h = 0
+    emeta = {k: (v.clone() if isinstance(v, torch.Tensor) else v) for k, v in dmeta.items()}
+    set_context(**emeta)  # static metadata buffers: the graphs read them, every step refills them
+
+    def group_fn(g0, g1):
+        def fn():
+            for layer in range(g0, g1):
+                q, k, v = slab_views(eslab[layer], B, Hq, Hkv)
+                dout[layer].copy_(layers[layer](q, k, v))
+        return fn
+
+    eslab.copy_(dslab)
+    ggraphs = [capture(group_fn(g0, g1)) for g0, g1 in groups]
     s_in, s_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
-    ev_in = [torch.cuda.Event() for _ in range(L)]
-    ev_out = [torch.cuda.Event() for _ in range(L)]
-    sq = torch.empty_like(dq)    # device staging of the host inputs, one slice per layer
-    skv = torch.empty_like(dkv)
+    ev_in = [torch.cuda.Event() for _ in groups]
+    ev_out = [torch.cuda.Event() for _ in groups]
+    meta_keys = ("slot_mapping", "context_lens", "block_tables")
+    h2d = sum(meta[k].numel() * meta[k].element_size() for k in meta_keys) + \
+        st["host_slab"].numel() * 2
+    d2h = host_out.numel() * 2
 
     def step_e2e():
-        """One decode step from HOST buffers: metadata + every layer's q/k/v go pinned-host ->
-        device on a copy stream, each layer's Attention.forward waits only for its own inputs, and
-        its output goes device -> pinned-host on a second copy stream, so PCIe traffic overlaps
-        the kernels. The step ends when the last output is on the host."""
-        nonlocal h2d, d2h
-        h2d = d2h = 0
         cur = torch.cuda.current_stream(dev)
-        m = md.context_kwargs(meta, dev)  # pinned -> device, non_blocking (model_runner.py:217-225)
-        set_context(**m)
-        for t in (m["slot_mapping"], m["context_lens"], m["block_tables"]):
-            h2d += t.numel() * t.element_size()
+        for k in meta_keys:  # pinned -> device, non_blocking (model_runner.py:217-225)
+            emeta[k].copy_(meta[k], non_blocking=True)
         s_in.wait_stream(cur)
         with torch.cuda.stream(s_in):
-            for layer in range(L):
-                sq[layer].copy_(st["host_q"][layer], non_blocking=True)
-                skv[layer].copy_(st["host_kv"][layer], non_blocking=True)
-                ev_in[layer].record(s_in)
-                h2d += sq[layer].numel() * 2 + skv[layer].numel() * 2
-        outs = []
-        for layer in range(L):
-            cur.wait_event(ev_in[layer])
-            kv = skv[layer]
-            k = kv[:, :Hkv * D].view(B, Hkv, D)
-            v = kv[:, Hkv * D:].view(B, Hkv, D)
-            o = layers[layer](sq[layer], k, v)
-            ev_out[layer].record(cur)
-            outs.append(o)  # keep alive until its D2H copy has run
+            for i, (g0, g1) in enumerate(groups):
+                eslab[g0:g1].copy_(st["host_slab"][g0:g1], non_blocking=True)
+                ev_in[i].record(s_in)
+        for i, (g0, g1) in enumerate(groups):
+            cur.wait_event(ev_in[i])
+            ggraphs[i].replay()
+            ev_out[i].record(cur)
             with torch.cuda.stream(s_out):
-                s_out.wait_event(ev_out[layer])
-                host_out[layer].copy_(o, non_blocking=True)
-            d2h += o.numel() * 2
+                s_out.wait_event(ev_out[i])
+                host_out[g0:g1].copy_(dout[g0:g1], non_blocking=True)
         s_out.synchronize()  # the step's results are on the host
-        cur.synchronize()
 
     for _ in range(3):
         step_e2e()
@@ -280,6 +366,10 @@ def run_ours(args, w, rank, world, dev):
         step_e2e()
     barrier()
     ms_e2e = parallel.max_over_ranks((time.perf_counter() - t0) * 1e3 / e2e_steps)
+    set_context(**dmeta)
+
+    # ---- flash-attn leg: the reference's own Attention module on the same per-rank state
+    fa = flash_attn_leg(args, st, dslab, dmeta, B, Hq, Hkv, L, warmup, barrier)
     reset_context()
 
     if rank != 0:
@@ -287,9 +377,10 @@ def run_ours(args, w, rank, world, dev):
     pk, pk_kind = peaks()
     alg = algorithmic_bytes(lens, Hq, Hkv)
     achieved = alg / (ms_kernel * 1e-3) / 1e9
+    traffic, traffic_src = measured_traffic(f"{args.workload}_tp{world}")
     return {
         "metric": "decode tokens/sec (bench.py shape)", "value": B / (ms_step * 1e-3),
-        "unit": "tokens/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "unit": "tokens/s", "n_gpus": world, "steps": args.steps, "warmup": warmup,
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
         "config": {
@@ -298,35 +389,387 @@ def run_ours(args, w, rank, world, dev):
                         f"{w['Hq']}/{w['Hkv']} over TP={world} -> {Hq}/{Hkv} per rank, "
                         f"block_size {BLOCK}, CUDA graph replay",
             "l2": f"inputs larger than L2: {alg * L / 1e9:.2f} GB of KV streamed per step",
-            "parallelism": f"tp{world}", "decode_splits": int(splits),
+            "parallelism": f"tp{world}", "decode_ctas": int(n_ctas),
         },
         "roofline": {
             "bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
-            "frac": achieved / pk["hbm_gbs"],
-            "traffic": measured_traffic(args.workload, world), "peak_kind": pk_kind,
-            "kernel": "decode_split_kernel (+ merge when splits > 1)",
+            "frac": achieved / pk["hbm_gbs"], "traffic": traffic,
+            "traffic_source": (f"committed ncu --set full capture ({traffic_src}), not "
+                               f"re-measured by this run") if traffic is not None else None,
+            "peak_kind": pk_kind,
+            "kernel": "decode_stream_kernel (persistent, in-launch merge), graph replay of one "
+                      "launch per layer",
             "algorithmic_bytes_per_launch": alg, "ms_per_launch": ms_kernel,
             "frac_of_8TBs_nominal": achieved / 8000.0,
         },
         "e2e": {"value": B / (ms_e2e * 1e-3), "unit": "tokens/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e,
-                "path": "Attention.forward per layer from pinned HOST q/k/v (copy stream) with outputs "
-                        "back to pinned host (second copy stream); H2D/D2H inside the timed region"},
+                "path": f"pinned HOST q/k/v slab per {GROUP_LAYERS}-layer group -> device (copy "
+                        f"stream), captured graph of Attention.forward per group, outputs back to "
+                        f"pinned host (second copy stream); H2D/D2H inside the timed region"},
         "gpu_launches": int(launches_per_step * args.steps),
         "launches_per_step": int(launches_per_step),
         "clocks": clocks,
+        "flash_attn": fa,
+        "vs_flash_attn": (fa["ms_per_step"] / ms_step) if "ms_per_step" in fa else None,
     }
 
 
-def cpu_reference(w, steps, warmup, sample_seqs=None, budget_s=20.0):
+def flash_attn_leg(args, st, dslab, dmeta, B, Hq, Hkv, L, warmup, barrier):
+    """The reference's Attention.forward (decode branch: Triton store_kvcache +
+    flash_attn_with_kvcache) per layer on the same caches / tables / lens / inputs, captured in a
+    CUDA graph like ModelRunner captures it, timed exactly like ours. Runs on every rank (the
+    timing is a max over ranks); returns a dict on every rank."""
+    from byox_vllm_b200 import parallel
+
+    mods, why = load_reference_attention()
+    ok = 1.0 if mods else 0.0
+    if parallel.max_over_ranks(-ok) != -1.0:  # some rank cannot run it: nobody does
+        return {"unavailable": why or "unavailable on another rank"}
+    att, ctx = mods
+    kv = st["kv_cache"]
+    ref_layers = []
+    for layer in range(L):
+        a = att.Attention(Hq, D, D ** -0.5, Hkv)
+        a.k_cache, a.v_cache = kv[0, layer], kv[1, layer]
+        ref_layers.append(a)
+    ctx.set_context(False, slot_mapping=dmeta["slot_mapping"], context_lens=dmeta["context_lens"],
+                    block_tables=dmeta["block_tables"])
+
+    def step_ref():
+        o = None
+        for layer in range(L):
+            q, k, v = slab_views(dslab[layer], B, Hq, Hkv)
+            o = ref_layers[layer](q, k, v)
+        return o
+
+    try:
+        g = capture(step_ref)
+        ms = parallel.max_over_ranks(time_replays(g, args.steps, warmup, barrier))
+    finally:
+        ctx.reset_context()
+    return {"ms_per_step": ms, "tokens_per_s": B / (ms * 1e-3), "version": flash_attn_version(),
+            "path": "baseline/_ref nanovllm.layers.attention.Attention.forward per layer "
+                    "(Triton store_kvcache + flash_attn_with_kvcache), same caches / tables / "
+                    "lens / inputs, CUDA graph replay, same steps and warm-up"}
+
+
+# ------------------------------------------------------------------------------------------------
+# extras: kernel-level rooflines beside the reference's kernels (single GPU)
+# ------------------------------------------------------------------------------------------------
+_flush_buf = None
+
+
+def l2_flush():
+    global _flush_buf
+    if _flush_buf is None:
+        _flush_buf = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")
+    _flush_buf.zero_()
+
+
+def timed_call(fn, iters=8, warm=3):
+    """Median ms of ONE call, L2 flushed (512 MiB written) before every timed call."""
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(iters):
+        l2_flush()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    return statistics.median(ts)
+
+
+def timed_graph_many(make_fn, n_copies, reps=5):
+    """ms per launch with the launches of `n_copies` independent input sets captured into ONE graph
+    (back-to-back launches like the layers of a model step; the sets together exceed L2)."""
+    fns = [make_fn(i) for i in range(n_copies)]
+
+    def all_():
+        for f in fns:
+            f()
+
+    g = capture(all_)
+    return time_replays(g, reps, 2, torch.cuda.synchronize) / n_copies
+
+
+def decode_inputs(B, lens_l, Hq, Hkv, n_copies, shared_pages=0, seed=0):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    lens = torch.tensor(lens_l, dtype=torch.int32, device="cuda")
+    pages = [(c + BLOCK - 1) // BLOCK for c in lens_l]
+    W = max(pages)
+    own = [p - min(shared_pages, p) for p in pages]
+    nb = shared_pages + sum(own) + 4
+    sets = []
+    for _ in range(n_copies):
+        perm = torch.randperm(nb, generator=g, device="cuda").to(torch.int32).cpu()
+        bt = torch.full((B, W), -1, dtype=torch.int32)
+        at = shared_pages
+        for b, (p, o) in enumerate(zip(pages, own)):
+            s = p - o
+            bt[b, :s] = perm[:s]
+            bt[b, s:p] = perm[at:at + o]
+            at += o
+        bt = bt.cuda()
+        kc = torch.empty(nb, BLOCK, Hkv, D, dtype=torch.bfloat16, device="cuda").normal_(generator=g)
+        vc = torch.empty(nb, BLOCK, Hkv, D, dtype=torch.bfloat16, device="cuda").normal_(generator=g)
+        q = torch.empty(B, Hq, D, dtype=torch.bfloat16, device="cuda").normal_(generator=g)
+        sets.append((q, kc, vc, bt))
+    unique_tokens = shared_pages * BLOCK + sum(c - min(shared_pages * BLOCK, c) for c in lens_l)
+    io = 2 * B * Hq * D * 2 + 4 * sum(pages) + 4 * B
+    return lens, sets, unique_tokens * Hkv * D * 4 + io, sum(lens_l) * Hkv * D * 4 + io
+
+
+def extra_decode(name, B, ctx, Hq, Hkv, shared_tokens=0, ref=True):
+    from byox_vllm_b200.attention import (cascade_chunks, cascade_plan, decode_num_splits,
+                                          paged_decode)
+
+    lens_l = context_lengths(dict(ctx=ctx, batch=B))
+    per_copy = sum(lens_l) * Hkv * D * 4
+    n_copies = max(2, min(24, -(-(400 << 20) // max(per_copy, 1))))
+    sp = shared_tokens // BLOCK
+    lens, sets, alg, logical = decode_inputs(B, lens_l, Hq, Hkv, n_copies, sp)
+    scale = D ** -0.5
+    W = sets[0][3].size(1)
+    outs = [torch.empty_like(s[0]) for s in sets]
+    chunks = cascade_chunks(B, Hq, Hkv, W, BLOCK) if sp else 0
+    plans = [cascade_plan(lens, s[3], BLOCK) if chunks else None for s in sets]
+
+    def ours(i):
+        q, kc, vc, bt = sets[i]
+        return lambda: paged_decode(q, kc, vc, lens, bt, scale, out=outs[i], plan=plans[i],
+                                    prefix_chunks=chunks)
+
+    ms = timed_graph_many(ours, n_copies)
+    pk, pk_kind = peaks()
+    rec = {"workload": name, "batch": B, "ctx": f"{min(lens_l)}-{max(lens_l)}",
+           "heads": f"{Hq}/{Hkv}", "bound": "hbm", "ms_per_launch": ms,
+           "algorithmic_bytes_per_launch": alg, "achieved": alg / ms / 1e6, "peak": pk["hbm_gbs"],
+           "unit": "GB/s", "frac": alg / ms / 1e6 / pk["hbm_gbs"],
+           "frac_of_8TBs_nominal": alg / ms / 1e6 / 8000.0, "peak_kind": pk_kind,
+           "decode_ctas": decode_num_splits(B, Hkv, W, BLOCK),
+           "timing": f"{n_copies} independent cache sets ({n_copies * per_copy / 1e9:.2f} GB > L2) "
+                     f"captured back to back in one graph, CUDA events"}
+    if sp:
+        rec.update(shared_prefix_tokens=sp * BLOCK, cascade_chunks=chunks,
+                   logical_bytes_per_launch=logical, effective_gbs=logical / ms / 1e6,
+                   note="achieved = unique-page bytes (each physical page once); effective = "
+                        "per-row bytes (may exceed the peak: shared pages are attended once)")
+    try:
+        if not ref:
+            raise ImportError("reference leg not requested")
+        from flash_attn import flash_attn_with_kvcache
+
+        def fa(i):
+            q, kc, vc, bt = sets[i]
+            q4 = q.unsqueeze(1)
+            return lambda: flash_attn_with_kvcache(q4, kc, vc, cache_seqlens=lens, block_table=bt,
+                                                   softmax_scale=scale, causal=True)
+
+        ms_fa = timed_graph_many(fa, n_copies)
+        ref = flash_attn_with_kvcache(sets[0][0].unsqueeze(1), sets[0][1], sets[0][2],
+                                      cache_seqlens=lens, block_table=sets[0][3],
+                                      softmax_scale=scale, causal=True).squeeze(1)
+        ours(0)()
+        torch.cuda.synchronize()
+        rec.update(flash_attn_ms=ms_fa, vs_flash_attn=ms_fa / ms,
+                   max_abs_diff_vs_flash_attn=(outs[0].float() - ref.float()).abs().max().item())
+    except ImportError as e:
+        rec["flash_attn_unavailable"] = str(e)
+    del sets, outs
+    torch.cuda.empty_cache()
+    return rec
+
+
+def prefill_flops(lens, cached, Hq):
+    fl = 0
+    for n, c in zip(lens, cached):
+        lq = n - c
+        fl += 4 * Hq * D * (lq * c + lq * (lq + 1) // 2)
+    return fl
+
+
+def extra_prefill(name, lens, cached, Hq, Hkv):
+    import random
+
+    from byox_vllm_b200.attention import prefill_varlen
+    from tools import metadata_ref as md
+
+    if lens is None:  # the reference bench's prefill step: ~24 prompts of 100-1024 tokens
+        rng = random.Random(0)
+        lens = [rng.randint(100, 1024) for _ in range(24)]
+    cached = cached or [0] * len(lens)
+    g = torch.Generator(device="cuda").manual_seed(1)
+    need = [(n + BLOCK - 1) // BLOCK for n in lens]
+    nb = sum(need) + 2
+    ids = torch.randperm(nb, generator=g, device="cuda").tolist()
+    seqs, at = [], 0
+    for n, nbk, c in zip(lens, need, cached):
+        seqs.append(md.SeqState(n, ids[at:at + nbk], c))
+        at += nbk
+    m = md.prepare_prefill(seqs, BLOCK)
+    total_q = sum(n - c for n, c in zip(lens, cached))
+    q = torch.empty(total_q, Hq, D, dtype=torch.bfloat16, device="cuda").normal_(generator=g)
+    cu_q, cu_k = m["cu_seqlens_q"].cuda(), m["cu_seqlens_k"].cuda()
+    scale = D ** -0.5
+    if any(cached):
+        kc = torch.empty(nb, BLOCK, Hkv, D, dtype=torch.bfloat16, device="cuda").normal_(generator=g)
+        vc = torch.empty_like(kc).normal_(generator=g)
+        k, v, bt = kc, vc, m["block_tables"].cuda()
+    else:
+        packed = torch.empty(total_q, (Hq + 2 * Hkv) * D, dtype=torch.bfloat16,
+                             device="cuda").normal_(generator=g)
+        k = packed[:, Hq * D:(Hq + Hkv) * D].contiguous().view(total_q, Hkv, D)
+        v = packed[:, (Hq + Hkv) * D:].view(total_q, Hkv, D)
+        bt = None
+    o = torch.empty_like(q)
+    fl = prefill_flops(lens, cached, Hq)
+    ms = timed_call(lambda: prefill_varlen(q, k, v, cu_q, cu_k, m["max_seqlen_q"],
+                                           m["max_seqlen_k"], scale, block_tables=bt, out=o))
+    pk, pk_kind = peaks()
+    rec = {"workload": name, "heads": f"{Hq}/{Hkv}", "total_q": total_q, "bound": "tensor",
+           "ms_per_launch": ms, "algorithmic_flops_per_launch": fl, "achieved": fl / ms / 1e9,
+           "peak": pk["bf16_tflops"], "unit": "TFLOP/s", "frac": fl / ms / 1e9 / pk["bf16_tflops"],
+           "peak_kind": pk_kind + " (burst: kernel timed alone)",
+           "timing": "one call, L2 flushed before each, CUDA events, median of 8"}
+    try:
+        from flash_attn import flash_attn_varlen_func
+
+        fa = lambda: flash_attn_varlen_func(  # noqa: E731
+            q, k, v, max_seqlen_q=m["max_seqlen_q"], cu_seqlens_q=cu_q,
+            max_seqlen_k=m["max_seqlen_k"], cu_seqlens_k=cu_k, softmax_scale=scale, causal=True,
+            block_table=bt)
+        ms_fa = timed_call(fa)
+        rec.update(flash_attn_ms=ms_fa, vs_flash_attn=ms_fa / ms,
+                   max_abs_diff_vs_flash_attn=(o.float() - fa().float()).abs().max().item())
+    except ImportError as e:
+        rec["flash_attn_unavailable"] = str(e)
+    del q, k, v, o
+    torch.cuda.empty_cache()
+    return rec
+
+
+def extra_store(N, Hq, Hkv):
+    from byox_vllm_b200.attention import store_kvcache
+
+    row = Hkv * D
+    g = torch.Generator(device="cuda").manual_seed(N)
+    k = torch.empty(N, Hkv, D, dtype=torch.bfloat16, device="cuda").normal_(generator=g)
+    packed = torch.empty(N, (Hq + 2 * Hkv) * D, dtype=torch.bfloat16,
+                         device="cuda").normal_(generator=g)
+    v = packed[:, (Hq + Hkv) * D:].view(N, Hkv, D)
+    nb = max(64, (N + BLOCK - 1) // BLOCK * 2)
+    kc = torch.zeros(nb, BLOCK, Hkv, D, dtype=torch.bfloat16, device="cuda")
+    vc = torch.zeros_like(kc)
+    slots = torch.randperm(nb * BLOCK, generator=g, device="cuda")[:N].to(torch.int32)
+    alg = N * row * 2 * 2 * 2 + 4 * N
+    ms = timed_call(lambda: store_kvcache(k, v, kc, vc, slots), iters=12)
+    pk, pk_kind = peaks()
+    rec = {"workload": f"store_kvcache {N} tokens x Hkv {Hkv}", "bound": "hbm", "ms_per_launch": ms,
+           "algorithmic_bytes_per_launch": alg, "achieved": alg / ms / 1e6, "peak": pk["hbm_gbs"],
+           "unit": "GB/s", "frac": alg / ms / 1e6 / pk["hbm_gbs"], "peak_kind": pk_kind,
+           "timing": "one call, L2 flushed before each, CUDA events, median of 12"}
+    mods, why = load_reference_attention()
+    if mods:
+        kc2, vc2 = torch.zeros_like(kc), torch.zeros_like(vc)
+        ms_ref = timed_call(lambda: mods[0].store_kvcache(k, v, kc2, vc2, slots), iters=12)
+        rec.update(reference_triton_ms=ms_ref, vs_reference=ms_ref / ms,
+                   bit_equal=bool(torch.equal(kc, kc2) and torch.equal(vc, vc2)))
+    else:
+        rec["reference_unavailable"] = why
+    return rec
+
+
+def run_extras(which):
+    out = {}
+    with torch.inference_mode():
+        if "c3" in which:
+            out["c3_decode_b128_ctx4096"] = extra_decode(
+                "c3: batch 128 x ctx 4096, 32/8", 128, 4096, 32, 8)
+        if "c4" in which:
+            out["c4_decode_tp8_rank"] = extra_decode(
+                "c4 per rank: batch 256 x ctx 8192, 7680 shared, 8/1 (cascade)", 256, 8192, 8, 1,
+                shared_tokens=7680)
+        if "c5" in which:
+            for B, ctx in ((64, 4096), (16, 4096), (1, 131072), (512, 1024), (16, 1024)):
+                out[f"c5_decode_b{B}_ctx{ctx}"] = extra_decode(
+                    f"c5: batch {B} x ctx {ctx}, 32/8", B, ctx, 32, 8)
+        if "tp8" in which:
+            for Hq, Hkv, tp in ((2, 1, 8), (4, 2, 4), (8, 4, 2)):
+                out[f"c2_decode_tp{tp}_rank"] = extra_decode(
+                    f"c2 per rank at TP={tp}: batch 256, bench lengths, {Hq}/{Hkv}", 256, "bench",
+                    Hq, Hkv)
+        if "prefill" in which:
+            for name, lens, cached, Hq, Hkv in (
+                    ("bench24", None, None, 16, 8), ("16x1024", [1024] * 16, None, 16, 8),
+                    ("4x4096", [4096] * 4, None, 32, 8), ("1x16384", [16384], None, 32, 8),
+                    ("32x(7680+512)", [8192] * 32, [7680] * 32, 8, 1)):
+                out[f"prefill_{name}"] = extra_prefill(name, lens, cached, Hq, Hkv)
+        if "store" in which:
+            out["store_16384x8"] = extra_store(16384, 32, 8)
+            out["store_16384x1"] = extra_store(16384, 4, 1)
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
+# engine leg: the unmodified reference engine end to end (single GPU)
+# ------------------------------------------------------------------------------------------------
+def run_engine_e2e(budget_s=300):
+    """BASELINE config 2 through baseline/_ref's LLM.generate (tools/e2e_nanovllm.py), three arms
+    in subprocesses: reference attention; the drop-in at the frozen Attention.forward boundary
+    (no fused QKV, no device-side metadata); the drop-in with every SURVEY §8(f) row enabled."""
+    if not (ROOT / "baseline" / "_ref" / "nanovllm").exists():
+        return {"skipped": "baseline/_ref is not installed"}
+    arms = (("ref", "ref", {}),
+            ("ours_frozen", "ours", {"B200ATTN_FUSE_QKV": "0", "B200ATTN_FAST_META": "0"}),
+            ("ours_full", "ours", {}))
+    res = {"workload": "Qwen3-0.6B random-init, 256 seqs, in/out 100-1024 (reference "
+                       "bench.py:17-42), CUDA graphs on, TP=1; tokens/s = sum(max_tokens) / wall "
+                       "of generate()"}
+    for key, impl, env_extra in arms:
+        env = dict(os.environ, **env_extra)
+        for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT"):
+            env.pop(k, None)
+        t0 = time.time()
+        try:
+            r = subprocess.run([sys.executable, str(ROOT / "tools" / "e2e_nanovllm.py"), "--impl",
+                                impl, "--model", "0.6b"], env=env, capture_output=True, text=True,
+                               timeout=budget_s)
+        except subprocess.TimeoutExpired:
+            res[key] = {"error": f"timeout after {budget_s} s"}
+            continue
+        line = [ln for ln in r.stdout.splitlines() if ln.startswith('{"tool"')]
+        if r.returncode != 0 or not line:
+            res[key] = {"error": (r.stderr or r.stdout)[-400:]}
+            continue
+        j = json.loads(line[-1])
+        res[key] = {"tok_s": j["tokens_per_s"], "decode_tok_s": j["decode_tokens_per_s"],
+                    "prefill_tok_s": j["prefill_tokens_per_s"],
+                    "wall_s": round(time.time() - t0, 1)}
+    if all("tok_s" in res.get(k, {}) for k in ("ref", "ours_frozen", "ours_full")):
+        res.update(ref_tok_s=res["ref"]["tok_s"], ours_frozen_tok_s=res["ours_frozen"]["tok_s"],
+                   ours_full_tok_s=res["ours_full"]["tok_s"],
+                   frozen_vs_ref=res["ours_frozen"]["tok_s"] / res["ref"]["tok_s"],
+                   full_vs_ref=res["ours_full"]["tok_s"] / res["ref"]["tok_s"])
+    return res
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU legs
+# ------------------------------------------------------------------------------------------------
+def cpu_reference(w, steps, warmup, budget_s=20.0):
     """The CPU restatement (oracle/) of store_kvcache + paged decode, timed on the host cores on a
-    bounded sample: ONE layer of the workload over the first `sample_seqs` sequences; tokens/s is
-    scaled by the layer count (layers are identical work)."""
+    bounded sample: ONE layer of the workload over its first CPU_SAMPLE_SEQS sequences; tokens/s
+    is scaled by the layer count (layers are identical work). Both CPU legs use this sample."""
     from oracle import attention_oracle as orc  # timed CPU baseline leg
     from tools import synth
 
     lens = context_lengths(w)
-    n = min(sample_seqs or len(lens), len(lens))
+    n = min(CPU_SAMPLE_SEQS, len(lens))
     case = synth.decode_case(n, lens[:n], w["Hq"], w["Hkv"], seed=0)
     ctx = type("Ctx", (), dict(case.meta))()
 
@@ -346,7 +789,10 @@ def cpu_reference(w, steps, warmup, sample_seqs=None, budget_s=20.0):
             break
     t = statistics.median(times)
     tok_s = n / (t * w["layers"])
-    return tok_s, t, n, len(times)
+    sample = (f"1 of {w['layers']} layers x first {n} of {w['batch']} sequences (store + paged "
+              f"decode, fp32 torch on CPU), {len(times)} timed passes, median {t * 1e3:.1f} "
+              f"ms/pass; tokens/s = {n} / (pass time x {w['layers']} layers)")
+    return tok_s, t, n, len(times), sample
 
 
 def run_reference(args, w, rank, world):
@@ -354,14 +800,15 @@ def run_reference(args, w, rank, world):
         return None
     # torchrun exports OMP_NUM_THREADS=1; the reference arm uses every host thread it can.
     torch.set_num_threads(len(os.sched_getaffinity(0)))
-    tok_s, t, n, done = cpu_reference(w, args.steps, max(args.warmup, 1), budget_s=120.0)
+    tok_s, t, n, done, sample = cpu_reference(w, args.steps, max(args.warmup, 1), budget_s=120.0)
     cores = torch.get_num_threads()
-    sample = (f"1 of {w['layers']} layers x {n} of {w['batch']} sequences (store + paged decode, "
-              f"fp32 torch on CPU), {done} timed passes, tokens/s scaled by the layer count")
     return {
         "impl": "reference", "metric": "decode tokens/sec (bench.py shape)", "value": tok_s,
         "unit": "tokens/s", "n_gpus": world, "steps": done, "warmup": max(args.warmup, 1),
-        "ms_per_step": t * w["layers"] * 1e3, "higher_is_better": True, "scaling": "strong",
+        # extrapolated: one full-batch step of all layers at the sampled rate (the timed pass is
+        # 1 layer x n sequences; the driver's wall clock sees only the sampled passes)
+        "ms_per_step": w["batch"] / tok_s * 1e3, "ms_per_sampled_pass": t * 1e3,
+        "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{args.workload}: {w['model']} attention path on host cores",
                    "parallelism": "cpu"},
@@ -379,12 +826,25 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS) + list(EXTRA_ONLY))
+    ap.add_argument("--extras", default=None,
+                    help="comma list of extra blocks (c3,c4,c5,tp8,prefill,store) or 'none'; "
+                         "default: all at N=1, none at N>1")
+    ap.add_argument("--engine", default=None, choices=["on", "off"],
+                    help="run the reference-engine e2e arms (default: on at N=1; "
+                         "B200_BENCH_ENGINE=0 turns it off)")
     args = ap.parse_args()
-    w = WORKLOADS[args.workload]
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.workload in EXTRA_ONLY:
+        assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+        torch.cuda.set_device(local)
+        if rank == 0:
+            print(json.dumps({"extra": run_extras({args.workload})}), flush=True)
+        return
+    w = WORKLOADS[args.workload]
 
     if args.impl == "reference":
         line = run_reference(args, w, rank, world)
@@ -403,14 +863,21 @@ def main():
             line = run_ours(args, w, rank, world, dev)
         if rank == 0 and world > 1:
             line["cpu_baseline"] = None  # timed at N=1 only
+            if args.extras and args.extras != "none":
+                line["extra"] = run_extras(set(args.extras.split(",")))
             print(json.dumps(line), flush=True)
         elif rank == 0:
-            tok_s, t, n, done = cpu_reference(w, 5, 1, sample_seqs=64, budget_s=20.0)
-            line["cpu_baseline"] = {
-                "value": tok_s, "unit": "tokens/s", "cores": torch.get_num_threads(),
-                "kind": "port",
-                "sample": f"1 of {w['layers']} layers x {n} of {w['batch']} sequences, {done} "
-                          f"passes, median {t * 1e3:.1f} ms/layer, scaled by the layer count"}
+            extras = args.extras or "c3,c4,c5,tp8,prefill,store"
+            if extras != "none":
+                line["extra"] = run_extras(set(extras.split(",")))
+            engine = args.engine or ("off" if os.environ.get("B200_BENCH_ENGINE") == "0" else "on")
+            if engine == "on":
+                torch.cuda.empty_cache()
+                line["engine_e2e"] = run_engine_e2e()
+            tok_s, t, n, done, sample = cpu_reference(w, 5, 1, budget_s=20.0)
+            line["cpu_baseline"] = {"value": tok_s, "unit": "tokens/s",
+                                    "cores": torch.get_num_threads(), "kind": "port",
+                                    "sample": sample}
             print(json.dumps(line), flush=True)
     finally:
         if world > 1:

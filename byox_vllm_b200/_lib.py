@@ -12,7 +12,7 @@ from pathlib import Path
 
 LIB_PATH = Path(__file__).resolve().parent / "libb200attn.so"
 
-ABI_VERSION = 7
+ABI_VERSION = 8
 DTYPE_BF16 = 0
 
 E_BADARG = -1
@@ -30,7 +30,8 @@ PROTOTYPES = {
     "b200attn_store_kvcache": (
         _i32, [_vp, _i64, _vp, _i64, _vp, _vp, _vp, _i32, _i32, _i64, _i32, _vp]),
     "b200attn_decode_pick_splits": (_i32, [_i32, _i32, _i32, _i32, _i32]),
-    "b200attn_decode_workspace_bytes": (_sz, [_i32, _i32, _i32, _i32]),
+    "b200attn_decode_partition_host": (_i32, [_vp, _i32, _i32, _i32, _i32, _i32, _vp, _i32]),
+    "b200attn_decode_workspace_bytes": (_sz, [_i32, _i32, _i32, _i32, _i32]),
     "b200attn_decode": (
         _i32, [_vp, _vp, _vp, _vp, _i64, _i32, _vp, _vp, _vp, _sz,
                _i32, _i32, _i32, _i32, _i32, _i64, _f32, _i32, _i32, _vp]),

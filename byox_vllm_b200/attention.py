@@ -83,8 +83,13 @@ def ensure_split_counters(device: torch.device) -> None:
     reference warms every batch size up eagerly before capturing it, model_runner.py:281), kept
     alive for the life of the process; every launch leaves them zero."""
     idx = device.index if device.index is not None else torch.cuda.current_device()
-    if idx in _SPLIT_COUNTERS or torch.cuda.is_current_stream_capturing():
+    if idx in _SPLIT_COUNTERS:
         return
+    if torch.cuda.is_current_stream_capturing():
+        raise RuntimeError(
+            "byox_vllm_b200: the decode arrival counters must be registered before CUDA-graph "
+            "capture; run one eager decode step (or attention.ensure_split_counters(device)) "
+            "first, as ModelRunner's warm-up before capture does (model_runner.py:281)")
     with torch.cuda.device(idx):
         buf = torch.zeros(_SPLIT_COUNTER_SLOTS, dtype=torch.int32, device=device)
         torch.cuda.current_stream(device).synchronize()
@@ -94,7 +99,9 @@ def ensure_split_counters(device: torch.device) -> None:
 
 
 def decode_num_splits(batch: int, num_kv_heads: int, table_width: int, block_size: int) -> int:
-    """Host-only split heuristic (a function of host-visible sizes: graph-capture rule)."""
+    """Host-only choice of the number of persistent CTAs the batch's KV tile stream is cut into
+    (a function of host-visible sizes: graph-capture rule; the cut itself happens on the device
+    from context_lens)."""
     lib = _lib.load()
     return lib.b200attn_decode_pick_splits(batch, num_kv_heads, table_width, block_size,
                                            lib.b200attn_sm_count())
@@ -173,8 +180,8 @@ def paged_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
     ws, ws_bytes = None, 0
     if num_splits > 1:
         ensure_split_counters(q.device)
-    if num_splits + prefix_chunks > 1:
-        ws_bytes = lib.b200attn_decode_workspace_bytes(B, Hq, D, num_splits + prefix_chunks)
+    if num_splits > 1 or prefix_chunks > 0:
+        ws_bytes = lib.b200attn_decode_workspace_bytes(B, Hq, D, num_splits, prefix_chunks)
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=q.device)
     stream = _stream(q.device)
     if key is not None:

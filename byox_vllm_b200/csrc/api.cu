@@ -159,7 +159,8 @@ int check_attn_shape(int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim
 
 }  // namespace
 
-// Caller-registered arrival counters for the in-launch split merge, per device.
+// Caller-registered zeroed counters, per device: arrival counters of the in-launch merge of cut
+// rows + the two counters of the dynamic work distribution (the last two of the buffer).
 struct SplitCounters {
     int32_t* ptr = nullptr;
     int64_t count = 0;
@@ -167,12 +168,7 @@ struct SplitCounters {
 static SplitCounters g_split_counters[64];
 static std::mutex g_split_counters_mu;
 
-static int32_t* split_counters_for(int64_t need) {
-    static const bool enabled = [] {
-        const char* e = std::getenv("B200ATTN_FUSED_MERGE");
-        return !(e && e[0] == '0');
-    }();
-    if (!enabled) return nullptr;
+static int32_t* split_counters_for(int64_t need, int32_t** sched) {
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
         (void)cudaGetLastError();
@@ -180,7 +176,9 @@ static int32_t* split_counters_for(int64_t need) {
     }
     std::lock_guard<std::mutex> lock(g_split_counters_mu);
     const SplitCounters& c = g_split_counters[dev];
-    return (c.ptr != nullptr && c.count >= need) ? c.ptr : nullptr;
+    if (c.ptr == nullptr || c.count < need) return nullptr;
+    *sched = c.ptr + c.count - 2;  // the last two counters drive the dynamic work distribution
+    return c.ptr;
 }
 
 // Shared body of every decode entry point. `nr` != nullptr: q / key are raw QKV-projection rows
@@ -207,8 +205,10 @@ static int store_decode_impl(const void* q, int64_t q_row_stride, const void* ke
     if (batch < 0 || num_blocks <= 0 || table_width < 0 || num_splits < 1)
         return fail(B200ATTN_E_BADARG, "negative or zero size");
     if (batch == 0) return 0;
-    if (batch > 65535) return fail(B200ATTN_E_UNSUPPORTED, "batch %d > 65535", batch);
-    if (num_splits > 64) return fail(B200ATTN_E_UNSUPPORTED, "num_splits %d > 64", num_splits);
+    if (num_splits > 2048) return fail(B200ATTN_E_UNSUPPORTED, "num_splits %d > 2048", num_splits);
+    if (prefix_chunks > 0 && batch > b200::kDecodeMaxBatch)
+        return fail(B200ATTN_E_UNSUPPORTED, "cascade decode handles at most %d rows, got %d",
+                    b200::kDecodeMaxBatch, batch);
     if (!q || !k_cache || !v_cache || !block_tables || !context_lens || !out)
         return fail(B200ATTN_E_BADARG, "null pointer");
     if (!std::isfinite(scale)) return fail(B200ATTN_E_BADARG, "scale is not finite");
@@ -218,12 +218,13 @@ static int store_decode_impl(const void* q, int64_t q_row_stride, const void* ke
                     static_cast<long long>(num_slots));
     if (!aligned16(q) || !aligned16(out) || !aligned16(k_cache) || !aligned16(v_cache))
         return fail(B200ATTN_E_BADARG, "pointers must be 16-byte aligned");
-    const int32_t ws_slots = num_splits + prefix_chunks;
-    if (ws_slots > 1) {
-        const size_t need = b200::decode_workspace_bytes(batch, num_q_heads, ws_slots);
+    if (q_row_stride % 8 != 0) return fail(B200ATTN_E_BADARG, "q rows must be 16-byte aligned");
+    if (num_splits > 1 || prefix_chunks > 0) {
+        const size_t need =
+            b200::decode_workspace_bytes(batch, num_q_heads, num_splits, prefix_chunks);
         if (!workspace || workspace_bytes < need || !aligned16(workspace))
             return fail(B200ATTN_E_WORKSPACE,
-                        "workspace %zu B < %zu B needed for %d splits + %d prefix chunks",
+                        "workspace %zu B < %zu B needed for %d CTA ranges + %d prefix chunks",
                         workspace_bytes, need, num_splits, prefix_chunks);
     }
     cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -269,7 +270,9 @@ static int store_decode_impl(const void* q, int64_t q_row_stride, const void* ke
     p.num_kv_heads = num_kv_heads;
     p.group = num_q_heads / num_kv_heads;
     p.block_size = block_size;
-    p.num_splits = num_splits;
+    p.num_ctas = num_splits;
+    p.tun = b200::decode_tunables();
+    if (num_splits == 1) p.tun.waves = 1;  // no counters: static regime (one CTA walks every item)
     p.scale_log2 = scale * 1.4426950408889634f;
     if (with_store && fused_store) {
         p.new_key = key;
@@ -281,18 +284,23 @@ static int store_decode_impl(const void* q, int64_t q_row_stride, const void* ke
         p.value_row_stride = value_row_stride;
         p.num_slots = num_slots;
     }
-    if (ws_slots > 1) {
-        p.ws_o = static_cast<float*>(workspace);
-        p.ws_lse = p.ws_o + static_cast<size_t>(batch) * num_q_heads * ws_slots * b200::kHeadDim;
-    }
+    b200::decode_workspace_layout(workspace, batch, num_q_heads, num_splits, prefix_chunks, &p);
     p.plan = plan;
     p.prefix_chunks = prefix_chunks;
-    if (num_splits > 1)
-        p.split_counters = split_counters_for(static_cast<int64_t>(batch) * num_kv_heads);
+    if (num_splits > 1) {
+        const int64_t rows = batch < b200::kDecodeMaxBatch ? batch : b200::kDecodeMaxBatch;
+        // layout of the registered buffer: [rows * Hkv arrival counters | ... | sched[2] at the end]
+        p.split_counters = split_counters_for(rows * num_kv_heads + 2, &p.sched);
+        if (p.split_counters == nullptr)
+            return fail(B200ATTN_E_WORKSPACE,
+                        "num_splits %d > 1 needs %lld zeroed counters registered with "
+                        "b200attn_set_split_counters on this device",
+                        num_splits, static_cast<long long>(rows * num_kv_heads + 2));
+    }
     if (prefix_chunks > 0) {
         // Shared-prefix pass first (tcgen05): B*G query rows of every KV head against the P
-        // shared pages, partials into workspace slots [num_splits, num_splits + prefix_chunks).
-        // It never touches the slot the fused scatter writes (that token lies after the prefix).
+        // shared pages, partials into the prefix region of the workspace. It never touches the
+        // slot the fused scatter writes (that token lies after the prefix).
         const int group = num_q_heads / num_kv_heads;
         CUtensorMap q_map, k_map128, v_map128;
         if (int rc = encode_rows_map(q, num_q_heads, batch,
@@ -314,17 +322,39 @@ static int store_decode_impl(const void* q, int64_t q_row_stride, const void* ke
         pp.block_size = block_size;
         pp.scale_log2 = p.scale_log2;
         pp.plan = plan;
-        pp.ws_o = p.ws_o;
-        pp.ws_lse = p.ws_lse;
+        pp.ws_o = p.prefix_o;
+        pp.ws_lse = p.prefix_lse;
         pp.batch = batch;
         pp.prefix_chunks = prefix_chunks;
-        pp.ws_slot0 = num_splits;
-        pp.ws_slots = ws_slots;
+        pp.ws_slot0 = 0;
+        pp.ws_slots = prefix_chunks;
         cudaError_t e0 = b200::launch_cascade_prefix(pp, q_map, k_map128, v_map128, st);
         if (e0 != cudaSuccess) return cuda_fail(e0, "cascade prefix launch");
     }
-    cudaError_t e = b200::launch_decode(p, k_map, v_map, st);
-    return e == cudaSuccess ? 0 : cuda_fail(e, "decode launch");
+    // The kernel keeps the scan of the batch in shared memory: larger batches (eager decode above
+    // the graph sizes, model_runner.py:230) run as consecutive launches over row blocks.
+    for (int32_t row0 = 0; row0 < batch; row0 += b200::kDecodeMaxBatch) {
+        b200::DecodeParams pc = p;
+        const int32_t rows = batch - row0 < b200::kDecodeMaxBatch ? batch - row0
+                                                                  : b200::kDecodeMaxBatch;
+        pc.batch = rows;
+        pc.q = static_cast<const __nv_bfloat16*>(q) + static_cast<int64_t>(row0) * q_row_stride;
+        pc.out = static_cast<__nv_bfloat16*>(out) +
+                 static_cast<int64_t>(row0) * num_q_heads * head_dim;
+        pc.block_tables = block_tables + static_cast<int64_t>(row0) * table_row_stride;
+        pc.context_lens = context_lens + row0;
+        if (pc.new_key) {
+            pc.new_key = static_cast<const __nv_bfloat16*>(key) +
+                         static_cast<int64_t>(row0) * key_row_stride;
+            pc.new_value = static_cast<const __nv_bfloat16*>(value) +
+                           static_cast<int64_t>(row0) * value_row_stride;
+            pc.slot_mapping = slot_mapping + row0;
+        }
+        if (pc.nr.positions) pc.nr.positions += row0;
+        cudaError_t e = b200::launch_decode(pc, k_map, v_map, st);
+        if (e != cudaSuccess) return cuda_fail(e, "decode launch");
+    }
+    return 0;
 }
 
 
@@ -376,13 +406,25 @@ int b200attn_store_kvcache(const void* key, int64_t key_row_stride, const void* 
 int b200attn_decode_pick_splits(int32_t batch, int32_t num_kv_heads, int32_t table_width,
                                 int32_t block_size, int32_t sm_count) {
     if (sm_count <= 0) sm_count = 148;
-    return b200::decode_pick_splits(batch, num_kv_heads, table_width, block_size, sm_count);
+    return b200::decode_pick_ctas(batch, num_kv_heads, table_width, block_size, sm_count);
+}
+
+int b200attn_decode_partition_host(const int32_t* context_lens, int32_t batch,
+                                   int32_t num_kv_heads, int32_t num_splits, int32_t shared_pages,
+                                   int32_t block_size, int32_t* pieces, int32_t max_pieces) {
+    if (batch < 0 || num_kv_heads <= 0 || num_splits < 1 || shared_pages < 0 ||
+        block_size <= 0 || block_size % 64 != 0 || max_pieces < 0)
+        return fail(B200ATTN_E_BADARG, "bad sizes");
+    if (batch > 0 && !context_lens) return fail(B200ATTN_E_BADARG, "null context_lens");
+    if (max_pieces > 0 && !pieces) return fail(B200ATTN_E_BADARG, "null pieces");
+    return b200::decode_partition_host(context_lens, batch, num_kv_heads, num_splits, shared_pages,
+                                       block_size, pieces, max_pieces);
 }
 
 size_t b200attn_decode_workspace_bytes(int32_t batch, int32_t num_q_heads, int32_t head_dim,
-                                       int32_t num_splits) {
+                                       int32_t num_splits, int32_t prefix_chunks) {
     if (batch <= 0 || num_q_heads <= 0 || head_dim != b200::kHeadDim) return 0;
-    return b200::decode_workspace_bytes(batch, num_q_heads, num_splits);
+    return b200::decode_workspace_bytes(batch, num_q_heads, num_splits, prefix_chunks);
 }
 
 int b200attn_cascade_pick_chunks(int32_t batch, int32_t num_q_heads, int32_t num_kv_heads,

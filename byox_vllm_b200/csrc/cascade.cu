@@ -105,7 +105,9 @@ int cascade_pick_chunks(int32_t batch, int32_t num_q_heads, int32_t num_kv_heads
     // so by default it is only armed where a shared prefix can pay for it: a batch that fills
     // 128-row tensor-core tiles and tables that can hold long contexts.
     const int mode = cascade_mode_from_env();
-    if (mode == 0 || batch < 2 || block_size % 128 != 0 || num_kv_heads <= 0) return 0;
+    if (mode == 0 || batch < 2 || batch > kDecodeMaxBatch || block_size % 128 != 0 ||
+        num_kv_heads <= 0)
+        return 0;
     const int group = num_q_heads / num_kv_heads;
     if (group < 1 || 128 % group != 0) return 0;
     const int64_t capacity = static_cast<int64_t>(table_width) * block_size;

@@ -5,6 +5,7 @@
 #include <cstddef>
 #include <cstdint>
 
+#include "decode_plan.cuh"
 #include "norm_rope.cuh"
 
 namespace b200 {
@@ -72,8 +73,14 @@ struct DecodeParams {
     void* out;                    // [B, Hq, 128] bf16
     const int32_t* block_tables;  // [B, table_row_stride]
     const int32_t* context_lens;  // [B]
-    float* ws_o;                  // [B, Hq, S, 128] fp32 normalised partials (S > 1)
-    float* ws_lse;                // [B, Hq, S] fp32 log2-domain log-sum-exp (S > 1)
+    // workspace (decode_workspace_layout): partial pieces of rows cut by a CTA-range boundary,
+    // two slots per CTA (2c = tail of a row the previous CTA started, 2c+1 = head of a row the
+    // next CTA continues), each [8 heads][128] normalised fp32 O + [8] log2-domain log-sum-exp
+    float* piece_o;               // [2 * num_ctas, 8, 128]   (num_ctas > 1)
+    float* piece_lse;             // [2 * num_ctas, 8]
+    // shared-prefix partials written by the cascade prefix pass
+    float* prefix_o;              // [B * Hq, prefix_chunks, 128]   (prefix_chunks > 0)
+    float* prefix_lse;            // [B * Hq, prefix_chunks]
     int64_t table_row_stride;
     int32_t table_width;
     int32_t batch;
@@ -81,8 +88,9 @@ struct DecodeParams {
     int32_t num_kv_heads;
     int32_t group;  // Hq / Hkv, 1..8
     int32_t block_size;
-    int32_t num_splits;
-    float scale_log2;  // softmax scale * log2(e)
+    int32_t num_ctas;   // persistent CTAs
+    StreamTunables tun; // partition tunables (decode_plan.cuh)
+    float scale_log2;   // softmax scale * log2(e)
     // optional fused scatter of this step's K/V rows (nullptr => no store)
     const void* new_key;
     const void* new_value;
@@ -94,7 +102,7 @@ struct DecodeParams {
     int64_t num_slots;
     // optional shared-prefix cascade (cascade.cu): plan[0] = leading pages shared by every active
     // row (device-resident, written by cascade_plan_kernel); their attention was computed by the
-    // prefix kernel into workspace slots [num_splits, num_splits + prefix_chunks).
+    // prefix kernel into the prefix region of the workspace.
     const int32_t* plan;
     int32_t prefix_chunks;  // 0 => no cascade
     // optional fused q/k RMSNorm + RoPE (norm_rope.cuh): with nr.positions set, q
@@ -102,16 +110,32 @@ struct DecodeParams {
     // loaded into registers, the new K row while it is scattered (needs new_key / slot_mapping).
     int64_t q_row_stride;  // elements between q rows of consecutive sequences
     NormRopeArgs nr;
-    // optional in-launch merge (num_splits > 1): zeroed int32 arrival counters, one per
-    // (sequence, KV head); the split CTA that arrives last merges the partials itself and resets
-    // the counter, so no merge kernel is launched. nullptr => separate decode_merge_kernel.
+    // in-launch merge (num_ctas > 1): zeroed int32 arrival counters, one per (sequence, KV
+    // head); the piece of a cut row that arrives last merges the partials itself and resets the
+    // counter, so no merge kernel is launched. Required when num_ctas > 1.
     int32_t* split_counters;
+    // dynamic work distribution (num_ctas > 1): sched[0] = next work item beyond the first wave,
+    // sched[1] = CTAs finished; both zero between launches (the last CTA resets them).
+    int32_t* sched;
 };
 cudaError_t launch_decode(const DecodeParams& p, const CUtensorMap& k_map, const CUtensorMap& v_map,
                           cudaStream_t stream);
-size_t decode_workspace_bytes(int32_t batch, int32_t num_q_heads, int32_t num_splits);
-int decode_pick_splits(int32_t batch, int32_t num_kv_heads, int32_t table_width, int32_t block_size,
-                       int32_t sm_count);
+constexpr int kDecodeMaxBatch = 1024;  // rows of one launch (the scan lives in shared memory)
+size_t decode_workspace_bytes(int32_t batch, int32_t num_q_heads, int32_t num_ctas,
+                              int32_t prefix_chunks);
+void decode_workspace_layout(void* workspace, int32_t batch, int32_t num_q_heads, int32_t num_ctas,
+                             int32_t prefix_chunks, DecodeParams* p);
+int decode_pick_ctas(int32_t batch, int32_t num_kv_heads, int32_t table_width, int32_t block_size,
+                     int32_t sm_count);
+int decode_partition_host(const int32_t* context_lens, int32_t batch, int32_t num_kv_heads,
+                          int32_t num_ctas, int32_t shared_pages, int32_t block_size,
+                          int32_t* pieces, int32_t max_pieces);
+int decode_min_units();
+int decode_row_cost();
+int decode_snap();
+int decode_waves();
+int decode_dyn_min();
+StreamTunables decode_tunables();
 
 // ---- prefill_attn.cu -------------------------------------------------------------------------
 struct PrefillParams {

@@ -76,18 +76,31 @@ class DecodeMetaStager:
     def fits(self, batch: int, table_width: int) -> bool:
         return 0 < batch <= min(self.capacity, 1024) and table_width <= self.max_width
 
-    def stage(self, last_tokens, num_tokens, block_tables) -> tuple[int, int]:
-        """Pack, copy and expand. Returns (batch, table_width). Asynchronous on the current
-        stream."""
+    def _next_pinned(self) -> int:
         i = self._turn
         self._turn ^= 1
         if self._used[i]:
             self._events[i].synchronize()
+        return i
+
+    def stage(self, last_tokens, num_tokens, block_tables) -> tuple[int, int]:
+        """Pack, copy and expand. Returns (batch, table_width). Asynchronous on the current
+        stream."""
+        i = self._next_pinned()
         rec, width = pack_decode_record(last_tokens, num_tokens, block_tables, self._np[i])
-        B = len(last_tokens)
+        return self._launch(i, rec.size, len(last_tokens), width)
+
+    def stage_record(self, rec: np.ndarray, batch: int) -> tuple[int, int]:
+        """The same from an already packed record (fast_rpc: what a tensor-parallel worker gets
+        from rank 0 IS this record, so no per-sequence Python object is ever built)."""
+        width = int(rec[2 * batch:3 * batch].max()) if batch else 0
+        i = self._next_pinned()
+        self._np[i][:rec.size] = rec
+        return self._launch(i, rec.size, batch, width)
+
+    def _launch(self, i: int, n: int, B: int, width: int) -> tuple[int, int]:
         if not self.fits(B, width):
             raise ValueError(f"batch {B} x table width {width} exceeds the staged buffers")
-        n = rec.size
         self._dev[:n].copy_(self._pinned[i][:n], non_blocking=True)
         self._events[i].record()
         self._used[i] = True
@@ -221,6 +234,30 @@ def prepare_decode(self, seqs):
     return gv["input_ids"][:bs], gv["positions"][:bs]
 
 
+def prepare_decode_from_record(self, rec: np.ndarray, batch: int):
+    """prepare_decode for a tensor-parallel worker that received the packed decode record of
+    fast_rpc instead of Sequence objects. Returns (input_ids, positions) or None when the staged
+    buffers cannot take the batch (the caller then rebuilds sequence views)."""
+    import sys
+
+    from . import attention as _attn
+
+    set_context = sys.modules[_attn.get_context.__module__].set_context
+    st = None if self.enforce_eager else _stager_of(self)
+    if st is None or batch <= 0:
+        return None
+    width = int(rec[2 * batch:3 * batch].max())
+    if not st.fits(batch, width):
+        return None
+    st.stage_record(rec, batch)
+    gv = self.graph_vars
+    set_context(False, slot_mapping=gv["slot_mapping"][:batch],
+                context_lens=gv["context_lens"][:batch],
+                block_tables=gv["block_tables"][:batch, :width])
+    self._b200_meta_staged = batch
+    return gv["input_ids"][:batch], gv["positions"][:batch]
+
+
 def prepare_prefill(self, seqs):
     """ModelRunner._prepare_prefill (model_runner.py:160-204): the per-token lists (positions,
     slot_mapping) and the cu_seqlens come from one device launch; input_ids (the token ids
@@ -231,6 +268,7 @@ def prepare_prefill(self, seqs):
     from . import attention as _attn
 
     set_context = sys.modules[_attn.get_context.__module__].set_context
+    self._b200_meta_staged = 0
     if len(seqs) > 1024:
         return _ORIG["_prepare_prefill"](self, seqs)
     st = getattr(self, "_b200_prefill_stager", None)
@@ -266,8 +304,13 @@ def run_model(self, input_ids, positions, is_prefill):
     the graph inputs, replay the graph without the seven refresh copies."""
     staged = getattr(self, "_b200_meta_staged", 0)
     self._b200_meta_staged = 0
-    if is_prefill or not staged or staged != input_ids.size(0):
+    if is_prefill or not staged:
         return _ORIG["_run_model"](self, input_ids, positions, is_prefill)
+    if staged != input_ids.size(0):
+        # prepare_decode handed out views of the graph inputs: the reference's _run_model would
+        # fill_(-1) / zero_() those very buffers before copying them onto themselves
+        raise RuntimeError(f"decode metadata was staged for {staged} rows but _run_model got "
+                           f"{input_ids.size(0)}: call _prepare_decode again for this batch")
     bs = staged
     graph = self.graphs[next(x for x in self.graph_bs if x >= bs)]
     graph.replay()

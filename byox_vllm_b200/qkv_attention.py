@@ -114,7 +114,7 @@ def qkv_decode(qkv: torch.Tensor, positions: torch.Tensor, q_weight, k_weight, e
     ws, ws_bytes = None, 0
     if num_splits > 1:
         _attn.ensure_split_counters(qkv.device)
-        ws_bytes = lib.b200attn_decode_workspace_bytes(B, Hq, D, num_splits)
+        ws_bytes = lib.b200attn_decode_workspace_bytes(B, Hq, D, num_splits, 0)
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=qkv.device)
     rc = lib.b200attn_qkv_decode(
         qkv.data_ptr(), qkv.stride(0), positions.data_ptr(), _ptr(q_weight), _ptr(k_weight),

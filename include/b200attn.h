@@ -45,7 +45,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 7
+#define B200ATTN_ABI_VERSION 8
 
 #define B200ATTN_DTYPE_BF16 0
 
@@ -83,15 +83,47 @@ int b200attn_store_kvcache(const void* key, int64_t key_row_stride, const void* 
                            const int32_t* slot_mapping, int32_t n_tokens, int32_t row_elems,
                            int64_t num_slots, int32_t dtype, void* stream);
 
-/* Host-only heuristic: split count for b200attn_decode. Depends only on host-visible sizes
- * (graph-capture rule: context_lens is device-only under replay, model_runner.py:242-254). */
+/*
+ * Work partition of the decode kernel. The KV tiles (64 tokens) of the sequences of the batch,
+ * plus a small fixed cost per sequence, form one unit stream per KV head. The kernel launches
+ * `num_splits` persistent CTAs and cuts the stream into contiguous ranges ON THE DEVICE from
+ * context_lens; a work item is (range, KV head), items with adjacent ids stream the same tokens of
+ * adjacent KV heads side by side. Many short rows: ranges are whole rows (no row is cut, nothing
+ * is merged), several per CTA, and CTAs take items beyond their first from an atomic counter, so
+ * the faster SMs take more of them. Few long rows: one equal range per CTA group (num_splits /
+ * num_kv_heads groups); a range boundary cuts at most one row and cut rows are finished by the
+ * piece that arrives last (in-launch merge through the workspace). Both regimes need the counters
+ * of b200attn_set_split_counters when num_splits > 1. Any num_splits in [1, 2048] gives the same
+ * result within rounding (1 = one CTA walks the whole batch).
+ *
+ * b200attn_decode_pick_splits: host-only choice of num_splits from host-visible sizes (graph-
+ * capture rule: context_lens is device-only under replay, model_runner.py:242-254): two CTAs per
+ * SM, fewer when even full tables could not give every CTA its minimum amount of work.
+ */
 int b200attn_decode_pick_splits(int32_t batch, int32_t num_kv_heads, int32_t table_width,
                                 int32_t block_size, int32_t sm_count);
 
-/* Bytes of fp32 workspace b200attn_decode needs for (batch, num_q_heads, head_dim, num_splits).
- * 0 when num_splits <= 1. */
+/*
+ * Host-only introspection of that partition (no GPU needed; runs the kernel's own partition code on
+ * the host): for HOST arrays context_lens[batch] and `shared_pages` leading pages skipped by the
+ * cascade, writes up to max_pieces records of 12 int32
+ *     {item, sequence, kv_head, tile_begin, tile_end, tiles_total, first, last, range_first,
+ *      range_last, range, units_per_range}
+ * in work-item order and returns the number of pieces (which may exceed max_pieces), or a
+ * negative error. Field 0 is the work item (= range * num_kv_heads + kv_head; items below
+ * num_splits are the CTAs' first items, later ones are taken dynamically), field 10 its range,
+ * field 11 the units per range with bit 30 set in the dynamic regime. Tiles are 64 tokens. Uses
+ * the same B200ATTN_DECODE_MIN_TILES / _ROW_COST / _SNAP / _WAVES / _DYN_MIN tunables.
+ */
+int b200attn_decode_partition_host(const int32_t* context_lens, int32_t batch,
+                                   int32_t num_kv_heads, int32_t num_splits, int32_t shared_pages,
+                                   int32_t block_size, int32_t* pieces, int32_t max_pieces);
+
+/* Bytes of fp32 workspace the decode entry points need: two partial-piece slots per work item that
+ * can hold a cut row when num_splits > 1 (at most num_splits + num_q_heads items), plus batch * num_q_heads * prefix_chunks shared-prefix partials for the cascade
+ * (prefix_chunks = 0 otherwise). 0 when num_splits <= 1 and prefix_chunks == 0. */
 size_t b200attn_decode_workspace_bytes(int32_t batch, int32_t num_q_heads, int32_t head_dim,
-                                       int32_t num_splits);
+                                       int32_t num_splits, int32_t prefix_chunks);
 
 /*
  * Paged decode attention (one query token per sequence):
@@ -103,6 +135,8 @@ size_t b200attn_decode_workspace_bytes(int32_t batch, int32_t num_q_heads, int32
  * read no table entry; table entries at or beyond ceil(ctx_b / block_size) are never read.
  *   q   [batch, num_q_heads, head_dim] contiguous;  out same shape/dtype
  *   workspace: >= b200attn_decode_workspace_bytes(...) bytes when num_splits > 1, else may be NULL
+ *   num_splits > 1 needs the arrival counters of b200attn_set_split_counters (else
+ *   B200ATTN_E_WORKSPACE). batch may exceed 1024: the call then issues one launch per 1024 rows.
  */
 int b200attn_decode(const void* q, const void* k_cache, const void* v_cache,
                     const int32_t* block_tables, int64_t table_row_stride, int32_t table_width,
@@ -119,7 +153,10 @@ int b200attn_decode(const void* q, const void* k_cache, const void* v_cache,
  * cache slot of token context_lens[b] - 1 of row b, i.e.
  *     block_tables[b][(ctx_b-1)/block_size] * block_size + (ctx_b-1) % block_size.
  * The CTA that attends that token writes it first (generic stores, fence.proxy.async, then its
- * own TMA reads), so no other work item ever reads a slot being written.
+ * own TMA reads), so no other work item ever reads a slot being written. A caller that breaks the
+ * precondition (a slot that belongs to another token of the batch) gets the row stored, but rows
+ * that attend that slot may read it before or after the store: use b200attn_store_kvcache followed
+ * by b200attn_decode when slot_mapping is not the decode step's own.
  */
 int b200attn_store_decode(const void* q, const void* key, int64_t key_row_stride, const void* value,
                           int64_t value_row_stride, const int32_t* slot_mapping, void* k_cache,
@@ -148,8 +185,8 @@ int b200attn_store_decode(const void* q, const void* key, int64_t key_row_stride
  *   b200attn_store_decode_cascade  = b200attn_store_decode + (plan, prefix_chunks). The split
  *       counts and launch shapes depend on host-visible sizes only; P is read on the device, so the
  *       call is graph-capturable and P == 0 degrades to the plain path. The workspace must hold
- *       b200attn_decode_workspace_bytes(batch, num_q_heads, head_dim, num_splits + prefix_chunks).
- *       plan == NULL and prefix_chunks == 0 is exactly b200attn_store_decode.
+ *       b200attn_decode_workspace_bytes(batch, num_q_heads, head_dim, num_splits, prefix_chunks).
+ *       plan == NULL and prefix_chunks == 0 is exactly b200attn_store_decode. batch <= 1024.
  */
 int b200attn_cascade_pick_chunks(int32_t batch, int32_t num_q_heads, int32_t num_kv_heads,
                                  int32_t table_width, int32_t block_size, int32_t sm_count);
@@ -261,15 +298,18 @@ int b200attn_prepare_decode(const int32_t* packed, int32_t batch, int32_t table_
                             int64_t table_row_stride, int32_t capacity, void* stream);
 
 /*
- * In-launch split merge. With num_splits > 1 the decode entry points normally launch a second
- * (merge) kernel. If the caller registers a ZEROED device buffer of `count` int32 for the current
- * device, the split CTA of a (sequence, KV head) that finishes last merges the partials itself
- * (fence + atomic arrival counter, reset to zero before the launch ends) whenever
- * batch * num_kv_heads <= count: one launch instead of two, same arithmetic, bit-identical output.
- * The buffer stays owned by the caller and must outlive every later decode call on that device
- * (the library keeps the pointer: the one exception, besides cached TMA descriptors, to "keeps no
- * pointers"); decode calls that use it must be stream-ordered with respect to each other.
- * counters == NULL unregisters. B200ATTN_FUSED_MERGE=0 ignores the registration (A/B runs).
+ * Counters of the decode kernel. A (sequence, KV head) row whose tiles were cut across work items
+ * is finished by the piece that arrives last (acq_rel atomic arrival counter, reset to zero before
+ * the launch ends); the dynamic work distribution uses two more counters (next item, CTAs done;
+ * the CTA that finishes last resets them). The caller registers a ZEROED device buffer of `count`
+ * int32 for the current device once; every decode call with num_splits > 1 needs
+ * min(batch, 1024) * num_kv_heads + 2 <= count (the last two entries of the buffer are the
+ * scheduler's). The buffer stays owned by the caller and must outlive every later decode call on
+ * that device (the library keeps the pointer: the one exception, besides cached TMA descriptors, to
+ * "keeps no pointers"). Decode calls on one device must be stream-ordered with respect to each
+ * other (one engine per device, as nanovllm runs): two decode launches in flight at once on
+ * different streams would share the counters. A launch that is aborted mid-flight may leave
+ * counters non-zero: re-zero and re-register the buffer. counters == NULL unregisters.
  */
 int b200attn_set_split_counters(void* counters, int64_t count);
 

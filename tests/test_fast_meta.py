@@ -7,7 +7,8 @@ import numpy as np
 import pytest
 import torch
 
-from byox_vllm_b200 import fast_meta as fm, metadata as md
+from byox_vllm_b200 import fast_meta as fm
+from tools import metadata_ref as md
 
 
 def test_pack_decode_record_layout():

@@ -15,7 +15,7 @@ pytestmark = pytest.mark.gpu
 
 @pytest.mark.parametrize("Hq,Hkv", [(16, 8), (8, 1)])
 def test_prefill_then_decode_steps(cuda_dev, Hq, Hkv):
-    from byox_vllm_b200 import metadata as md
+    from tools import metadata_ref as md
     from byox_vllm_b200.attention import Attention
     from byox_vllm_b200.context import reset_context, set_context
 

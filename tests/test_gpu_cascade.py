@@ -197,3 +197,36 @@ def test_cascade_module_under_graph_replay(cuda_dev):
     assert int(other.meta["block_tables"].max()) < limit
     replay(other)
     replay(shared)
+
+
+def test_cascade_at_config4_size(cuda_dev):
+    """BASELINE config 4's per-rank shape: Qwen3-32B at TP=8 -> heads 8/1, batch 256, ctx 8192
+    with a 7680-token (30-page) shared prefix + 512 own tokens. The size heuristic must arm the
+    cascade by itself; the plan must find the 30 pages; the result must equal plain paged decode
+    on every row and the oracle on sampled rows; the fused store must leave the cache bit-exact."""
+    from byox_vllm_b200.attention import cascade_chunks, cascade_plan, paged_decode
+
+    B, Hq, Hkv, ctx, P = 256, 8, 1, 8192, 30
+    c = synth.shared_prefix_decode_case([ctx] * B, P, Hq, Hkv, seed=57, device=cuda_dev)
+    m = {k: (v.to(cuda_dev) if isinstance(v, torch.Tensor) else v) for k, v in c.meta.items()}
+    W = m["block_tables"].size(1)
+    chunks = cascade_chunks(B, Hq, Hkv, W, 256)
+    assert chunks > 0, "the size heuristic must arm the cascade for config 4"
+    plan = cascade_plan(m["context_lens"], m["block_tables"], 256)
+    assert plan.cpu()[0].item() == P
+    kc, vc = c.k_cache.clone(), c.v_cache.clone()
+    got = paged_decode(c.q, kc, vc, m["context_lens"], m["block_tables"], c.scale, key=c.k,
+                       value=c.v, slot_mapping=m["slot_mapping"], plan=plan, prefix_chunks=chunks)
+    kc2, vc2 = c.k_cache.clone(), c.v_cache.clone()
+    plain = paged_decode(c.q, kc2, vc2, m["context_lens"], m["block_tables"], c.scale, key=c.k,
+                         value=c.v, slot_mapping=m["slot_mapping"])
+    torch.cuda.synchronize()
+    assert torch.equal(kc.view(torch.int16), kc2.view(torch.int16))
+    assert torch.equal(vc.view(torch.int16), vc2.view(torch.int16))
+    assert_close(got, plain.float(), "config 4 cascade vs plain decode")
+    k_cpu, v_cpu = kc.cpu(), vc.cpu()
+    for b in (0, 101, B - 1):
+        want = orc.paged_decode_ref(c.q[b:b + 1].cpu(), k_cpu, v_cpu,
+                                    c.meta["context_lens"][b:b + 1].cpu(),
+                                    c.meta["block_tables"][b:b + 1].cpu(), c.scale)
+        assert_close(got[b:b + 1], want, f"config 4 row {b} vs oracle")

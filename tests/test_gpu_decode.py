@@ -210,14 +210,14 @@ def test_decode_properties_at_baseline_sizes(cuda_dev, shape):
         assert_close(o[b:b + 1], want, f"row {b} vs oracle")
 
 
-@pytest.mark.gpu
 @pytest.mark.parametrize("batch,ctx,Hq,Hkv,splits", [
     (1, 4096, 32, 8, 8), (3, [5000, 1, 300], 16, 8, 5), (2, [700, 64], 8, 1, 64),
-    (7, 1000, 4, 1, 3), (16, 2048, 16, 4, 2)])
-def test_in_launch_merge_equals_merge_kernel(cuda_dev, batch, ctx, Hq, Hkv, splits):
-    """num_splits > 1 with registered arrival counters (the last split CTA merges in the same
-    launch) must give the merge kernel's output bit for bit, launch once instead of twice, leave
-    the counters at zero, and handle empty splits / padding rows (ctx 0) that arrive last."""
+    (7, 1000, 4, 1, 3), (16, 2048, 16, 4, 2), (1, 20000, 8, 1, 296), (40, 333, 16, 8, 296)])
+def test_in_launch_merge_of_cut_rows(cuda_dev, batch, ctx, Hq, Hkv, splits):
+    """Rows cut across CTA ranges are finished by the piece that arrives last: ONE launch, the
+    arrival counters come back to zero every time, the result does not depend on which piece
+    arrived last (bit-identical across repeats) and agrees with the single-CTA walk (num_splits
+    = 1, no cut rows at all) and the oracle. Padding rows (ctx 0) stay zero."""
     from byox_vllm_b200 import _lib, attention as A
 
     lib = _lib.load()
@@ -226,27 +226,109 @@ def test_in_launch_merge_equals_merge_kernel(cuda_dev, batch, ctx, Hq, Hkv, spli
     m = d["meta"]
     lens = m["context_lens"].clone()
     if batch >= 3:
-        lens[1] = 0  # padding row of a captured batch: every split of it is empty
+        lens[1] = 0  # padding row of a captured batch
     args = (d["q"], d["k_cache"], d["v_cache"], lens, m["block_tables"], c.scale)
     A.ensure_split_counters(cuda_dev)
     counters = A._SPLIT_COUNTERS[cuda_dev.index or 0]
-    try:
-        assert lib.b200attn_set_split_counters(None, 0) == 0
-        n0 = lib.b200attn_launch_count()
-        want = A.paged_decode(*args, num_splits=splits)
-        torch.cuda.synchronize()
-        assert lib.b200attn_launch_count() - n0 == 2  # split + merge kernels
-    finally:
-        assert lib.b200attn_set_split_counters(counters.data_ptr(), counters.numel()) == 0
-    for _ in range(3):  # repeated launches: the counters must come back to zero every time
+    one = A.paged_decode(*args, num_splits=1)
+    torch.cuda.synchronize()
+    first = None
+    for _ in range(3):
         n0 = lib.b200attn_launch_count()
         got = A.paged_decode(*args, num_splits=splits)
         torch.cuda.synchronize()
         assert lib.b200attn_launch_count() - n0 == 1
-        assert torch.equal(got, want)
         assert int(counters.abs().sum()) == 0
+        first = got if first is None else first
+        assert torch.equal(got, first)
+    assert_close(got, one, "cut rows vs single-CTA walk")
     if batch >= 3:
         assert torch.count_nonzero(got[1]) == 0
     ref = orc.paged_decode_ref(c.q, c.k_cache, c.v_cache, lens.cpu(), c.meta["block_tables"],
                                c.scale)
     assert_close(got, ref, "in-launch merge vs oracle")
+
+
+def test_cut_rows_need_registered_counters(cuda_dev):
+    """num_splits > 1 without the arrival counters is an error, not a silent second path."""
+    from byox_vllm_b200 import _lib, attention as A
+
+    lib = _lib.load()
+    c = synth.decode_case(2, [700, 64], 8, 1, seed=62)
+    d = to_dev(c, cuda_dev)
+    m = d["meta"]
+    A.ensure_split_counters(cuda_dev)
+    counters = A._SPLIT_COUNTERS[cuda_dev.index or 0]
+    try:
+        assert lib.b200attn_set_split_counters(None, 0) == 0
+        with pytest.raises(_lib.B200AttnError) as e:
+            A.paged_decode(d["q"], d["k_cache"], d["v_cache"], m["context_lens"],
+                           m["block_tables"], c.scale, num_splits=4)
+        assert e.value.code == _lib.E_WORKSPACE and "counters" in e.value.msg
+        got = A.paged_decode(d["q"], d["k_cache"], d["v_cache"], m["context_lens"],
+                             m["block_tables"], c.scale, num_splits=1)  # needs none
+        torch.cuda.synchronize()
+    finally:
+        assert lib.b200attn_set_split_counters(counters.data_ptr(), counters.numel()) == 0
+    want = orc.paged_decode_ref(c.q, c.k_cache, c.v_cache, c.meta["context_lens"],
+                                c.meta["block_tables"], c.scale)
+    assert_close(got, want, "single CTA without counters")
+
+
+@pytest.mark.parametrize("shape", [(1, 131072, 32, 8), (512, 1024, 32, 8), (1, 131072, 4, 1),
+                                   (1500, 300, 8, 2)],
+                         ids=["b1_ctx128k_32_8", "b512_ctx1k_32_8", "b1_ctx128k_4_1_tp8",
+                              "b1500_eager_chunks"])
+def test_decode_config5_corners(cuda_dev, shape):
+    """BASELINE config 5's corners (B 1 x 131072: one row per KV head cut across up to 296 CTAs;
+    B 512 x 1024: many whole rows per CTA) and a batch above the 1024-row launch limit (eager
+    decode of > 512 sequences, model_runner.py:230): sampled rows vs the oracle, constant V,
+    agreement between the automatic partition and other CTA counts."""
+    from byox_vllm_b200.attention import paged_decode
+
+    B, ctx, Hq, Hkv = shape
+    dev = cuda_dev
+    c = synth.decode_case(B, ctx, Hq, Hkv, seed=44, device=dev)
+    m = {k: (v.to(dev) if isinstance(v, torch.Tensor) else v) for k, v in c.meta.items()}
+    args = (c.q, c.k_cache, c.v_cache, m["context_lens"], m["block_tables"], c.scale)
+    o = paged_decode(*args)
+    o3 = paged_decode(*args, num_splits=3 if B > 1 else 37)
+    assert_close(o, o3, "auto partition vs another CTA count")
+    vconst = torch.full_like(c.v_cache, -1.25)
+    oc = paged_decode(c.q, c.k_cache, vconst, m["context_lens"], m["block_tables"], c.scale)
+    assert (oc.float() + 1.25).abs().max().item() <= 1e-2
+    del vconst
+    k_cpu, v_cpu = c.k_cache.cpu(), c.v_cache.cpu()
+    for b in sorted({0, B // 2, B - 1}):
+        want = orc.paged_decode_ref(c.q[b:b + 1].cpu(), k_cpu, v_cpu,
+                                    c.meta["context_lens"][b:b + 1],
+                                    c.meta["block_tables"][b:b + 1], c.scale)
+        assert_close(o[b:b + 1], want, f"row {b} vs oracle")
+
+
+def test_fused_store_with_foreign_slot_mapping(cuda_dev):
+    """include/b200attn.h documents the fused store's precondition (slot_mapping[b] = slot of token
+    ctx_b - 1). A caller that breaks it still gets every row stored bit-exactly at the slot it
+    named; when that slot is attended by no row of the batch (here: free blocks) the attention
+    output is exactly the decode over the cache without this step's rows."""
+    from byox_vllm_b200.attention import paged_decode
+
+    c = synth.decode_case(4, [300, 256, 700, 65], 16, 8, seed=63)
+    d = to_dev(c, cuda_dev)
+    m = d["meta"]
+    nb = d["k_cache"].shape[0]
+    used = {b for s in c.seqs for b in s.block_table}
+    free = [b for b in range(nb) if b not in used]
+    assert len(free) >= 2
+    foreign = torch.tensor([free[0] * 256 + 3, free[0] * 256 + 4, -1, free[1] * 256 + 255],
+                           dtype=torch.int32, device=cuda_dev)
+    kc0, vc0 = d["k_cache"].clone(), d["v_cache"].clone()
+    plain = paged_decode(d["q"], kc0, vc0, m["context_lens"], m["block_tables"], c.scale)
+    got = paged_decode(d["q"], d["k_cache"], d["v_cache"], m["context_lens"], m["block_tables"],
+                       c.scale, key=d["k"], value=d["v"], slot_mapping=foreign)
+    torch.cuda.synchronize()
+    assert torch.equal(got.view(torch.int16), plain.view(torch.int16))
+    kc_ref, vc_ref = c.k_cache.clone(), c.v_cache.clone()
+    orc.store_kvcache_ref(c.k, c.v, kc_ref, vc_ref, foreign.cpu())
+    assert torch.equal(d["k_cache"].cpu().view(torch.int16), kc_ref.view(torch.int16))
+    assert torch.equal(d["v_cache"].cpu().view(torch.int16), vc_ref.view(torch.int16))

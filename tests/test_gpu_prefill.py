@@ -16,7 +16,7 @@ def _forward(dev, c, Hq, Hkv):
     """Attention.forward on the device for a prefill case; returns (out, device dict)."""
     from byox_vllm_b200.attention import Attention
     from byox_vllm_b200.context import reset_context, set_context
-    from byox_vllm_b200.metadata import context_kwargs
+    from tools.metadata_ref import context_kwargs
 
     d = to_dev(c, dev)
     attn = Attention(Hq, 128, c.scale, Hkv)
@@ -66,7 +66,7 @@ def test_warmup_path_without_cache(cuda_dev):
     """_warmup_model (model_runner.py:102-113): empty caches, no slots, dense attention."""
     from byox_vllm_b200.attention import Attention
     from byox_vllm_b200.context import reset_context, set_context
-    from byox_vllm_b200.metadata import SeqState, context_kwargs, prepare_prefill
+    from tools.metadata_ref import SeqState, context_kwargs, prepare_prefill
 
     dev = cuda_dev
     meta = prepare_prefill([SeqState(300), SeqState(300)], 256)
@@ -93,7 +93,7 @@ def test_prefill_last_row_equals_decode(cuda_dev):
     ends = c.meta["cu_seqlens_q"][1:].long() - 1
     qd = d["q"][ends.to(cuda_dev)]
     lens = torch.tensor([700, 129], dtype=torch.int32, device=cuda_dev)
-    from byox_vllm_b200.metadata import prepare_block_tables
+    from tools.metadata_ref import prepare_block_tables
 
     bt = prepare_block_tables(c.seqs).to(cuda_dev)
     od = paged_decode(qd, d["k_cache"], d["v_cache"], lens, bt, c.scale)

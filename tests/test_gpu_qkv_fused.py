@@ -190,7 +190,8 @@ def test_qkv_attention_dispatch(cuda_dev):
     """qkv_attention under a Context: dense prefill, paged-prefix prefill, decode — against
     qwen3.py:75-84 restated on the CPU; then the decode step that follows the prefill reads what
     the prefill stored."""
-    from byox_vllm_b200 import metadata as md, qkv_attention as fused
+    from byox_vllm_b200 import qkv_attention as fused
+    from tools import metadata_ref as md
     from byox_vllm_b200.attention import Attention
     from byox_vllm_b200.context import reset_context, set_context
 
@@ -246,7 +247,7 @@ def test_qkv_decode_graph_replay(cuda_dev):
 
     Hq, Hkv, B = 16, 8, 8
     dev = cuda_dev
-    from byox_vllm_b200 import metadata as md
+    from tools import metadata_ref as md
 
     first = _fused_decode_case(6, [300, 17, 1000, 256, 257, 511], Hq, Hkv, 41, dev)
     c0 = first[0]

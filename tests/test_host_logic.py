@@ -16,34 +16,38 @@ def lib(built_lib):
 
 
 def test_pick_splits_is_host_only_and_sane(lib):
+    """num_splits = persistent CTAs of the decode kernel: two per SM, fewer when even full tables
+    could not give every CTA its minimum range (8 units by default, 1 unit per row of overhead).
+    How the work is cut is decided on the device (tests/test_decode_partition.py)."""
     sm = 148
-    # big batches never split; tiny batches with long tables split; never more splits than
-    # 256-token pieces of the longest possible context
-    assert lib.b200attn_decode_pick_splits(512, 8, 4, 256, sm) == 1
-    assert lib.b200attn_decode_pick_splits(128, 8, 16, 256, sm) == 1
-    s = lib.b200attn_decode_pick_splits(1, 8, 512, 256, sm)
-    assert 16 <= s <= 128
-    assert lib.b200attn_decode_pick_splits(1, 8, 1, 256, sm) == 1
+    assert lib.b200attn_decode_pick_splits(512, 8, 4, 256, sm) == 2 * sm
+    assert lib.b200attn_decode_pick_splits(128, 8, 16, 256, sm) == 2 * sm
+    assert lib.b200attn_decode_pick_splits(256, 1, 16, 256, sm) == 2 * sm  # TP=8 rank of config 2
+    assert lib.b200attn_decode_pick_splits(1, 8, 512, 256, sm) == 2 * sm   # one long sequence
+    # one page per row, one row per KV head: 8 rows x (4 tiles + 1) = 40 units -> 5 CTAs
+    assert lib.b200attn_decode_pick_splits(1, 8, 1, 256, sm) == 5   # < Hkv: CTAs walk heads
+    assert lib.b200attn_decode_pick_splits(1, 8, 4, 256, sm) == 16  # multiples of Hkv beyond
+    assert lib.b200attn_decode_pick_splits(1, 1, 1, 256, sm) == 1
     for b in (1, 2, 4, 8, 16, 64):
         for w in (1, 4, 16, 128):
             s = lib.b200attn_decode_pick_splits(b, 1, w, 256, sm)
-            assert 1 <= s <= max(1, w)
+            assert 1 <= s <= 2 * sm
+            assert s <= max(1, -(-b * (4 * w + 1) // 8))
     assert lib.b200attn_decode_pick_splits(4, 8, 16, 256, 0) >= 1  # unknown SM count -> 148
-    # calibration points of tools/sweep_splits.py (profiles/r01_sweep_splits.log): about one CTA
-    # per SM, no split once (sequence, KV head) items reach ~0.7 x SMs, pieces >= 512 tokens
-    assert lib.b200attn_decode_pick_splits(16, 8, 16, 256, sm) == 1
-    assert lib.b200attn_decode_pick_splits(128, 1, 16, 256, sm) == 1
-    assert lib.b200attn_decode_pick_splits(8, 8, 64, 256, sm) == 2
-    assert lib.b200attn_decode_pick_splits(4, 8, 16, 256, sm) == 5
-    assert lib.b200attn_decode_pick_splits(1, 8, 16, 256, sm) == 8
-    assert lib.b200attn_decode_pick_splits(1, 8, 512, 256, sm) in (18, 19)
+    assert lib.b200attn_decode_pick_splits(0, 8, 16, 256, sm) == 1
 
 
 def test_workspace_bytes(lib):
-    assert lib.b200attn_decode_workspace_bytes(4, 16, 128, 1) == 0
-    n = lib.b200attn_decode_workspace_bytes(4, 16, 128, 3)
-    assert n == 4 * 16 * 3 * (128 + 1) * 4
-    assert lib.b200attn_decode_workspace_bytes(4, 16, 64, 3) == 0  # unsupported head_dim
+    slot = 8 * (128 + 1) * 4  # one partial piece: [8 heads][128] fp32 O + [8] lse
+    # two slots per work item that can hold a cut row (static regime: <= num_splits + num_q_heads
+    # items); not per row of the batch
+    assert lib.b200attn_decode_workspace_bytes(4, 16, 128, 1, 0) == 0
+    assert lib.b200attn_decode_workspace_bytes(4, 16, 128, 3, 0) == (3 + 16) * 2 * slot
+    assert lib.b200attn_decode_workspace_bytes(400, 16, 128, 296, 0) == (296 + 16) * 2 * slot
+    pre = 4 * 16 * 5 * (128 + 1) * 4
+    assert lib.b200attn_decode_workspace_bytes(4, 16, 128, 1, 5) == pre
+    assert lib.b200attn_decode_workspace_bytes(4, 16, 128, 3, 5) == (3 + 16) * 2 * slot + pre
+    assert lib.b200attn_decode_workspace_bytes(4, 16, 64, 3, 0) == 0  # unsupported head_dim
 
 
 def test_argument_errors_have_codes_and_messages(lib):
@@ -115,8 +119,11 @@ def test_install_under_a_nanovllm_package(tmp_path, monkeypatch, built_lib):
     (pkg / "utils").mkdir(parents=True)
     (pkg / "layers").mkdir()
     (pkg / "models").mkdir()
-    for d in (pkg, pkg / "utils", pkg / "layers", pkg / "models"):
+    for d in (pkg / "utils", pkg / "layers", pkg / "models"):
         (d / "__init__.py").write_text("")
+    # like the real package: importing ANY nanovllm submodule runs __init__ -> llm -> ... ->
+    # models.qwen3 -> `from nanovllm.layers.attention import Attention`
+    (pkg / "__init__.py").write_text("from nanovllm.models import qwen3  # noqa: F401\n")
     (pkg / "utils" / "context.py").write_text(textwrap.dedent("""
         from dataclasses import dataclass
         @dataclass
@@ -146,6 +153,47 @@ def test_install_under_a_nanovllm_package(tmp_path, monkeypatch, built_lib):
     from byox_vllm_b200.context import get_context
 
     assert ours.get_context is get_context
+
+
+_BLOCKED_INSTALL = r"""
+import sys, importlib.abc
+class Block(importlib.abc.MetaPathFinder):
+    def find_spec(self, name, path=None, target=None):
+        if name.split(".")[0] in ("flash_attn", "flash_attn_2_cuda", "triton"):
+            raise ImportError(name + " is blocked for this test")
+        return None
+sys.meta_path.insert(0, Block())
+sys.path.insert(0, {root!r}); sys.path.insert(0, {ref!r})
+from byox_vllm_b200 import install
+install.install(fuse_qkv=True, fast_meta=True, fast_rpc=True)
+import nanovllm.models.qwen3 as qwen3
+import nanovllm.engine.model_runner as mr
+import nanovllm.utils.context as ctx
+from byox_vllm_b200 import attention as ours, fast_meta, qkv_attention
+assert qwen3.Attention is ours.Attention and ours.get_context is ctx.get_context
+assert qwen3.Qwen3Attention.forward is qkv_attention.qwen3_attention_forward
+assert mr.ModelRunner._prepare_decode is fast_meta.prepare_decode
+bad = sorted(m for m in sys.modules if m.split(".")[0] in ("flash_attn", "triton"))
+assert not bad, bad
+print("INSTALL-OK")
+"""
+
+
+def test_install_never_imports_flash_attn_or_triton(built_lib):
+    """The UNMODIFIED reference (baseline/_ref) with install() in a fresh interpreter where
+    flash_attn and triton cannot be imported at all: the engine modules import, every rebinding is
+    in place, and neither wheel is in sys.modules (install() registers our module under
+    nanovllm.layers.attention BEFORE the first nanovllm import)."""
+    import subprocess
+
+    from conftest import ROOT
+
+    ref = ROOT / "baseline" / "_ref"
+    if not (ref / "nanovllm" / "layers" / "attention.py").exists():
+        pytest.skip("baseline/_ref is not installed (needs /root/reference: __graft_entry__.build)")
+    r = subprocess.run([sys.executable, "-c", _BLOCKED_INSTALL.format(root=str(ROOT), ref=str(ref))],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "INSTALL-OK" in r.stdout, r.stdout[-1500:] + r.stderr[-1500:]
 
 
 def test_cascade_chunks_heuristic_is_host_only(lib):

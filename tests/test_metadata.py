@@ -2,7 +2,7 @@
 (reference tests/test_prepare_funcs.py:17-206, block_size 16) and scale to block_size 256."""
 import torch
 
-from byox_vllm_b200 import metadata as md
+from tools import metadata_ref as md
 from byox_vllm_b200.context import get_context, reset_context, set_context
 
 

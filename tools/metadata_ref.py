@@ -5,7 +5,10 @@ Restates reference nanovllm/engine/model_runner.py:152-158 (_prepare_block_table
 on plain (length, num_cached_tokens, block_table) triples instead of `Sequence` objects
 (engine/sequence.py:55-69 for num_blocks / last_block_num_tokens / num_cached_blocks). Used by
 the standalone harnesses (tests, bench, smoke) to drive the op exactly as the engine would; under
-a real nanovllm the engine's own builders run and this module is not involved.
+a real nanovllm the engine's own builders run and this module is not involved. It is HARNESS code
+(it lives in tools/, not in the product package): the device-side builders of
+byox_vllm_b200/fast_meta.py are checked against it on the CPU and against the reference's own
+ModelRunner builders on the GPU box (tests/test_engine_parity.py).
 
 All tensors are built on the CPU (int32, like the reference) and optionally pinned; the caller
 moves them with .cuda(non_blocking=True) as the reference does.

@@ -320,7 +320,7 @@ def bench_prefill(out, quick):
 
     from flash_attn import flash_attn_varlen_func
 
-    from byox_vllm_b200 import metadata as md
+    from tools import metadata_ref as md
     from byox_vllm_b200.attention import prefill_varlen
 
     shapes = PREFILL_SHAPES[:3] if quick else PREFILL_SHAPES

@@ -14,7 +14,7 @@ from dataclasses import dataclass
 
 import torch
 
-from byox_vllm_b200 import metadata as md
+from tools import metadata_ref as md
 
 
 @dataclass
