@@ -166,6 +166,7 @@ struct SplitCounters {
     int64_t count = 0;
 };
 static SplitCounters g_split_counters[64];
+static unsigned long long* g_decode_trace = nullptr;  // b200attn_debug_decode_trace
 static std::mutex g_split_counters_mu;
 
 static int32_t* split_counters_for(int64_t need, int32_t** sched) {
@@ -272,7 +273,8 @@ static int store_decode_impl(const void* q, int64_t q_row_stride, const void* ke
     p.block_size = block_size;
     p.num_ctas = num_splits;
     p.tun = b200::decode_tunables();
-    if (num_splits == 1) p.tun.waves = 1;  // no counters: static regime (one CTA walks every item)
+    if (num_splits == 1) p.tun.dyn_ok = 0;  // no counters: static regime (one CTA walks every item)
+    p.trace = g_decode_trace;
     p.scale_log2 = scale * 1.4426950408889634f;
     if (with_store && fused_store) {
         p.new_key = key;
@@ -726,6 +728,10 @@ int b200attn_prepare_decode(const int32_t* packed, int32_t batch, int32_t table_
     p.block_size = block_size;
     cudaError_t e = b200::launch_prepare_decode(p, static_cast<cudaStream_t>(stream));
     return e == cudaSuccess ? 0 : cuda_fail(e, "prepare_decode launch");
+}
+
+void b200attn_debug_decode_trace(void* stamps) {
+    g_decode_trace = static_cast<unsigned long long*>(stamps);
 }
 
 int b200attn_set_split_counters(void* counters, int64_t count) {

@@ -117,6 +117,8 @@ struct DecodeParams {
     // dynamic work distribution (num_ctas > 1): sched[0] = next work item beyond the first wave,
     // sched[1] = CTAs finished; both zero between launches (the last CTA resets them).
     int32_t* sched;
+    // debug: 16 uint64 stamps per CTA (b200attn_debug_decode_trace); nullptr = the product kernel
+    unsigned long long* trace;
 };
 cudaError_t launch_decode(const DecodeParams& p, const CUtensorMap& k_map, const CUtensorMap& v_map,
                           cudaStream_t stream);
@@ -133,8 +135,9 @@ int decode_partition_host(const int32_t* context_lens, int32_t batch, int32_t nu
 int decode_min_units();
 int decode_row_cost();
 int decode_snap();
-int decode_waves();
-int decode_dyn_min();
+int decode_dyn_ok();
+int decode_dyn_pct();
+int decode_static_pct();
 StreamTunables decode_tunables();
 
 // ---- prefill_attn.cu -------------------------------------------------------------------------

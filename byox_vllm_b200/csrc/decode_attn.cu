@@ -47,7 +47,7 @@ constexpr int kDecodeThreads = (kConsumerWarps + 1) * 32;
 constexpr int kSubTileBytes = kTile * 128;  // [64 tok][64 dims] bf16 = 8 KiB, 128-byte rows
 constexpr int kStageBytes = 4 * kSubTileBytes;  // K lo/hi + V lo/hi = 32 KiB
 constexpr int kScratchFloats = 2 * 8 * kHeadDim;  // two partial O^T sets of [8 heads][128 dims]
-constexpr int kItemQueue = 4;  // work-item ids in flight from the producer warp to the consumers
+constexpr int kPieceQueue = 4;  // piece descriptors in flight from the producer warp to the consumers
 
 // Programmatic dependent launch: block until the primary grid (the cascade prefix pass) has
 // completed and its global writes are visible. A no-op when launched without the attribute.
@@ -328,14 +328,30 @@ struct DecodeSmem {
     static constexpr int kCum = kScratch + kScratchFloats * 4;       // int32[kDecodeMaxBatch + 1]
     static constexpr int kWarpSums = kCum + (kDecodeMaxBatch + 2) * 4;  // int32[8] sums | int32[8] maxima
     static constexpr int kFlag = kWarpSums + 16 * 4;
-    static constexpr int kQueueBars = kFlag + 16;                    // q_full[kItemQueue] | q_empty[..]
-    static constexpr int kQueue = kQueueBars + 2 * kItemQueue * 8;   // int32[kItemQueue]
-    static constexpr int kBytes = kQueue + kItemQueue * 4;
+    static constexpr int kQueueBars = kFlag + 16;                    // q_full[kPieceQueue] | q_empty[..]
+    static constexpr int kQueue = (kQueueBars + 2 * kPieceQueue * 8 + 15) & ~15;  // PieceDesc[kPieceQueue]
+    static constexpr int kBytes = kQueue + kPieceQueue * 32;
     static_assert(kBars % 8 == 0 && kQueueBars % 8 == 0, "mbarriers need 8-byte alignment");
-    static_assert(kScratch % 16 == 0, "float4 reads of the scratch");
+    static_assert(kScratch % 16 == 0 && kQueue % 16 == 0, "float4 / int4 shared-memory accesses");
+    static_assert(sizeof(PieceDesc) == 32, "queue slots are two int4");
 };
 
-template <int kStages>
+// Debug trace (b200attn_debug_decode_trace): 16 uint64 per CTA.
+//   0 globaltimer at entry   1 clock at entry        2 clock after the scan
+//   3 producer: first piece known                    4 producer: first TMA issued
+//   5 consumer: first tile landed                    6 consumer: first piece's tiles done
+//   7 consumer: first piece's epilogue done          8 producer: all tiles issued (clock)
+//   9 consumer: exit (clock)  10 pieces  11 tiles    12 SM id   13 clocks waiting for tiles
+//  14 globaltimer at consumer exit                   15 clocks in epilogues
+enum { kTrEntryNs = 0, kTrEntry, kTrScan, kTrPiece0, kTrTma0, kTrTile0, kTrTilesDone0, kTrEpi0,
+       kTrProdExit, kTrConsExit, kTrPieces, kTrTiles, kTrSm, kTrWait, kTrExitNs, kTrEpi };
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+template <int kStages, bool kTrace>
 __global__ void __launch_bounds__(kDecodeThreads, 2)
 decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
                      const __grid_constant__ CUtensorMap v_map, const DecodeParams p) {
@@ -349,14 +365,33 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
     int32_t* warp_sums = reinterpret_cast<int32_t*>(smem + L::kWarpSums);
     int* last_flag = reinterpret_cast<int*>(smem + L::kFlag);
     uint64_t* q_full = reinterpret_cast<uint64_t*>(smem + L::kQueueBars);
-    uint64_t* q_empty = q_full + kItemQueue;
-    volatile int32_t* item_q = reinterpret_cast<volatile int32_t*>(smem + L::kQueue);
+    uint64_t* q_empty = q_full + kPieceQueue;
+    int4* piece_q = reinterpret_cast<int4*>(smem + L::kQueue);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     const int G = p.group;
     const int Hq = p.num_q_heads;
     const int B = p.batch;
+    unsigned long long* trace = kTrace ? p.trace + static_cast<size_t>(blockIdx.x) * 16 : nullptr;
+    if (kTrace && threadIdx.x == 0) {
+        trace[kTrEntryNs] = global_timer_ns();
+        trace[kTrEntry] = clock64();
+        unsigned smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        trace[kTrSm] = smid;
+    }
+
+    // The block tables are read right after the scan (first piece's page window): start them on
+    // their way into L2 now, one 128-byte line per thread, spread over the CTAs.
+    {
+        const int64_t lines =
+            (static_cast<int64_t>(B) * p.table_row_stride * 4 + 127) / 128;
+        const int64_t mine = static_cast<int64_t>(blockIdx.x) * kDecodeThreads + threadIdx.x;
+        if (mine < lines && mine < 8192)
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(
+                reinterpret_cast<const uint8_t*>(p.block_tables) + mine * 128));
+    }
 
     if (threadIdx.x == 0) {
 #pragma unroll
@@ -365,7 +400,7 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
             mbar_init(&empty_bar[s], kConsumerWarps);
         }
 #pragma unroll
-        for (int s = 0; s < kItemQueue; ++s) {
+        for (int s = 0; s < kPieceQueue; ++s) {
             mbar_init(&q_full[s], 1);
             mbar_init(&q_empty[s], kConsumerWarps);
         }
@@ -416,17 +451,7 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
         if (threadIdx.x == kDecodeThreads - 1) cum[B] = base;  // all threads before + own
         __syncthreads();
     }
-    int max_row_units = 0;
-#pragma unroll
-    for (int w = 0; w < kConsumerWarps + 1; ++w) max_row_units = max(max_row_units, warp_sums[8 + w]);
-    Stream st;
-    stream_init(st, cum, B, p.num_kv_heads, gridDim.x, p.tun, t_skip, max_row_units);
-    // Work items: every CTA starts with item = its id. Static regime: it goes on with items
-    // id + CTAs, id + 2 CTAs, ... (only when there are fewer CTAs than KV heads). Dynamic regime:
-    // further items come from the atomic counter sched[0]; producer lane 0 takes them and hands
-    // the ids to the consumers through a small shared-memory queue. An id >= total_items ends
-    // the CTA.
-    const bool dynamic = st.dynamic;
+    if (kTrace && threadIdx.x == 0) trace[kTrScan] = clock64();
 
     // Padding rows of a CUDA-graph batch (ctx == 0) carry no units: their output rows are zeroed
     // here, spread over the CTAs. No table entry of such a row is ever read.
@@ -441,49 +466,85 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
         shared_pages > 0 ? prefix_chunks_of(shared_pages, p.block_size, p.prefix_chunks).valid : 0;
 
     if (warp == kConsumerWarps) {
-        // ===================== TMA producer =====================
+        // ===================== TMA producer (and the CTA's scheduler) =====================
         if (lane == 0) {
             tma_prefetch_desc(&k_map);
             tma_prefetch_desc(&v_map);
         }
+        int max_row_units = 0;
+#pragma unroll
+        for (int w = 0; w < kConsumerWarps + 1; ++w)
+            max_row_units = max(max_row_units, warp_sums[8 + w]);
+        Stream st;
+        stream_init(st, cum, B, p.num_kv_heads, gridDim.x, p.tun, t_skip, max_row_units);
+        // Work items: every CTA starts with item = its id. Static regime: it goes on with items
+        // id + CTAs, ... (only when there are fewer CTAs than ranges x KV heads). Dynamic regime:
+        // further items come from the atomic counter sched[0]. The number is requested two tiles
+        // before the current piece has been issued and used one tile later: early enough to hide
+        // the round trip, late enough that no CTA sits on a reserved row while others go idle.
+        // The consumers never see items, only finished piece descriptors (shared-memory queue).
+        const bool dynamic = st.dynamic;
         const int tiles_per_page = p.block_size / kTile;
+        const float rcp_tpp = 1.0f / static_cast<float>(tiles_per_page);
         const uint64_t policy = l2_policy_evict_first();
         const bool with_store = p.new_key != nullptr;
-        // Piece source: the pieces of the current item, then of the next item this CTA takes.
         ItemIter iter;
         int item = blockIdx.x;
-        int n_taken = 0;  // items pushed to the consumers so far (queue sequence number)
         bool item_live = item < st.total_items;
         if (item_live) iter.init(st, item);
+        int pre_item = 0;        // lane 0: the number requested from sched[0]
+        bool pre_valid = false;  // a request is outstanding (warp-uniform)
+        auto request_item = [&]() {
+            if (dynamic && !pre_valid) {
+                if (lane == 0) pre_item = static_cast<int>(gridDim.x) + atomicAdd(p.sched, 1);
+                pre_valid = true;
+            }
+        };
+        int n_pushed = 0;
+        auto push = [&](const PieceDesc& d) {
+            if (lane == 0) {
+                const int qs = n_pushed % kPieceQueue;
+                mbar_wait(&q_empty[qs], ((n_pushed / kPieceQueue) & 1u) ^ 1u);
+                piece_q[2 * qs] = make_int4(d.b, d.kvh, d.t_begin, d.t_end);
+                piece_q[2 * qs + 1] = make_int4(d.tiles_total, d.range, d.g_first, d.g_last);
+                mbar_arrive(&q_full[qs]);
+            }
+            ++n_pushed;
+        };
+        // Next piece of this CTA (all lanes compute it redundantly), pushed to the consumers; the
+        // end of the work is pushed as a descriptor with b = -1.
         auto next_piece = [&](Piece& pc) -> bool {
             for (;;) {
-                if (!item_live) return false;
-                if (iter.next(st, pc)) return true;
-                int nxt_item = item + gridDim.x;  // static regime: a fixed stride, nothing to hand over
-                if (dynamic) {
-                    if (lane == 0) nxt_item = gridDim.x + atomicAdd(p.sched, 1);
-                    nxt_item = __shfl_sync(0xffffffffu, nxt_item, 0);
-                    if (lane == 0) {
-                        const int qs = n_taken % kItemQueue;
-                        mbar_wait(&q_empty[qs], ((n_taken / kItemQueue) & 1u) ^ 1u);
-                        item_q[qs] = nxt_item;
-                        mbar_arrive(&q_full[qs]);
-                    }
-                    ++n_taken;
+                if (!item_live) {
+                    PieceDesc end{};
+                    end.b = -1;
+                    push(end);
+                    return false;
                 }
-                item = nxt_item;
+                if (iter.next(st, pc)) {
+                    push(piece_desc(st, pc));
+                    return true;
+                }
+                if (dynamic) {
+                    request_item();  // normally requested a tile ago: the shuffle waits for it
+                    item = __shfl_sync(0xffffffffu, pre_item, 0);
+                    pre_valid = false;
+                } else {
+                    item += gridDim.x;
+                }
                 item_live = item < st.total_items;
                 if (item_live) iter.init(st, item);
             }
         };
         Piece cur, nxt;
         bool have = next_piece(cur);
+        if (kTrace && lane == 0) trace[kTrPiece0] = clock64();
         // block-table window of a piece: 32 pages from its first page, one entry per lane
         auto load_window = [&](const Piece& pc) {
             const int32_t* table =
                 p.block_tables + static_cast<int64_t>(pc.b) * p.table_row_stride;
-            const int page0 = pc.t_begin / tiles_per_page;
-            const int last_page = (pc.t_end - 1) / tiles_per_page;
+            const int page0 = idiv_rcp(pc.t_begin, tiles_per_page, rcp_tpp);
+            const int last_page = idiv_rcp(pc.t_end - 1, tiles_per_page, rcp_tpp);
             return page0 + lane <= last_page ? ld_nc_s32(table + page0 + lane) : 0;
         };
         int cur_block = 0;
@@ -494,35 +555,42 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
         }
         int it = 0;
         while (have) {
-            // next piece's table window and new K/V row: loads issued now, consumed after this
-            // piece's tiles have been issued
-            const bool have_next = next_piece(nxt);
-            int nxt_block = 0;
-            ScatterPre nxt_sc{};
-            if (have_next) {
-                nxt_block = load_window(nxt);
-                if (with_store && nxt.last) nxt_sc = scatter_prefetch(p, nxt.b, nxt.kvh, lane);
-            }
             if (with_store && cur.last) scatter_finish(p, cur_sc, cur.b, cur.kvh, lane);
             const int32_t* table =
                 p.block_tables + static_cast<int64_t>(cur.b) * p.table_row_stride;
-            const int last_page = (cur.t_end - 1) / tiles_per_page;
-            int page_base = cur.t_begin / tiles_per_page;
+            const int last_page = idiv_rcp(cur.t_end - 1, tiles_per_page, rcp_tpp);
+            int page_base = idiv_rcp(cur.t_begin, tiles_per_page, rcp_tpp);
+            int page = page_base;
+            int in_page = cur.t_begin - page_base * tiles_per_page;
             int my_block = cur_block;
+            bool have_next = false;
+            int nxt_block = 0;
+            ScatterPre nxt_sc{};
+            const int request_t = max(cur.t_begin, cur.t_end - 2);
             for (int t = cur.t_begin; t < cur.t_end; ++t, ++it) {
                 const int stage = it % kStages;
                 const uint32_t phase = (it / kStages) & 1u;
-                const int page = t / tiles_per_page;
+                if (t == request_t && iter.u >= iter.hi) request_item();
+                if (t == cur.t_end - 1) {
+                    // before the last tile goes out: the next piece, handed to the consumers (they
+                    // take it when this tile has landed), its table window and new K/V row
+                    have_next = next_piece(nxt);
+                    if (have_next) {
+                        nxt_block = load_window(nxt);
+                        if (with_store && nxt.last)
+                            nxt_sc = scatter_prefetch(p, nxt.b, nxt.kvh, lane);
+                    }
+                }
                 if (page - page_base >= 32) {
                     page_base = page;
                     my_block = (page_base + lane <= last_page) ? table[page_base + lane] : 0;
                 }
                 const int block_id = __shfl_sync(0xffffffffu, my_block, page - page_base);
+                const int slot = block_id * p.block_size + in_page * kTile;
                 if (lane == 0) {
+                    uint8_t* dst = smem + stage * kStageBytes;
                     mbar_wait(&empty_bar[stage], phase ^ 1u);
                     mbar_expect_tx(&full_bar[stage], kStageBytes);
-                    const int slot = block_id * p.block_size + (t % tiles_per_page) * kTile;
-                    uint8_t* dst = smem + stage * kStageBytes;
                     tma_load_3d_hint(dst, &k_map, &full_bar[stage], 0, cur.kvh, slot, policy);
                     tma_load_3d_hint(dst + kSubTileBytes, &k_map, &full_bar[stage], 64, cur.kvh,
                                      slot, policy);
@@ -530,17 +598,24 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
                                      slot, policy);
                     tma_load_3d_hint(dst + 3 * kSubTileBytes, &v_map, &full_bar[stage], 64,
                                      cur.kvh, slot, policy);
+                    if (kTrace && it == 0) trace[kTrTma0] = clock64();
                 }
                 __syncwarp();
+                if (++in_page == tiles_per_page) {
+                    in_page = 0;
+                    ++page;
+                }
             }
             cur = nxt;
             cur_block = nxt_block;
             cur_sc = nxt_sc;
             have = have_next;
         }
-        // Dynamic regime: the CTA that finishes last puts the item counter back to zero for the
-        // next launch (every CTA passes here exactly once).
+        if (kTrace && lane == 0) trace[kTrProdExit] = clock64();
+        // Dynamic regime: the CTA that finishes last puts the counters back to zero for the next
+        // launch (every CTA passes here exactly once, after its last request has been answered).
         if (dynamic && lane == 0) {
+            asm volatile("" ::"r"(pre_item) : "memory");
             const int old = atomicAdd(p.sched + 1, 1);
             if (old == static_cast<int>(gridDim.x) - 1) {
                 p.sched[0] = 0;
@@ -563,36 +638,33 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
     const uint32_t v_row = warp * 16 + ((lane >> 4) << 3) + (lane & 7);
     const uint32_t v_csel = (lane >> 3) & 1;
 
-    ItemIter iter;
-    int item = blockIdx.x;
-    int n_taken = 0;
-    bool item_live = item < st.total_items;
-    if (item_live) iter.init(st, item);
-    auto next_piece = [&](Piece& out) -> bool {
-        for (;;) {
-            if (!item_live) return false;
-            if (iter.next(st, out)) return true;
-            if (dynamic) {
-                const int qs = n_taken % kItemQueue;
-                mbar_wait(&q_full[qs], (n_taken / kItemQueue) & 1u);
-                item = item_q[qs];
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&q_empty[qs]);
-                ++n_taken;
-            } else {
-                item += gridDim.x;
-            }
-            item_live = item < st.total_items;
-            if (item_live) iter.init(st, item);
-        }
+    int n_popped = 0;
+    auto pop = [&]() -> PieceDesc {
+        const int qs = n_popped % kPieceQueue;
+        mbar_wait(&q_full[qs], (n_popped / kPieceQueue) & 1u);
+        const int4 lo = piece_q[2 * qs], hi = piece_q[2 * qs + 1];
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&q_empty[qs]);
+        ++n_popped;
+        PieceDesc d;
+        d.b = lo.x;
+        d.kvh = lo.y;
+        d.t_begin = lo.z;
+        d.t_end = lo.w;
+        d.tiles_total = hi.x;
+        d.range = hi.y;
+        d.g_first = hi.z;
+        d.g_last = hi.w;
+        return d;
     };
-    Piece pc, nxt;
-    bool have = next_piece(pc);
+    PieceDesc pc = pop();
     QPre qpre;
-    if (have) q_prefetch(p, pc.b, pc.kvh, G, lane, qpre);
+    if (pc.b >= 0) q_prefetch(p, pc.b, pc.kvh, G, lane, qpre);
     int it = 0;
     int parity = 0;
-    while (have) {
+    unsigned long long tr_wait = 0, tr_epi = 0, tr_t0 = 0;
+    int tr_pieces = 0;
+    while (pc.b >= 0) {
         const int b = pc.b, kvh = pc.kvh;
         const int ctx = qpre.ctx;
         uint32_t qf[8][2];
@@ -602,13 +674,14 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
             qf[ks][1] = qpre.qf[ks][1];
         }
         q_finish(p, b, G, lane, qf);
-        const bool have_next = next_piece(nxt);
-        if (have_next) q_prefetch(p, nxt.b, nxt.kvh, G, lane, qpre);  // consumed next iteration
+        PieceDesc nxt;
+        nxt.b = -1;
         // A cut row is merged by the piece that arrives last at its counter: the ranges that hold
         // the row's first and last tile give the number of pieces and their workspace slots.
-        const bool whole = pc.first && pc.last;
-        int g_first = 0, g_last = 0;
-        if (!whole) piece_ranges(st, pc.b, &g_first, &g_last);
+        const int g_first = pc.g_first, g_last = pc.g_last;
+        const bool whole = g_first == g_last;
+        const bool first_piece = pc.range == g_first;
+
 
         float m_run[2] = {-INFINITY, -INFINITY};  // running max (log2 domain), heads 2*(lane%4)+{0,1}
         float l_run[2] = {0.f, 0.f};              // per-thread partial row sums
@@ -621,7 +694,21 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
         for (int t = pc.t_begin; t < pc.t_end; ++t, ++it) {
             const int stage = it % kStages;
             const uint32_t phase = (it / kStages) & 1u;
-            mbar_wait(&full_bar[stage], phase);
+            if (kTrace && threadIdx.x == 0) {
+                const unsigned long long w0 = clock64();
+                mbar_wait(&full_bar[stage], phase);
+                const unsigned long long w1 = clock64();
+                tr_wait += w1 - w0;
+                if (it == 0) trace[kTrTile0] = w1;
+            } else {
+                mbar_wait(&full_bar[stage], phase);
+            }
+            if (t == pc.t_end - 1) {
+                // The producer pushed the next descriptor before it issued this (last) tile, so
+                // it is there now. Its q loads run under this tile and the epilogue.
+                nxt = pop();
+                if (nxt.b >= 0) q_prefetch(p, nxt.b, nxt.kvh, G, lane, qpre);
+            }
             const uint32_t kb = smem_base + stage * kStageBytes;
             const uint32_t vb = kb + 2 * kSubTileBytes;
 
@@ -694,6 +781,10 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
             if (lane == 0) mbar_arrive(&empty_bar[stage]);
         }
 
+        if (kTrace && threadIdx.x == 0) {
+            tr_t0 = clock64();
+            if (tr_pieces == 0) trace[kTrTilesDone0] = tr_t0;
+        }
         // ---- finish the row sums (tokens are spread over lane/4) ----
 #pragma unroll
         for (int off = 4; off < 32; off <<= 1) {
@@ -753,7 +844,7 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
         // Final reduction: warp w owns heads w, w+4; lane owns dims 4*lane..4*lane+3 (float4
         // shared-memory reads, 8-byte bf16 / 16-byte fp32 global stores, a head row is one line).
         const int64_t q_row0 = static_cast<int64_t>(b) * Hq + static_cast<int64_t>(kvh) * G;
-        const int slot = 2 * (pc.range * p.num_kv_heads + kvh) + (pc.first ? 1 : 0);
+        const int slot = 2 * (pc.range * p.num_kv_heads + kvh) + (first_piece ? 1 : 0);
         for (int h = warp; h < G; h += kConsumerWarps) {
             float m = -INFINITY;
 #pragma unroll
@@ -847,13 +938,26 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
                 merge_row(src, static_cast<__nv_bfloat16*>(p.out), lane);
             }
         }
+        if (kTrace && threadIdx.x == 0) {
+            const unsigned long long now = clock64();
+            if (tr_pieces == 0) trace[kTrEpi0] = now;
+            tr_epi += now - tr_t0;
+            ++tr_pieces;
+        }
         pc = nxt;
-        have = have_next;
+    }
+    if (kTrace && threadIdx.x == 0) {
+        trace[kTrConsExit] = clock64();
+        trace[kTrExitNs] = global_timer_ns();
+        trace[kTrPieces] = tr_pieces;
+        trace[kTrTiles] = it;
+        trace[kTrWait] = tr_wait;
+        trace[kTrEpi] = tr_epi;
     }
     if (p.plan != nullptr) grid_dependency_wait();
 }
 
-template <int kStages>
+template <int kStages, bool kTrace>
 cudaError_t launch_stream(const DecodeParams& p, const CUtensorMap& k_map, const CUtensorMap& v_map,
                           cudaStream_t stream) {
     constexpr int smem = DecodeSmem<kStages>::kBytes;
@@ -862,7 +966,7 @@ cudaError_t launch_stream(const DecodeParams& p, const CUtensorMap& k_map, const
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) dev = 0;
     if (dev < 0 || dev >= 64 || !configured[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(decode_stream_kernel<kStages>,
+        cudaError_t e = cudaFuncSetAttribute(decode_stream_kernel<kStages, kTrace>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
         if (dev >= 0 && dev < 64) configured[dev] = true;
@@ -885,7 +989,8 @@ cudaError_t launch_stream(const DecodeParams& p, const CUtensorMap& k_map, const
         cfg.attrs = attr;
         cfg.numAttrs = 1;
     }
-    cudaError_t e = cudaLaunchKernelEx(&cfg, decode_stream_kernel<kStages>, k_map, v_map, p);
+    cudaError_t e =
+        cudaLaunchKernelEx(&cfg, decode_stream_kernel<kStages, kTrace>, k_map, v_map, p);
     count_launch();
     return e != cudaSuccess ? e : cudaGetLastError();
 }
@@ -899,7 +1004,7 @@ int env_int(const char* name, int dflt, int lo, int hi) {
 
 int decode_stages_from_env() {
     static int stages = [] {
-        const int s = env_int("B200ATTN_DECODE_STAGES", 3, 2, 3);
+        const int s = env_int("B200ATTN_DECODE_STAGES", 3, 2, 6);
         return s;
     }();
     return stages;
@@ -911,7 +1016,7 @@ int decode_stages_from_env() {
 // before another CTA is started (below that the partials + merge cost more than the extra
 // parallelism hides); B200ATTN_DECODE_ROW_COST = virtual units charged per row for its fixed cost.
 int decode_min_units() {
-    static int v = env_int("B200ATTN_DECODE_MIN_TILES", 8, 1, 4096);
+    static int v = env_int("B200ATTN_DECODE_MIN_TILES", 16, 1, 4096);
     return v;
 }
 int decode_row_cost() {
@@ -923,14 +1028,19 @@ int decode_snap() {
     static int v = env_int("B200ATTN_DECODE_SNAP", 2, 0, 64);
     return v;
 }
-// Dynamic regime: B200ATTN_DECODE_WAVES ranges per CTA group aimed for (1 = always static), used
-// when uncut rows leave at least B200ATTN_DECODE_DYN_MIN ranges per CTA group.
-int decode_waves() {
-    static int v = env_int("B200ATTN_DECODE_WAVES", 8, 1, 16);
+// Dynamic regime (whole rows from an atomic counter): B200ATTN_DECODE_DYNAMIC=0 switches it off;
+// it is used when the longest row is at most B200ATTN_DECODE_DYN_PCT % of a CTA group's share.
+int decode_dyn_ok() {
+    static int v = env_int("B200ATTN_DECODE_DYNAMIC", 1, 0, 1);
     return v;
 }
-int decode_dyn_min() {
-    static int v = env_int("B200ATTN_DECODE_DYN_MIN", 2, 1, 16);
+int decode_dyn_pct() {
+    static int v = env_int("B200ATTN_DECODE_DYN_PCT", 200, 0, 100000);
+    return v;
+}
+// Static regime: percent of the CTA groups that get a range.
+int decode_static_pct() {
+    static int v = env_int("B200ATTN_DECODE_STATIC_PCT", 50, 1, 100);
     return v;
 }
 
@@ -979,7 +1089,9 @@ int decode_pick_ctas(int32_t batch, int32_t num_kv_heads, int32_t table_width, i
     const int64_t max_units =
         rows * (static_cast<int64_t>(table_width) * block_size / kTile + decode_row_cost());
     int64_t n = (max_units + decode_min_units() - 1) / decode_min_units();
-    const int64_t cap = 2 * static_cast<int64_t>(sm_count);
+    static const int per_sm = env_int("B200ATTN_DECODE_CTAS_PER_SM", 2, 1, 2);
+    const int64_t cap = per_sm * static_cast<int64_t>(sm_count);
+    if (n < rows) n = rows;  // never fewer CTAs than rows (while they fit): a row is never queued
     if (n > cap) n = cap;
     if (n >= num_kv_heads) n -= n % num_kv_heads;
     return static_cast<int>(n < 1 ? 1 : n);
@@ -990,8 +1102,9 @@ StreamTunables decode_tunables() {
     t.min_units = decode_min_units();
     t.row_cost = decode_row_cost();
     t.snap = decode_snap();
-    t.waves = decode_waves();
-    t.dyn_min = decode_dyn_min();
+    t.dyn_ok = decode_dyn_ok();
+    t.dyn_pct = decode_dyn_pct();
+    t.static_pct = decode_static_pct();
     return t;
 }
 
@@ -1001,7 +1114,7 @@ int decode_partition_host(const int32_t* context_lens, int32_t batch, int32_t nu
     // The kernel's own partition code (decode_plan.cuh) run on the host: scan, ranges, pieces.
     const int t_skip = shared_pages * (block_size / kTile);
     StreamTunables tun = decode_tunables();
-    if (num_ctas == 1) tun.waves = 1;  // as the decode entry points do without counters
+    if (num_ctas == 1) tun.dyn_ok = 0;  // as the decode entry points do without counters
     int32_t* cum = new int32_t[batch + 1];
     cum[0] = 0;
     int max_row_units = 0;
@@ -1020,8 +1133,17 @@ int decode_partition_host(const int32_t* context_lens, int32_t batch, int32_t nu
         while (iter.next(st, pc)) {
             if (n < max_pieces) {
                 int32_t* o = pieces + static_cast<int64_t>(n) * 12;
-                int g_first = pc.range, g_last = pc.range;
-                if (!(pc.first && pc.last)) piece_ranges(st, pc.b, &g_first, &g_last);
+                const PieceDesc d = piece_desc(st, pc);  // what the consumers are handed
+                const int g_first = d.g_first, g_last = d.g_last;
+                if (!(pc.first && pc.last)) {
+                    // the closed forms must agree with the definition (search over the boundaries)
+                    int gf, gl;
+                    piece_ranges(st, pc.b, &gf, &gl);
+                    if (gf != g_first || gl != g_last) {
+                        delete[] cum;
+                        return -1000 - item;
+                    }
+                }
                 o[0] = item;
                 o[1] = pc.b;
                 o[2] = pc.kvh;
@@ -1045,9 +1167,12 @@ int decode_partition_host(const int32_t* context_lens, int32_t batch, int32_t nu
 cudaError_t launch_decode(const DecodeParams& p, const CUtensorMap& k_map, const CUtensorMap& v_map,
                           cudaStream_t stream) {
     if (p.batch == 0) return cudaSuccess;
+    if (p.trace != nullptr) return launch_stream<3, true>(p, k_map, v_map, stream);
     switch (decode_stages_from_env()) {
-        case 2: return launch_stream<2>(p, k_map, v_map, stream);
-        default: return launch_stream<3>(p, k_map, v_map, stream);
+        case 2: return launch_stream<2, false>(p, k_map, v_map, stream);
+        case 4: return launch_stream<4, false>(p, k_map, v_map, stream);
+        case 6: return launch_stream<6, false>(p, k_map, v_map, stream);
+        default: return launch_stream<3, false>(p, k_map, v_map, stream);
     }
 }
 

@@ -88,9 +88,10 @@ int b200attn_store_kvcache(const void* key, int64_t key_row_stride, const void* 
  * plus a small fixed cost per sequence, form one unit stream per KV head. The kernel launches
  * `num_splits` persistent CTAs and cuts the stream into contiguous ranges ON THE DEVICE from
  * context_lens; a work item is (range, KV head), items with adjacent ids stream the same tokens of
- * adjacent KV heads side by side. Many short rows: ranges are whole rows (no row is cut, nothing
- * is merged), several per CTA, and CTAs take items beyond their first from an atomic counter, so
- * the faster SMs take more of them. Few long rows: one equal range per CTA group (num_splits /
+ * adjacent KV heads side by side. Many rows (the longest at most B200ATTN_DECODE_DYN_PCT % of a
+ * CTA group's share): a range is one whole sequence (no row is cut, nothing is merged) and CTAs
+ * take items beyond their first from an atomic counter, so the faster SMs take more of them.
+ * Few or long rows: one equal range per CTA group (num_splits /
  * num_kv_heads groups); a range boundary cuts at most one row and cut rows are finished by the
  * piece that arrives last (in-launch merge through the workspace). Both regimes need the counters
  * of b200attn_set_split_counters when num_splits > 1. Any num_splits in [1, 2048] gives the same
@@ -113,11 +114,16 @@ int b200attn_decode_pick_splits(int32_t batch, int32_t num_kv_heads, int32_t tab
  * negative error. Field 0 is the work item (= range * num_kv_heads + kv_head; items below
  * num_splits are the CTAs' first items, later ones are taken dynamically), field 10 its range,
  * field 11 the units per range with bit 30 set in the dynamic regime. Tiles are 64 tokens. Uses
- * the same B200ATTN_DECODE_MIN_TILES / _ROW_COST / _SNAP / _WAVES / _DYN_MIN tunables.
+ * the same B200ATTN_DECODE_MIN_TILES / _ROW_COST / _SNAP / _DYNAMIC / _DYN_PCT tunables.
  */
 int b200attn_decode_partition_host(const int32_t* context_lens, int32_t batch,
                                    int32_t num_kv_heads, int32_t num_splits, int32_t shared_pages,
                                    int32_t block_size, int32_t* pieces, int32_t max_pieces);
+
+/* Debug only: with a device buffer of 16 uint64 per CTA registered, the decode entry points launch
+ * an instrumented build of the kernel that stamps its phases there (tools/trace_decode.py);
+ * NULL (the default) restores the product kernel. Not thread-safe, not for production. */
+void b200attn_debug_decode_trace(void* stamps);
 
 /* Bytes of fp32 workspace the decode entry points need: two partial-piece slots per work item that
  * can hold a cut row when num_splits > 1 (at most num_splits + num_q_heads items), plus batch * num_q_heads * prefix_chunks shared-prefix partials for the cascade

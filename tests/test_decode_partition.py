@@ -10,8 +10,8 @@ kernel's correctness rests on are pinned without a GPU:
     piece reports the same pair;
   * an item writes at most one piece per workspace slot (2i = continues an earlier range's row,
     2i+1 = continued by the next range), and the slots fit the workspace the ABI sizes;
-  * every KV head sees the same cut; ranges are balanced (static regime) or fine enough for the
-    atomic item counter to balance them (dynamic regime), and short rows are never cut there.
+  * every KV head sees the same cut; ranges are balanced (static regime) or whole sequences taken
+    from the atomic item counter (dynamic regime: no row is ever cut there).
 """
 import ctypes
 import random
@@ -38,7 +38,7 @@ def partition(lib, lens, Hkv, n_cta, shared_pages=0, block_size=256):
     return out[:n]
 
 
-WAVES = 8  # B200ATTN_DECODE_WAVES default
+DYN_PCT = 60  # B200ATTN_DECODE_DYN_PCT default
 
 
 def check(lib, lens, Hkv, n_cta, shared_pages=0, block_size=256):
@@ -125,55 +125,85 @@ def test_shared_prefix_is_skipped(lib):
     assert pieces[:, 3].min() == 12  # no piece starts before the 3 shared pages (12 tiles)
 
 
+MIN_UNITS, DYN_PCT, STATIC_PCT = 16, 200, 50  # B200ATTN_DECODE_MIN_TILES / _DYN_PCT / _STATIC_PCT
+
+
+def units_of(lens):
+    return [-(-c // 64) + 1 if c > 0 else 0 for c in lens]
+
+
+def expect_regime(lens, Hkv, n_cta):
+    """(dynamic, per) as csrc/decode_plan.cuh stream_init decides them."""
+    u = units_of(lens)
+    groups = max(n_cta // Hkv, 1)
+    share = -(-sum(u) // groups)
+    if n_cta > 1 and sum(u) > 0 and max(u) * 100 <= DYN_PCT * share:
+        return True, max(share, MIN_UNITS)
+    g_static = max(groups * STATIC_PCT // 100, 1)
+    return False, max(-(-sum(u) // g_static), MIN_UNITS)
+
+
 def test_static_regime_is_balanced(lib):
-    """bench.py's c2 shape at TP=8 / TP=4 (Hkv 1 / 2): ragged 169..1502 tokens, about 12 / 24 units
-    per CTA group: one range per group, equal to within the boundary snap, and the longest row
-    (24 tiles) is cut instead of being the tail."""
-    rng = random.Random(1)
-    lens = [rng.randint(169, 1502) for _ in range(256)]
-    total = sum(-(-c // 64) + 1 for c in lens)
-    for Hkv, n_cta in ((1, 296), (2, 296)):
+    """Few long rows (the longest more than twice a CTA group's share): equal ranges over half the
+    CTA groups (one CTA per SM streams evenly; fewer pieces to merge), each range equal to within
+    the boundary snap, so a long row is cut instead of being the tail."""
+    for lens, Hkv, n_cta in (([16384] * 8, 8, 296), ([32768] * 2, 8, 296), ([131072], 8, 296),
+                             ([131072], 1, 296), ([60000] + [300] * 255, 8, 296),
+                             ([4096] * 4, 8, 256)):
         pieces = check(lib, lens, Hkv, n_cta)
         per, dynamic = regime(pieces)
-        n_groups = n_cta // Hkv
-        assert not dynamic and per == max(-(-total // n_groups), 8)
-        units = np.zeros(n_groups, dtype=np.int64)
+        assert (dynamic, per) == expect_regime(lens, Hkv, n_cta)
+        assert not dynamic
+        n_ranges = int(pieces[:, 10].max()) + 1
+        assert n_ranges <= max((n_cta // Hkv) * STATIC_PCT // 100, 1)
+        units = np.zeros(n_ranges, dtype=np.int64)
         for item, b, kvh, t0, t1, tot, first, *_ in pieces.tolist():
             if kvh == 0:
                 units[item // Hkv] += t1 - t0 + (1 if first else 0)  # row cost on the first piece
-        assert units.sum() == total
+        assert units.sum() == sum(units_of(lens))
         busy = units[units > 0]
         assert busy.max() <= per + 2 * 2, "a range grows by less than the snap at each end"
-        if Hkv == 1:
-            assert busy.max() < 24 + 1
 
 
 def test_dynamic_regime_never_cuts_a_row(lib):
-    """c2 at TP=1 (Hkv 8, ~97 units per CTA group): ranges of half the longest row or 1/8 of a
-    group's share, every boundary on a row boundary: no row is cut, nothing is merged, and there
-    are several items per CTA for the atomic counter to balance. Few long rows fall back to the
-    static regime (cutting them finer would only add pieces to merge)."""
+    """Many rows (the longest at most twice a CTA group's share): a range is one sequence, an item
+    one whole (sequence, KV head) row in batch order: no row is cut, nothing is merged, no search
+    is needed, and CTAs beyond their first item take rows from the atomic counter."""
     rng = random.Random(1)
     lens = [rng.randint(169, 1502) for _ in range(256)]
-    units = [-(-c // 64) + 1 for c in lens]
-    pieces = check(lib, lens, 8, 296)
-    per, dynamic = regime(pieces)
-    assert dynamic and per == max(-(-sum(units) // (37 * WAVES)), -(-max(units) // 2), 8)
-    assert all(f and l for f, l in pieces[:, 6:8].tolist()), "no row may be cut"
-    n_items = len({int(i) for i in pieces[:, 0]})
-    assert 2 * 296 <= n_items <= WAVES * 296
-    # config 3 (128 x 4096): rows of 65 units -> ranges of 33: one row per item, never cut
-    pieces = check(lib, [4096] * 128, 8, 296)
-    assert regime(pieces) == (33, True)
-    assert all(f and l for f, l in pieces[:, 6:8].tolist()) and len(pieces) == 128 * 8
-    # one 128k-token sequence / 8 x 16k / 16 x 4096: too few rows to balance uncut -> static
-    for lens_, groups in (([131072], 37), ([16384] * 8, 37), ([4096] * 16, 37)):
-        pieces = check(lib, lens_, 8, 296)
+    for Hkv in (8, 2, 1):  # bench.py's c2 shape at TP = 1, 4, 8
+        pieces = check(lib, lens, Hkv, 296)
         per, dynamic = regime(pieces)
-        assert not dynamic and per == -(-sum(-(-c // 64) + 1 for c in lens_) // groups)
+        assert dynamic and (dynamic, per) == expect_regime(lens, Hkv, 296)
+        assert all(f and l for f, l in pieces[:, 6:8].tolist()), "no row may be cut"
+        assert pieces[:, 0].tolist() == list(range(256 * Hkv)), "item = sequence * Hkv + kv head"
+        assert pieces[:, 10].tolist() == pieces[:, 1].tolist(), "range id = sequence"
+    # padding rows are items without a piece
+    pieces = check(lib, [0 if i % 5 == 0 else l for i, l in enumerate(lens)], 8, 296)
+    assert regime(pieces)[1] and len(pieces) == 8 * sum(1 for i in range(256) if i % 5)
+    # config 3 (128 x 4096), 64 x 4096, 32 x 4096 (65 units against a share of 57): dynamic
+    for B in (128, 64, 32):
+        pieces = check(lib, [4096] * B, 8, 296)
+        assert regime(pieces)[1] and len(pieces) == B * 8
+    # 16 x 4096 (share 29): rows are cut
+    assert not regime(check(lib, [4096] * 16, 8, 296))[1]
     # a single CTA (no counters registered) walks every item statically
     pieces = check(lib, lens, 8, 1)
     assert not regime(pieces)[1] and all(f and l for f, l in pieces[:, 6:8].tolist())
+
+
+def test_closed_form_first_and_last_range(lib):
+    """b200attn_decode_partition_host cross-checks the O(1) first / last range of every cut row
+    against the definition (search over the snapped boundaries) and fails with < -1000 on a
+    mismatch; check() asserts n >= 0. Ragged batches with many cuts, all snap cases."""
+    rng = random.Random(7)
+    for _ in range(300):
+        B = rng.choice([1, 2, 3, 5, 9, 17, 40])
+        Hkv = rng.choice([1, 2, 8])
+        n_cta = rng.choice([8, 16, 37, 74, 148, 296])
+        lens = [rng.choice([0, 64, 65, 128, 129, 1000, 1023, 1024, 1025, rng.randint(1, 70000)])
+                for _ in range(B)]
+        check(lib, lens, Hkv, n_cta)
 
 
 def test_boundary_snap_avoids_tiny_pieces(lib):

@@ -17,22 +17,23 @@ def lib(built_lib):
 
 def test_pick_splits_is_host_only_and_sane(lib):
     """num_splits = persistent CTAs of the decode kernel: two per SM, fewer when even full tables
-    could not give every CTA its minimum range (8 units by default, 1 unit per row of overhead).
+    could not give every CTA its minimum range (16 units by default, 1 unit per row of overhead)
+    - but never fewer than one per (sequence, KV head) row while the rows fit.
     How the work is cut is decided on the device (tests/test_decode_partition.py)."""
     sm = 148
     assert lib.b200attn_decode_pick_splits(512, 8, 4, 256, sm) == 2 * sm
     assert lib.b200attn_decode_pick_splits(128, 8, 16, 256, sm) == 2 * sm
     assert lib.b200attn_decode_pick_splits(256, 1, 16, 256, sm) == 2 * sm  # TP=8 rank of config 2
     assert lib.b200attn_decode_pick_splits(1, 8, 512, 256, sm) == 2 * sm   # one long sequence
-    # one page per row, one row per KV head: 8 rows x (4 tiles + 1) = 40 units -> 5 CTAs
-    assert lib.b200attn_decode_pick_splits(1, 8, 1, 256, sm) == 5   # < Hkv: CTAs walk heads
-    assert lib.b200attn_decode_pick_splits(1, 8, 4, 256, sm) == 16  # multiples of Hkv beyond
+    # one page per row, one row per KV head: 8 rows x (4 tiles + 1) = 40 units -> one CTA per row
+    assert lib.b200attn_decode_pick_splits(1, 8, 1, 256, sm) == 8   # never fewer CTAs than rows
+    assert lib.b200attn_decode_pick_splits(1, 8, 8, 256, sm) == 16  # multiples of Hkv beyond
     assert lib.b200attn_decode_pick_splits(1, 1, 1, 256, sm) == 1
     for b in (1, 2, 4, 8, 16, 64):
         for w in (1, 4, 16, 128):
             s = lib.b200attn_decode_pick_splits(b, 1, w, 256, sm)
             assert 1 <= s <= 2 * sm
-            assert s <= max(1, -(-b * (4 * w + 1) // 8))
+            assert s <= max(b, -(-b * (4 * w + 1) // 16))
     assert lib.b200attn_decode_pick_splits(4, 8, 16, 256, 0) >= 1  # unknown SM count -> 148
     assert lib.b200attn_decode_pick_splits(0, 8, 16, 256, sm) == 1
 

@@ -17,6 +17,8 @@ from pathlib import Path
 
 ROOT = Path(__file__).resolve().parents[1]
 sys.path.insert(0, str(ROOT))
+if os.environ.get("B200_AB_PKG"):  # A/B against another build of the package (e.g. an older tree)
+    sys.path.insert(0, str(ROOT / os.environ["B200_AB_PKG"]))
 
 SHAPES = [  # (B, ctx or "bench", Hq, Hkv)
     (256, "bench", 2, 1), (256, "bench", 4, 2), (256, "bench", 16, 8),
@@ -25,7 +27,9 @@ SHAPES = [  # (B, ctx or "bench", Hq, Hkv)
     (128, 4096, 4, 1), (512, 1024, 32, 8), (16, 4096, 32, 8), (2, 32768, 32, 8), (1, 1024, 32, 8),
     (256, 8192, 8, 1),
 ]
-GRID = {"B200ATTN_DECODE_WAVES": ["1", "2", "4", "8"], "B200ATTN_DECODE_DYN_MIN": ["16", "32", "64"]}
+GRID = {"B200ATTN_DECODE_WAVES": ["1", "4", "8", "16"], "B200ATTN_DECODE_DYN_MIN": ["2", "4"]}
+if os.environ.get("B200_SWEEP_GRID"):  # e.g. '{"B200_AB_PKG": ["", "_ab_old"]}'
+    GRID = json.loads(os.environ["B200_SWEEP_GRID"])
 
 
 def child():
@@ -35,6 +39,11 @@ def child():
 
     import bench
 
+    if os.environ.get("B200_AB_PKG"):  # bench.py put the repo root first again
+        sys.path.insert(0, str(ROOT / os.environ["B200_AB_PKG"]))
+    import byox_vllm_b200
+
+    print("package:", byox_vllm_b200.__file__, flush=True)
     res = []
     with torch.inference_mode():
         for (B, ctx, Hq, Hkv) in SHAPES:
@@ -47,7 +56,7 @@ def child():
 def main():
     if "--child" in sys.argv:
         return child()
-    out = ROOT / "gpurun_out" / "decode_tunables.jsonl"
+    out = ROOT / "gpurun_out" / os.environ.get("B200_SWEEP_OUT", "decode_tunables.jsonl")
     out.parent.mkdir(exist_ok=True)
     keys = list(GRID)
     with open(out, "w") as f:
@@ -59,6 +68,7 @@ def main():
             if r.returncode != 0 or not line:
                 print("FAILED", combo, r.stderr[-1500:], flush=True)
                 continue
+            print([l for l in r.stdout.splitlines() if l.startswith("package:")], flush=True)
             res = json.loads(line[-1][7:])
             f.write(json.dumps(dict(zip(keys, combo), results=res)) + "\n")
             f.flush()
