@@ -524,9 +524,20 @@ def decode_inputs(B, lens_l, Hq, Hkv, n_copies, shared_pages=0, seed=0):
     return lens, sets, unique_tokens * Hkv * D * 4 + io, sum(lens_l) * Hkv * D * 4 + io
 
 
-def extra_decode(name, B, ctx, Hq, Hkv, shared_tokens=0, ref=True):
+def extra_decode(name, B, ctx, Hq, Hkv, shared_tokens=0, ref=True, overlap=None):
     from byox_vllm_b200.attention import (cascade_chunks, cascade_plan, decode_num_splits,
                                           paged_decode)
+
+    if overlap is not None:  # overlap mode as under install(): launches are PDL dependents
+        from byox_vllm_b200.attention import set_decode_overlap
+
+        prev = set_decode_overlap(overlap)
+        try:
+            rec = extra_decode(name, B, ctx, Hq, Hkv, shared_tokens, ref)
+        finally:
+            set_decode_overlap(prev)
+        rec["overlap"] = bool(overlap)
+        return rec
 
     lens_l = context_lengths(dict(ctx=ctx, batch=B))
     per_copy = sum(lens_l) * Hkv * D * 4

@@ -98,6 +98,16 @@ def ensure_split_counters(device: torch.device) -> None:
     _SPLIT_COUNTERS[idx] = buf
 
 
+def set_decode_overlap(on: bool) -> bool:
+    """Overlap mode of the decode launches (b200attn_set_decode_overlap): each launch becomes a
+    programmatic dependent of the kernel before it in the stream and runs its prologue (scan of
+    context_lens, first work item, block-table window) while that kernel drains. Only valid when
+    context_lens / block_tables are not written by the kernel right before a decode call - true
+    inside the engine, where they are set once per step (model_runner.py:206-226); install()
+    switches it on. Returns the previous setting."""
+    return bool(_lib.load().b200attn_set_decode_overlap(1 if on else 0))
+
+
 def decode_num_splits(batch: int, num_kv_heads: int, table_width: int, block_size: int) -> int:
     """Host-only choice of the number of persistent CTAs the batch's KV tile stream is cut into
     (a function of host-visible sizes: graph-capture rule; the cut itself happens on the device

@@ -167,6 +167,7 @@ struct SplitCounters {
 };
 static SplitCounters g_split_counters[64];
 static unsigned long long* g_decode_trace = nullptr;  // b200attn_debug_decode_trace
+static std::atomic<int> g_decode_overlap{0};          // b200attn_set_decode_overlap
 static std::mutex g_split_counters_mu;
 
 static int32_t* split_counters_for(int64_t need, int32_t** sched) {
@@ -206,7 +207,11 @@ static int store_decode_impl(const void* q, int64_t q_row_stride, const void* ke
     if (batch < 0 || num_blocks <= 0 || table_width < 0 || num_splits < 1)
         return fail(B200ATTN_E_BADARG, "negative or zero size");
     if (batch == 0) return 0;
-    if (num_splits > 2048) return fail(B200ATTN_E_UNSUPPORTED, "num_splits %d > 2048", num_splits);
+    const bool rows_engine = b200::decode_engine_rows();
+    if (num_splits > (rows_engine ? 1024 : 2048))
+        return fail(B200ATTN_E_UNSUPPORTED, "num_splits %d too large", num_splits);
+    if (rows_engine && batch > 65535)
+        return fail(B200ATTN_E_UNSUPPORTED, "batch %d > 65535 rows per launch", batch);
     if (prefix_chunks > 0 && batch > b200::kDecodeMaxBatch)
         return fail(B200ATTN_E_UNSUPPORTED, "cascade decode handles at most %d rows, got %d",
                     b200::kDecodeMaxBatch, batch);
@@ -272,9 +277,11 @@ static int store_decode_impl(const void* q, int64_t q_row_stride, const void* ke
     p.group = num_q_heads / num_kv_heads;
     p.block_size = block_size;
     p.num_ctas = num_splits;
+    p.num_splits = num_splits;
     p.tun = b200::decode_tunables();
     if (num_splits == 1) p.tun.dyn_ok = 0;  // no counters: static regime (one CTA walks every item)
     p.trace = g_decode_trace;
+    p.overlap = (g_decode_overlap.load(std::memory_order_relaxed) != 0 && plan == nullptr) ? 1 : 0;
     p.scale_log2 = scale * 1.4426950408889634f;
     if (with_store && fused_store) {
         p.new_key = key;
@@ -290,7 +297,8 @@ static int store_decode_impl(const void* q, int64_t q_row_stride, const void* ke
     p.plan = plan;
     p.prefix_chunks = prefix_chunks;
     if (num_splits > 1) {
-        const int64_t rows = batch < b200::kDecodeMaxBatch ? batch : b200::kDecodeMaxBatch;
+        const int64_t rows =
+            (rows_engine || batch < b200::kDecodeMaxBatch) ? batch : b200::kDecodeMaxBatch;
         // layout of the registered buffer: [rows * Hkv arrival counters | ... | sched[2] at the end]
         p.split_counters = split_counters_for(rows * num_kv_heads + 2, &p.sched);
         if (p.split_counters == nullptr)
@@ -335,10 +343,10 @@ static int store_decode_impl(const void* q, int64_t q_row_stride, const void* ke
     }
     // The kernel keeps the scan of the batch in shared memory: larger batches (eager decode above
     // the graph sizes, model_runner.py:230) run as consecutive launches over row blocks.
-    for (int32_t row0 = 0; row0 < batch; row0 += b200::kDecodeMaxBatch) {
+    const int32_t rows_per_launch = rows_engine ? batch : b200::kDecodeMaxBatch;
+    for (int32_t row0 = 0; row0 < batch; row0 += rows_per_launch) {
         b200::DecodeParams pc = p;
-        const int32_t rows = batch - row0 < b200::kDecodeMaxBatch ? batch - row0
-                                                                  : b200::kDecodeMaxBatch;
+        const int32_t rows = batch - row0 < rows_per_launch ? batch - row0 : rows_per_launch;
         pc.batch = rows;
         pc.q = static_cast<const __nv_bfloat16*>(q) + static_cast<int64_t>(row0) * q_row_stride;
         pc.out = static_cast<__nv_bfloat16*>(out) +
@@ -728,6 +736,10 @@ int b200attn_prepare_decode(const int32_t* packed, int32_t batch, int32_t table_
     p.block_size = block_size;
     cudaError_t e = b200::launch_prepare_decode(p, static_cast<cudaStream_t>(stream));
     return e == cudaSuccess ? 0 : cuda_fail(e, "prepare_decode launch");
+}
+
+int b200attn_set_decode_overlap(int on) {
+    return g_decode_overlap.exchange(on ? 1 : 0, std::memory_order_relaxed);
 }
 
 void b200attn_debug_decode_trace(void* stamps) {

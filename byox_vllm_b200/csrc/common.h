@@ -114,9 +114,17 @@ struct DecodeParams {
     // head); the piece of a cut row that arrives last merges the partials itself and resets the
     // counter, so no merge kernel is launched. Required when num_ctas > 1.
     int32_t* split_counters;
+    // rows engine: pieces per (sequence, KV head) row, grid = (KV heads, num_splits, batch)
+    int32_t num_splits;
     // dynamic work distribution (num_ctas > 1): sched[0] = next work item beyond the first wave,
     // sched[1] = CTAs finished; both zero between launches (the last CTA resets them).
     int32_t* sched;
+    // Overlap mode (b200attn_set_decode_overlap): the launch is a programmatic dependent of the
+    // kernel before it in the stream; scan, first work item and its block-table window run while
+    // that kernel drains, griddepcontrol.wait comes before anything else is read or written.
+    // Requires that context_lens / block_tables are not written by that kernel. Ignored with the
+    // cascade armed (the launch is then a dependent of the prefix pass).
+    int32_t overlap;
     // debug: 16 uint64 stamps per CTA (b200attn_debug_decode_trace); nullptr = the product kernel
     unsigned long long* trace;
 };
@@ -132,6 +140,11 @@ int decode_pick_ctas(int32_t batch, int32_t num_kv_heads, int32_t table_width, i
 int decode_partition_host(const int32_t* context_lens, int32_t batch, int32_t num_kv_heads,
                           int32_t num_ctas, int32_t shared_pages, int32_t block_size,
                           int32_t* pieces, int32_t max_pieces);
+// Two engines behind the same entry points (B200ATTN_DECODE_ENGINE = rows | stream, default rows):
+//   rows   - one CTA per (KV head, split, sequence), hardware block scheduler, num_splits = equal
+//            pieces per row picked on the host from sizes;
+//   stream - num_splits persistent CTAs, device-built partition of the batch's tile stream.
+bool decode_engine_rows();
 int decode_min_units();
 int decode_row_cost();
 int decode_snap();

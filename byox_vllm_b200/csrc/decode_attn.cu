@@ -77,9 +77,11 @@ struct MergeSrc {
     const float* prefix_o;   // [B * Hq][chunks][128]
     const float* prefix_lse; // [B * Hq][chunks]
     int g_first, kvh, num_kv_heads, n_piece, h_local;
+    int rows_base;           // rows engine: slot of the row's split 0 (>= 0); stream engine: -1
     int64_t row;             // b * Hq + q head
     int prefix_chunks, n_prefix;
     __device__ __forceinline__ int piece_slot(int i) const {
+        if (rows_base >= 0) return rows_base + i;
         return 2 * ((g_first + i) * num_kv_heads + kvh) + (i == 0 ? 1 : 0);
     }
     __device__ __forceinline__ const float* lse_ptr(int i) const {
@@ -141,7 +143,8 @@ __device__ __forceinline__ void merge_row(const MergeSrc& src, __nv_bfloat16* __
     *reinterpret_cast<uint2*>(out + src.row * kHeadDim + lane * 4) = pk;
 }
 
-// Every piece of a cut row calls this after its partial is written (the 128 consumer threads).
+// Every piece of a cut row calls this after its partial is written (the 128 consumer threads, or
+// all 160 threads of a rows-engine CTA with an empty split).
 // Returns true in the CTA that arrived last - that one merges. The partial stores of all threads
 // are ordered before thread 0's arrival by the CTA barrier; the arrival is an acq_rel atomic at gpu
 // scope (release is cumulative over what the barrier ordered before it, acquire makes the other
@@ -155,16 +158,17 @@ __device__ __forceinline__ int atom_add_acq_rel_gpu(int32_t* addr, int v) {
                  : "memory");
     return old;
 }
+template <int kThreads, int kBarId>
 __device__ __forceinline__ bool piece_arrive_is_last(int32_t* counter, int n_pieces,
                                                      int* flag_smem) {
-    consumer_bar_sync();
+    asm volatile("bar.sync %0, %1;" ::"n"(kBarId), "n"(kThreads) : "memory");
     if (threadIdx.x == 0) {
         const int old = atom_add_acq_rel_gpu(counter, 1);
         const int last = old == n_pieces - 1;
         if (last) *counter = 0;
         *flag_smem = last;
     }
-    consumer_bar_sync();
+    asm volatile("bar.sync %0, %1;" ::"n"(kBarId), "n"(kThreads) : "memory");
     return *flag_smem != 0;
 }
 
@@ -351,7 +355,11 @@ __device__ __forceinline__ unsigned long long global_timer_ns() {
     return t;
 }
 
-template <int kStages, bool kTrace>
+// kRows = false: the persistent stream engine described above (grid = CTAs, work from the scan).
+// kRows = true: the rows engine - grid (KV head, split, sequence), one piece per CTA, the hardware
+//   block scheduler hands out the rows. No scan, no queue: every CTA derives its piece from its
+//   own context_lens entry, so its first TMA is two dependent loads from kernel entry.
+template <int kStages, bool kTrace, bool kRows>
 __global__ void __launch_bounds__(kDecodeThreads, 2)
 decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
                      const __grid_constant__ CUtensorMap v_map, const DecodeParams p) {
@@ -373,7 +381,8 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
     const int G = p.group;
     const int Hq = p.num_q_heads;
     const int B = p.batch;
-    unsigned long long* trace = kTrace ? p.trace + static_cast<size_t>(blockIdx.x) * 16 : nullptr;
+    const int cta_linear = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+    unsigned long long* trace = kTrace ? p.trace + static_cast<size_t>(cta_linear) * 16 : nullptr;
     if (kTrace && threadIdx.x == 0) {
         trace[kTrEntryNs] = global_timer_ns();
         trace[kTrEntry] = clock64();
@@ -382,6 +391,12 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
         trace[kTrSm] = smid;
     }
 
+    // Let a programmatic dependent (the next decode launch with overlap on) start its own prologue
+    // while this grid streams; it waits for this grid's completion before it touches data.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+
+    int shared_pages = 0, t_skip = 0;
+    if constexpr (!kRows) {
     // The block tables are read right after the scan (first piece's page window): start them on
     // their way into L2 now, one 128-byte line per thread, spread over the CTAs.
     {
@@ -411,8 +426,8 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
     // Shared-prefix cascade: the first P pages of every active row were attended by the prefix
     // kernel; this kernel streams the remainder only. P pages lie entirely before token ctx-1 of
     // every active row, so the remainder is never empty.
-    const int shared_pages = p.plan != nullptr ? p.plan[0] : 0;
-    const int t_skip = shared_pages * (p.block_size / kTile);
+    shared_pages = p.plan != nullptr ? p.plan[0] : 0;
+    t_skip = shared_pages * (p.block_size / kTile);
     {
         const int per_thread = (B + kDecodeThreads - 1) / kDecodeThreads;
         const int i0 = threadIdx.x * per_thread;
@@ -451,17 +466,79 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
         if (threadIdx.x == kDecodeThreads - 1) cum[B] = base;  // all threads before + own
         __syncthreads();
     }
+    }
+    // ---- rows engine: this CTA's single piece, from its own context_lens entry ----
+    PieceDesc own{};
+    if constexpr (kRows) {
+        const int kvh = blockIdx.x, split = blockIdx.y, b = blockIdx.z;
+        const int S = p.num_splits;
+        const int ctx = p.context_lens[b];
+        const int tiles_total = ctx > 0 ? (ctx + kTile - 1) / kTile : 0;
+        // Shared-prefix cascade: the first P pages were attended by the prefix kernel.
+        const int sp = (p.plan != nullptr && ctx > 0) ? p.plan[0] : 0;
+        shared_pages = sp;
+        t_skip = sp * (p.block_size / kTile);
+        const int per_split = (tiles_total - t_skip + S - 1) / S;
+        own.b = b;
+        own.kvh = kvh;
+        own.t_begin = t_skip + split * per_split;
+        own.t_end = min(own.t_begin + per_split, tiles_total);
+        own.tiles_total = tiles_total;
+        own.range = split;
+        own.g_first = 0;
+        own.g_last = S - 1;
+        if (own.t_begin >= own.t_end) {
+            // Nothing to attend in this split (ctx == 0 padding row of a CUDA-graph batch, or a
+            // split beyond the sequence). No table entry is read.
+            if (p.overlap) grid_dependency_wait();
+            const int64_t q_row0 = static_cast<int64_t>(b) * Hq + static_cast<int64_t>(kvh) * G;
+            if (S == 1) {
+                __nv_bfloat16* out = static_cast<__nv_bfloat16*>(p.out) + q_row0 * kHeadDim;
+                for (int i = threadIdx.x; i < G * kHeadDim; i += kDecodeThreads)
+                    out[i] = __float2bfloat16(0.f);
+            } else {
+                const int slot = (b * p.num_kv_heads + kvh) * S + split;
+                if (threadIdx.x < 8) p.piece_lse[slot * 8 + threadIdx.x] = -INFINITY;
+                if (piece_arrive_is_last<kDecodeThreads, 2>(
+                        p.split_counters + b * p.num_kv_heads + kvh, S, last_flag)) {
+                    // this empty split arrived last: it merges the row group
+                    const int n_pre = sp > 0 ? prefix_chunks_of(sp, p.block_size,
+                                                                p.prefix_chunks).valid : 0;
+                    if (n_pre > 0) grid_dependency_wait();
+                    MergeSrc src;
+                    src.piece_o = p.piece_o;
+                    src.piece_lse = p.piece_lse;
+                    src.prefix_o = p.prefix_o;
+                    src.prefix_lse = p.prefix_lse;
+                    src.rows_base = (b * p.num_kv_heads + kvh) * S;
+                    src.g_first = 0;
+                    src.kvh = kvh;
+                    src.num_kv_heads = p.num_kv_heads;
+                    src.n_piece = S;
+                    src.prefix_chunks = p.prefix_chunks;
+                    src.n_prefix = n_pre;
+                    for (int h = warp; h < G; h += kConsumerWarps + 1) {
+                        src.h_local = h;
+                        src.row = q_row0 + h;
+                        merge_row(src, static_cast<__nv_bfloat16*>(p.out), lane);
+                    }
+                }
+            }
+            if (p.plan != nullptr) grid_dependency_wait();
+            return;
+        }
+        if (threadIdx.x == 0) {
+#pragma unroll
+            for (int s = 0; s < kStages; ++s) {
+                mbar_init(&full_bar[s], 1);
+                mbar_init(&empty_bar[s], kConsumerWarps);
+            }
+            fence_mbar_init();
+        }
+        __syncthreads();
+    }
     if (kTrace && threadIdx.x == 0) trace[kTrScan] = clock64();
 
-    // Padding rows of a CUDA-graph batch (ctx == 0) carry no units: their output rows are zeroed
-    // here, spread over the CTAs. No table entry of such a row is ever read.
-    for (int b = blockIdx.x; b < B; b += gridDim.x) {
-        if (cum[b + 1] == cum[b]) {
-            uint32_t* o32 = reinterpret_cast<uint32_t*>(static_cast<__nv_bfloat16*>(p.out) +
-                                                        static_cast<int64_t>(b) * Hq * kHeadDim);
-            for (int i = threadIdx.x; i < Hq * kHeadDim / 2; i += kDecodeThreads) o32[i] = 0u;
-        }
-    }
     const int n_prefix =
         shared_pages > 0 ? prefix_chunks_of(shared_pages, p.block_size, p.prefix_chunks).valid : 0;
 
@@ -471,12 +548,14 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
             tma_prefetch_desc(&k_map);
             tma_prefetch_desc(&v_map);
         }
-        int max_row_units = 0;
+        Stream st{};
+        if constexpr (!kRows) {
+            int max_row_units = 0;
 #pragma unroll
-        for (int w = 0; w < kConsumerWarps + 1; ++w)
-            max_row_units = max(max_row_units, warp_sums[8 + w]);
-        Stream st;
-        stream_init(st, cum, B, p.num_kv_heads, gridDim.x, p.tun, t_skip, max_row_units);
+            for (int w = 0; w < kConsumerWarps + 1; ++w)
+                max_row_units = max(max_row_units, warp_sums[8 + w]);
+            stream_init(st, cum, B, p.num_kv_heads, gridDim.x, p.tun, t_skip, max_row_units);
+        }
         // Work items: every CTA starts with item = its id. Static regime: it goes on with items
         // id + CTAs, ... (only when there are fewer CTAs than ranges x KV heads). Dynamic regime:
         // further items come from the atomic counter sched[0]. The number is requested two tiles
@@ -488,9 +567,9 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
         const float rcp_tpp = 1.0f / static_cast<float>(tiles_per_page);
         const uint64_t policy = l2_policy_evict_first();
         const bool with_store = p.new_key != nullptr;
-        ItemIter iter;
+        ItemIter iter{};
         int item = blockIdx.x;
-        bool item_live = item < st.total_items;
+        bool item_live = !kRows && item < st.total_items;
         if (item_live) iter.init(st, item);
         int pre_item = 0;        // lane 0: the number requested from sched[0]
         bool pre_valid = false;  // a request is outstanding (warp-uniform)
@@ -537,7 +616,20 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
             }
         };
         Piece cur, nxt;
-        bool have = next_piece(cur);
+        bool have;
+        if constexpr (kRows) {  // the one piece of this CTA; nothing is handed over
+            cur.b = own.b;
+            cur.kvh = own.kvh;
+            cur.range = own.range;
+            cur.t_begin = own.t_begin;
+            cur.t_end = own.t_end;
+            cur.tiles_total = own.tiles_total;
+            cur.first = own.t_begin == t_skip;
+            cur.last = own.t_end == own.tiles_total;
+            have = true;
+        } else {
+            have = next_piece(cur);
+        }
         if (kTrace && lane == 0) trace[kTrPiece0] = clock64();
         // block-table window of a piece: 32 pages from its first page, one entry per lane
         auto load_window = [&](const Piece& pc) {
@@ -549,10 +641,11 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
         };
         int cur_block = 0;
         ScatterPre cur_sc{};
-        if (have) {
-            cur_block = load_window(cur);
-            if (with_store && cur.last) cur_sc = scatter_prefetch(p, cur.b, cur.kvh, lane);
-        }
+        if (have) cur_block = load_window(cur);
+        // Overlap mode: up to here only step metadata was read. The new K/V rows, the cache and
+        // the scheduler counters belong to the stream order: wait for the preceding grid.
+        if (p.overlap) grid_dependency_wait();
+        if (have && with_store && cur.last) cur_sc = scatter_prefetch(p, cur.b, cur.kvh, lane);
         int it = 0;
         while (have) {
             if (with_store && cur.last) scatter_finish(p, cur_sc, cur.b, cur.kvh, lane);
@@ -570,8 +663,8 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
             for (int t = cur.t_begin; t < cur.t_end; ++t, ++it) {
                 const int stage = it % kStages;
                 const uint32_t phase = (it / kStages) & 1u;
-                if (t == request_t && iter.u >= iter.hi) request_item();
-                if (t == cur.t_end - 1) {
+                if (!kRows && t == request_t && iter.u >= iter.hi) request_item();
+                if (!kRows && t == cur.t_end - 1) {
                     // before the last tile goes out: the next piece, handed to the consumers (they
                     // take it when this tile has landed), its table window and new K/V row
                     have_next = next_piece(nxt);
@@ -629,6 +722,20 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
     }
 
     // ===================== consumers =====================
+    // Overlap mode: everything above read only step metadata (context_lens, block tables), which
+    // the caller promises is not written by the kernel right before this one. From here on the
+    // consumers read q and write out / workspace / counters: wait for the preceding grid.
+    if (p.overlap) grid_dependency_wait();
+    // Padding rows of a CUDA-graph batch (ctx == 0) carry no units: their output rows are zeroed
+    // here, spread over the CTAs. No table entry of such a row is ever read. (Rows engine: the
+    // CTAs of such a row did it above.)
+    for (int b = blockIdx.x; !kRows && b < B; b += gridDim.x) {
+        if (cum[b + 1] == cum[b]) {
+            uint32_t* o32 = reinterpret_cast<uint32_t*>(static_cast<__nv_bfloat16*>(p.out) +
+                                                        static_cast<int64_t>(b) * Hq * kHeadDim);
+            for (int i = threadIdx.x; i < Hq * kHeadDim / 2; i += kConsumerWarps * 32) o32[i] = 0u;
+        }
+    }
     const uint32_t smem_base = smem_u32(smem);
     // K A-fragment addressing (rows = tokens): lane -> row lane%16, 16-byte chunk +(lane/16)
     const uint32_t k_row = warp * 16 + (lane & 15);
@@ -657,7 +764,8 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
         d.g_last = hi.w;
         return d;
     };
-    PieceDesc pc = pop();
+    PieceDesc pc;
+    if constexpr (kRows) pc = own; else pc = pop();
     QPre qpre;
     if (pc.b >= 0) q_prefetch(p, pc.b, pc.kvh, G, lane, qpre);
     int it = 0;
@@ -703,7 +811,7 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
             } else {
                 mbar_wait(&full_bar[stage], phase);
             }
-            if (t == pc.t_end - 1) {
+            if (!kRows && t == pc.t_end - 1) {
                 // The producer pushed the next descriptor before it issued this (last) tile, so
                 // it is there now. Its q loads run under this tile and the epilogue.
                 nxt = pop();
@@ -844,7 +952,9 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
         // Final reduction: warp w owns heads w, w+4; lane owns dims 4*lane..4*lane+3 (float4
         // shared-memory reads, 8-byte bf16 / 16-byte fp32 global stores, a head row is one line).
         const int64_t q_row0 = static_cast<int64_t>(b) * Hq + static_cast<int64_t>(kvh) * G;
-        const int slot = 2 * (pc.range * p.num_kv_heads + kvh) + (first_piece ? 1 : 0);
+        const int rows_base = kRows ? (b * p.num_kv_heads + kvh) * p.num_splits : -1;
+        const int slot = kRows ? rows_base + pc.range
+                               : 2 * (pc.range * p.num_kv_heads + kvh) + (first_piece ? 1 : 0);
         for (int h = warp; h < G; h += kConsumerWarps) {
             float m = -INFINITY;
 #pragma unroll
@@ -917,8 +1027,8 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
             }
         }
         if (!whole &&
-            piece_arrive_is_last(p.split_counters + b * p.num_kv_heads + kvh,
-                                 g_last - g_first + 1, last_flag)) {
+            piece_arrive_is_last<kConsumerWarps * 32, 1>(
+                p.split_counters + b * p.num_kv_heads + kvh, g_last - g_first + 1, last_flag)) {
             // last piece of this (sequence, KV head) to finish: merge its G rows here
             if (n_prefix > 0) grid_dependency_wait();
             MergeSrc src;
@@ -926,6 +1036,7 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
             src.piece_lse = p.piece_lse;
             src.prefix_o = p.prefix_o;
             src.prefix_lse = p.prefix_lse;
+            src.rows_base = rows_base;
             src.g_first = g_first;
             src.kvh = kvh;
             src.num_kv_heads = p.num_kv_heads;
@@ -957,7 +1068,7 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
     if (p.plan != nullptr) grid_dependency_wait();
 }
 
-template <int kStages, bool kTrace>
+template <int kStages, bool kTrace, bool kRows>
 cudaError_t launch_stream(const DecodeParams& p, const CUtensorMap& k_map, const CUtensorMap& v_map,
                           cudaStream_t stream) {
     constexpr int smem = DecodeSmem<kStages>::kBytes;
@@ -966,19 +1077,21 @@ cudaError_t launch_stream(const DecodeParams& p, const CUtensorMap& k_map, const
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) dev = 0;
     if (dev < 0 || dev >= 64 || !configured[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(decode_stream_kernel<kStages, kTrace>,
+        cudaError_t e = cudaFuncSetAttribute(decode_stream_kernel<kStages, kTrace, kRows>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
         if (dev >= 0 && dev < 64) configured[dev] = true;
     }
     dim3 grid(p.num_ctas);
+    if (kRows) grid = dim3(p.num_kv_heads, p.num_splits, p.batch);
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = grid;
     cfg.blockDim = dim3(kDecodeThreads);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];
-    if (p.plan != nullptr) {
+    if (p.plan != nullptr || p.overlap) {
+        // Overlap mode: dependent of whatever kernel precedes it in the stream (see DecodeParams).
         // Programmatic dependent launch behind the prefix pass: this grid may start while the
         // prefix CTAs are still running (they signal launch_dependents at once) and only waits
         // (griddepcontrol.wait) where it consumes their partials. It touches nothing the prefix
@@ -990,7 +1103,7 @@ cudaError_t launch_stream(const DecodeParams& p, const CUtensorMap& k_map, const
         cfg.numAttrs = 1;
     }
     cudaError_t e =
-        cudaLaunchKernelEx(&cfg, decode_stream_kernel<kStages, kTrace>, k_map, v_map, p);
+        cudaLaunchKernelEx(&cfg, decode_stream_kernel<kStages, kTrace, kRows>, k_map, v_map, p);
     count_launch();
     return e != cudaSuccess ? e : cudaGetLastError();
 }
@@ -1004,7 +1117,7 @@ int env_int(const char* name, int dflt, int lo, int hi) {
 
 int decode_stages_from_env() {
     static int stages = [] {
-        const int s = env_int("B200ATTN_DECODE_STAGES", 3, 2, 6);
+        const int s = env_int("B200ATTN_DECODE_STAGES", 3, 2, 3);
         return s;
     }();
     return stages;
@@ -1044,16 +1157,33 @@ int decode_static_pct() {
     return v;
 }
 
+bool decode_engine_rows() {
+    static const bool rows = [] {
+        const char* e = std::getenv("B200ATTN_DECODE_ENGINE");
+        return !(e && e[0] == 's');  // "stream" selects the persistent engine
+    }();
+    return rows;
+}
+
 // Slot pairs of the piece region: one per work item (range, KV head) of the STATIC regime (the
 // dynamic regime never cuts a row, so it writes no partials): ranges * Hkv <= max(ctas, Hkv).
 static size_t piece_pairs(int32_t num_q_heads, int32_t num_ctas) {
     return static_cast<size_t>(num_ctas) + static_cast<size_t>(num_q_heads);
 }
 
+// Partial-piece slots ([8 heads][128] fp32 O + [8] lse each). Stream engine: two per work item
+// that can hold a cut row. Rows engine: one per (sequence, KV head, split); the KV-head count is
+// not an argument of the ABI's size query, so the bound num_q_heads >= num_kv_heads is used.
+static size_t piece_slots(int32_t batch, int32_t num_q_heads, int32_t num_splits) {
+    if (decode_engine_rows())
+        return static_cast<size_t>(batch) * num_q_heads * num_splits;
+    return piece_pairs(num_q_heads, num_splits) * 2;
+}
+
 size_t decode_workspace_bytes(int32_t batch, int32_t num_q_heads, int32_t num_ctas,
                               int32_t prefix_chunks) {
     size_t floats = 0;
-    if (num_ctas > 1) floats += piece_pairs(num_q_heads, num_ctas) * 2 * 8 * (kHeadDim + 1);
+    if (num_ctas > 1) floats += piece_slots(batch, num_q_heads, num_ctas) * 8 * (kHeadDim + 1);
     floats = (floats + 3) & ~static_cast<size_t>(3);  // keep the prefix region 16-byte aligned
     if (prefix_chunks > 0)
         floats += static_cast<size_t>(batch) * num_q_heads * prefix_chunks * (kHeadDim + 1);
@@ -1065,10 +1195,10 @@ void decode_workspace_layout(void* workspace, int32_t batch, int32_t num_q_heads
     float* w = static_cast<float*>(workspace);
     size_t at = 0;
     if (num_ctas > 1) {
-        const size_t pairs = piece_pairs(num_q_heads, num_ctas);
+        const size_t slots = piece_slots(batch, num_q_heads, num_ctas);
         p->piece_o = w;
-        p->piece_lse = w + pairs * 2 * 8 * kHeadDim;
-        at = pairs * 2 * 8 * (kHeadDim + 1);
+        p->piece_lse = w + slots * 8 * kHeadDim;
+        at = slots * 8 * (kHeadDim + 1);
     }
     at = (at + 3) & ~static_cast<size_t>(3);
     if (prefix_chunks > 0) {
@@ -1078,8 +1208,27 @@ void decode_workspace_layout(void* workspace, int32_t batch, int32_t num_q_heads
     }
 }
 
+// Rows engine: equal pieces per row, from host-visible sizes only (graph-capture rule).
+// Calibrated on B200 (profiles/r01_sweep_splits.log): one streaming CTA per SM already saturates
+// HBM, so splitting only pays while (sequence, KV head) rows are fewer than ~0.7 x SMs; then aim
+// for about one CTA per SM and never cut the longest possible context into pieces shorter than 8
+// tiles (512 tokens) - below that the partials + merge cost more than they hide.
+static int decode_pick_row_splits(int32_t batch, int32_t num_kv_heads, int32_t table_width,
+                                  int32_t block_size, int32_t sm_count) {
+    const int64_t base = static_cast<int64_t>(batch) * num_kv_heads;
+    if (base <= 0 || base * 10 >= static_cast<int64_t>(sm_count) * 7) return 1;
+    const int64_t max_tiles = static_cast<int64_t>(table_width) * block_size / kTile;
+    int64_t s = (sm_count + base / 2) / base;  // round(sm_count / base)
+    const int64_t cap = max_tiles / 8 > 1 ? max_tiles / 8 : 1;
+    if (s > cap) s = cap;
+    if (s > 64) s = 64;
+    return static_cast<int>(s < 1 ? 1 : s);
+}
+
 int decode_pick_ctas(int32_t batch, int32_t num_kv_heads, int32_t table_width, int32_t block_size,
                      int32_t sm_count) {
+    if (decode_engine_rows())
+        return decode_pick_row_splits(batch, num_kv_heads, table_width, block_size, sm_count);
     // Host-visible sizes only (graph-capture rule): two resident CTAs per SM, fewer when even the
     // longest contexts the table can describe would leave CTAs with less than min_units of work;
     // a multiple of the KV-head count (CTAs = groups x head lanes). How the work is cut is decided
@@ -1167,12 +1316,17 @@ int decode_partition_host(const int32_t* context_lens, int32_t batch, int32_t nu
 cudaError_t launch_decode(const DecodeParams& p, const CUtensorMap& k_map, const CUtensorMap& v_map,
                           cudaStream_t stream) {
     if (p.batch == 0) return cudaSuccess;
-    if (p.trace != nullptr) return launch_stream<3, true>(p, k_map, v_map, stream);
+    if (decode_engine_rows()) {
+        if (p.trace != nullptr) return launch_stream<3, true, true>(p, k_map, v_map, stream);
+        switch (decode_stages_from_env()) {
+            case 2: return launch_stream<2, false, true>(p, k_map, v_map, stream);
+            default: return launch_stream<3, false, true>(p, k_map, v_map, stream);
+        }
+    }
+    if (p.trace != nullptr) return launch_stream<3, true, false>(p, k_map, v_map, stream);
     switch (decode_stages_from_env()) {
-        case 2: return launch_stream<2, false>(p, k_map, v_map, stream);
-        case 4: return launch_stream<4, false>(p, k_map, v_map, stream);
-        case 6: return launch_stream<6, false>(p, k_map, v_map, stream);
-        default: return launch_stream<3, false>(p, k_map, v_map, stream);
+        case 2: return launch_stream<2, false, false>(p, k_map, v_map, stream);
+        default: return launch_stream<3, false, false>(p, k_map, v_map, stream);
     }
 }
 

@@ -25,6 +25,11 @@ The reference binds the op by name: `from nanovllm.layers.attention import Atten
      fast_rpc: rank 0 ships a compact int32 record per step instead of pickled Sequence objects,
      in a block sized from the engine's limits; `run` loses the debug f-string that dereferences
      `logits` on ranks > 0 (the unmodified reference cannot take a step at TP > 1).
+  7. switches the decode launches to overlap mode (attention.set_decode_overlap; B200ATTN_DECODE_
+     OVERLAP=0 keeps it off): each decode launch is a programmatic dependent of the kernel before
+     it and runs its prologue while that kernel drains. Valid here because the engine writes
+     context_lens / block_tables once per step (model_runner.py:206-226), never right before an
+     attention call.
 For tensor parallel runs nanovllm spawns ranks with multiprocessing "spawn"
 (engine/llm_engine.py:24-31): call install() at module top level of the launcher script so each
 spawned rank re-applies it on import of __main__.
@@ -96,6 +101,7 @@ def install(verbose: bool = False, fuse_qkv: bool | None = None,
             rpc.bind(mr)
         else:
             fast_rpc = False
+    ours.set_decode_overlap(os.environ.get("B200ATTN_DECODE_OVERLAP", "1") != "0")
     if verbose:
         print("[byox_vllm_b200] nanovllm.layers.attention -> byox_vllm_b200.attention"
               + (" (+ fused qkv path)" if fuse_qkv else "")
@@ -109,6 +115,7 @@ def uninstall() -> None:
     from . import context as own
 
     ours.get_context = own.get_context
+    ours.set_decode_overlap(False)
     global _ORIG_QWEN3_FORWARD
     qwen3 = sys.modules.get("nanovllm.models.qwen3")
     if qwen3 is not None and _ORIG_QWEN3_FORWARD is not None and hasattr(qwen3, "Qwen3Attention"):

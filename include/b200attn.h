@@ -120,6 +120,21 @@ int b200attn_decode_partition_host(const int32_t* context_lens, int32_t batch,
                                    int32_t num_kv_heads, int32_t num_splits, int32_t shared_pages,
                                    int32_t block_size, int32_t* pieces, int32_t max_pieces);
 
+/*
+ * Overlap mode of the decode entry points (process-wide switch, off by default; returns the
+ * previous setting). When on, a decode launch is a programmatic dependent (PDL) of the kernel that
+ * precedes it in the stream: the kernel's prologue - the scan of context_lens, its first work item
+ * and that item's block-table window - runs while the preceding kernel drains, and
+ * griddepcontrol.wait comes before q, the new K/V rows and the cache are read and before anything
+ * is written. THE CALLER PROMISES that context_lens and block_tables are not written by the kernel
+ * immediately before the decode launch in the stream (in nanovllm they are written once per step,
+ * model_runner.py:206-226, many kernels earlier; byox_vllm_b200.install() switches overlap on).
+ * Ignored for launches with a cascade plan (those are dependents of the shared-prefix pass).
+ * Every decode launch also signals launch_dependents at its start, so consecutive decode launches
+ * (one per layer) overlap tail and prologue.
+ */
+int b200attn_set_decode_overlap(int on);
+
 /* Debug only: with a device buffer of 16 uint64 per CTA registered, the decode entry points launch
  * an instrumented build of the kernel that stamps its phases there (tools/trace_decode.py);
  * NULL (the default) restores the product kernel. Not thread-safe, not for production. */

@@ -332,3 +332,77 @@ def test_fused_store_with_foreign_slot_mapping(cuda_dev):
     orc.store_kvcache_ref(c.k, c.v, kc_ref, vc_ref, foreign.cpu())
     assert torch.equal(d["k_cache"].cpu().view(torch.int16), kc_ref.view(torch.int16))
     assert torch.equal(d["v_cache"].cpu().view(torch.int16), vc_ref.view(torch.int16))
+
+
+@pytest.mark.parametrize("shape", [(24, [300, 1, 700, 256, 513, 90] * 4, 16, 8),      # whole rows
+                                   (2, [9000, 5000], 32, 8),                            # cut rows
+                                   (40, None, 4, 1)], ids=["rows", "cut", "ragged"])
+def test_overlap_mode_back_to_back(cuda_dev, shape):
+    """Overlap mode (b200attn_set_decode_overlap): every decode launch is a programmatic dependent
+    of the kernel before it and starts its prologue while that kernel still runs. The data it
+    reads after griddepcontrol.wait - q here, rewritten by a copy kernel right before each launch -
+    must be the new data, and consecutive launches share counters and workspace. Ten launches
+    back to back, eagerly and from one CUDA graph, against the same calls with overlap off."""
+    from byox_vllm_b200.attention import paged_decode, set_decode_overlap
+
+    B, ctx, Hq, Hkv = shape
+    if ctx is None:
+        rng = np.random.default_rng(5)
+        ctx = rng.integers(1, 3000, size=B).tolist()
+    c = synth.decode_case(B, ctx, Hq, Hkv, seed=77)
+    d = to_dev(c, cuda_dev)
+    m = d["meta"]
+    g = torch.Generator(device=cuda_dev).manual_seed(3)
+    qs = [torch.empty_like(d["q"]).normal_(generator=g) for _ in range(10)]
+    q = torch.empty_like(d["q"])
+
+    def run_all(outs):
+        for i in range(10):
+            q.copy_(qs[i])  # a kernel that writes q immediately before the dependent launch
+            paged_decode(q, d["k_cache"], d["v_cache"], m["context_lens"], m["block_tables"],
+                         c.scale, out=outs[i])
+
+    want = [torch.empty_like(q) for _ in range(10)]
+    prev = set_decode_overlap(False)
+    try:
+        run_all(want)
+        torch.cuda.synchronize()
+        assert_close(want[3], orc.paged_decode_ref(qs[3].cpu(), c.k_cache, c.v_cache,
+                                                   c.meta["context_lens"], c.meta["block_tables"],
+                                                   c.scale), "overlap off vs oracle")
+        set_decode_overlap(True)
+        got = [torch.zeros_like(q) for _ in range(10)]
+        run_all(got)
+        torch.cuda.synchronize()
+        for i in range(10):
+            assert torch.equal(got[i], want[i]), f"eager launch {i} differs with overlap on"
+        got = [torch.zeros_like(q) for _ in range(10)]
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            run_all(got)
+        for _ in range(3):
+            graph.replay()
+        torch.cuda.synchronize()
+        for i in range(10):
+            assert torch.equal(got[i], want[i]), f"graph launch {i} differs with overlap on"
+    finally:
+        set_decode_overlap(prev)
+
+
+def test_stream_engine_passes_the_decode_and_cascade_tests():
+    """The persistent stream engine (B200ATTN_DECODE_ENGINE=stream; the engine is read once per
+    process) against the same parity tests as the default rows engine."""
+    import os
+    import subprocess
+    import sys
+
+    if os.environ.get("B200ATTN_DECODE_ENGINE", "rows").startswith("s"):
+        pytest.skip("already the stream engine")
+    here = os.path.dirname(os.path.abspath(__file__))
+    env = dict(os.environ, B200ATTN_DECODE_ENGINE="stream")
+    r = subprocess.run([sys.executable, "-m", "pytest", "-x", "-q", "-m", "gpu",
+                        os.path.join(here, "test_gpu_decode.py"),
+                        os.path.join(here, "test_gpu_cascade.py"),
+                        os.path.join(here, "test_gpu_qkv_fused.py")],
+                       env=env, capture_output=True, text=True, timeout=1500)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]

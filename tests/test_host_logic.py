@@ -1,6 +1,8 @@
 """Host-side logic that needs no GPU: argument validation of the C-ABI (errors are returned
 before any CUDA call), the split heuristic, the module surface and the install shim."""
 import importlib
+import os
+import subprocess
 import sys
 import textwrap
 
@@ -15,40 +17,80 @@ def lib(built_lib):
     return _lib.load()
 
 
+STREAM = os.environ.get("B200ATTN_DECODE_ENGINE", "rows").startswith("s")
+
+
 def test_pick_splits_is_host_only_and_sane(lib):
-    """num_splits = persistent CTAs of the decode kernel: two per SM, fewer when even full tables
-    could not give every CTA its minimum range (16 units by default, 1 unit per row of overhead)
-    - but never fewer than one per (sequence, KV head) row while the rows fit.
-    How the work is cut is decided on the device (tests/test_decode_partition.py)."""
+    """Rows engine (default): num_splits = equal pieces per (sequence, KV head) row. Big batches
+    never split; tiny batches with long tables split towards one CTA per SM; pieces never shorter
+    than 512 tokens of the longest possible context. Stream engine (B200ATTN_DECODE_ENGINE=stream,
+    run by test_stream_engine_host_logic below): num_splits = persistent CTAs, two per SM, fewer
+    when even full tables could not give every CTA its minimum range (16 units), but never fewer
+    than one per row while the rows fit; the cut is decided on the device
+    (tests/test_decode_partition.py)."""
     sm = 148
-    assert lib.b200attn_decode_pick_splits(512, 8, 4, 256, sm) == 2 * sm
-    assert lib.b200attn_decode_pick_splits(128, 8, 16, 256, sm) == 2 * sm
-    assert lib.b200attn_decode_pick_splits(256, 1, 16, 256, sm) == 2 * sm  # TP=8 rank of config 2
-    assert lib.b200attn_decode_pick_splits(1, 8, 512, 256, sm) == 2 * sm   # one long sequence
-    # one page per row, one row per KV head: 8 rows x (4 tiles + 1) = 40 units -> one CTA per row
-    assert lib.b200attn_decode_pick_splits(1, 8, 1, 256, sm) == 8   # never fewer CTAs than rows
-    assert lib.b200attn_decode_pick_splits(1, 8, 8, 256, sm) == 16  # multiples of Hkv beyond
-    assert lib.b200attn_decode_pick_splits(1, 1, 1, 256, sm) == 1
+    pick = lib.b200attn_decode_pick_splits
+    assert pick(4, 8, 16, 256, 0) >= 1  # unknown SM count -> 148
+    assert pick(0, 8, 16, 256, sm) == 1
+    if STREAM:
+        assert pick(512, 8, 4, 256, sm) == 2 * sm
+        assert pick(128, 8, 16, 256, sm) == 2 * sm
+        assert pick(256, 1, 16, 256, sm) == 2 * sm  # TP=8 rank of config 2
+        assert pick(1, 8, 512, 256, sm) == 2 * sm   # one long sequence
+        assert pick(1, 8, 1, 256, sm) == 8          # never fewer CTAs than rows
+        assert pick(1, 8, 8, 256, sm) == 16         # multiples of Hkv beyond
+        assert pick(1, 1, 1, 256, sm) == 1
+        for b in (1, 2, 4, 8, 16, 64):
+            for w in (1, 4, 16, 128):
+                s = pick(b, 1, w, 256, sm)
+                assert 1 <= s <= 2 * sm
+                assert s <= max(b, -(-b * (4 * w + 1) // 16))
+        return
+    assert pick(512, 8, 4, 256, sm) == 1
+    assert pick(128, 8, 16, 256, sm) == 1
+    assert 16 <= pick(1, 8, 512, 256, sm) <= 128
+    assert pick(1, 8, 1, 256, sm) == 1
     for b in (1, 2, 4, 8, 16, 64):
         for w in (1, 4, 16, 128):
-            s = lib.b200attn_decode_pick_splits(b, 1, w, 256, sm)
-            assert 1 <= s <= 2 * sm
-            assert s <= max(b, -(-b * (4 * w + 1) // 16))
-    assert lib.b200attn_decode_pick_splits(4, 8, 16, 256, 0) >= 1  # unknown SM count -> 148
-    assert lib.b200attn_decode_pick_splits(0, 8, 16, 256, sm) == 1
+            assert 1 <= pick(b, 1, w, 256, sm) <= max(1, w)
+    # calibration points of tools/sweep_splits.py (profiles/r01_sweep_splits.log): about one CTA
+    # per SM, no split once (sequence, KV head) rows reach ~0.7 x SMs, pieces >= 512 tokens
+    assert pick(16, 8, 16, 256, sm) == 1
+    assert pick(128, 1, 16, 256, sm) == 1
+    assert pick(8, 8, 64, 256, sm) == 2
+    assert pick(4, 8, 16, 256, sm) == 5
+    assert pick(1, 8, 16, 256, sm) == 8
+    assert pick(1, 8, 512, 256, sm) in (18, 19)
 
 
 def test_workspace_bytes(lib):
     slot = 8 * (128 + 1) * 4  # one partial piece: [8 heads][128] fp32 O + [8] lse
-    # two slots per work item that can hold a cut row (static regime: <= num_splits + num_q_heads
-    # items); not per row of the batch
-    assert lib.b200attn_decode_workspace_bytes(4, 16, 128, 1, 0) == 0
-    assert lib.b200attn_decode_workspace_bytes(4, 16, 128, 3, 0) == (3 + 16) * 2 * slot
-    assert lib.b200attn_decode_workspace_bytes(400, 16, 128, 296, 0) == (296 + 16) * 2 * slot
+    ws = lib.b200attn_decode_workspace_bytes
     pre = 4 * 16 * 5 * (128 + 1) * 4
-    assert lib.b200attn_decode_workspace_bytes(4, 16, 128, 1, 5) == pre
-    assert lib.b200attn_decode_workspace_bytes(4, 16, 128, 3, 5) == (3 + 16) * 2 * slot + pre
-    assert lib.b200attn_decode_workspace_bytes(4, 16, 64, 3, 0) == 0  # unsupported head_dim
+    assert ws(4, 16, 128, 1, 0) == 0
+    assert ws(4, 16, 128, 1, 5) == pre
+    assert ws(4, 16, 64, 3, 0) == 0  # unsupported head_dim
+    if STREAM:
+        # two slots per work item that can hold a cut row (<= num_splits + num_q_heads items)
+        assert ws(4, 16, 128, 3, 0) == (3 + 16) * 2 * slot
+        assert ws(400, 16, 128, 296, 0) == (296 + 16) * 2 * slot
+        assert ws(4, 16, 128, 3, 5) == (3 + 16) * 2 * slot + pre
+    else:
+        # one slot per (sequence, KV head, split), KV heads bounded by the q heads
+        assert ws(4, 16, 128, 3, 0) == 4 * 16 * 3 * slot
+        assert ws(4, 16, 128, 3, 5) == 4 * 16 * 3 * slot + pre
+
+
+def test_stream_engine_host_logic():
+    """The same host-logic and partition tests with the persistent stream engine selected (the
+    engine is read once per process)."""
+    if STREAM:
+        pytest.skip("already the stream engine")
+    env = dict(os.environ, B200ATTN_DECODE_ENGINE="stream")
+    r = subprocess.run([sys.executable, "-m", "pytest", "-x", "-q", "-m", "not gpu", __file__,
+                        "-k", "pick_splits or workspace_bytes"], env=env, capture_output=True,
+                       text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
 
 
 def test_argument_errors_have_codes_and_messages(lib):

@@ -47,7 +47,10 @@ def child():
     res = []
     with torch.inference_mode():
         for (B, ctx, Hq, Hkv) in SHAPES:
-            r = bench.extra_decode("sweep", B, ctx, Hq, Hkv, ref=False)
+            kw = {}
+            if os.environ.get("B200_OVERLAP") in ("0", "1") and not os.environ.get("B200_AB_PKG"):
+                kw["overlap"] = os.environ["B200_OVERLAP"] == "1"
+            r = bench.extra_decode("sweep", B, ctx, Hq, Hkv, ref=False, **kw)
             res.append(dict(B=B, ctx=ctx, Hq=Hq, Hkv=Hkv, ctas=r["decode_ctas"],
                             us=r["ms_per_launch"] * 1e3, gbs=r["achieved"], frac=r["frac"]))
     print("RESULT " + json.dumps(res), flush=True)
