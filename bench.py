@@ -259,6 +259,11 @@ def run_ours(args, w, rank, world, dev):
     from tools import metadata_ref as md
 
     lib = _lib.load()
+    # as under install(): decode launches are programmatic dependents of the kernel before them
+    # (metadata is written once per step, never right before an attention call)
+    from byox_vllm_b200.attention import set_decode_overlap
+
+    set_decode_overlap(os.environ.get("B200_BENCH_OVERLAP", "1") != "0")
     shard = parallel.shard_heads(w["Hq"], w["Hkv"], world, rank)
     Hq, Hkv, L = shard.num_q_heads, shard.num_kv_heads, w["layers"]
     lens = context_lengths(w)
@@ -389,7 +394,9 @@ def run_ours(args, w, rank, world, dev):
                         f"{w['Hq']}/{w['Hkv']} over TP={world} -> {Hq}/{Hkv} per rank, "
                         f"block_size {BLOCK}, CUDA graph replay",
             "l2": f"inputs larger than L2: {alg * L / 1e9:.2f} GB of KV streamed per step",
-            "parallelism": f"tp{world}", "decode_ctas": int(n_ctas),
+            "parallelism": f"tp{world}", "decode_splits": int(n_ctas),
+            "decode_engine": os.environ.get("B200ATTN_DECODE_ENGINE", "rows"),
+            "decode_overlap": os.environ.get("B200_BENCH_OVERLAP", "1") != "0",
         },
         "roofline": {
             "bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
@@ -397,8 +404,8 @@ def run_ours(args, w, rank, world, dev):
             "traffic_source": (f"committed ncu --set full capture ({traffic_src}), not "
                                f"re-measured by this run") if traffic is not None else None,
             "peak_kind": pk_kind,
-            "kernel": "decode_stream_kernel (persistent, in-launch merge), graph replay of one "
-                      "launch per layer",
+            "kernel": "decode_stream_kernel<rows engine> (CTA per KV head x split x sequence, "
+                      "in-launch merge), graph replay of one launch per layer",
             "algorithmic_bytes_per_launch": alg, "ms_per_launch": ms_kernel,
             "frac_of_8TBs_nominal": achieved / 8000.0,
         },

@@ -30,6 +30,7 @@ when world_size > 1). Pure host code: no CUDA, no torch tensors on the wire.
 from __future__ import annotations
 
 import pickle
+import time
 from itertools import chain
 
 import numpy as np
@@ -204,13 +205,15 @@ def read_call(buf, block_size: int):
 
 # ---- ModelRunner drop-ins (bound by install.install(fast_rpc=True)) -------------------------------
 _ORIG: dict = {}
-_STATS = {"steps": 0, "bytes": 0}
+_STATS = {"steps": 0, "bytes": 0, "host_s": 0.0}
 
 
 def _write_shm(self, method_name, *args):
     """ModelRunner._write_shm (model_runner.py:93-100) with the compact wire format."""
     assert self.world_size > 1 and self.rank == 0
+    t0 = time.perf_counter()
     used = write_call(self.shm.buf, method_name, args)
+    _STATS["host_s"] += time.perf_counter() - t0
     _STATS["steps"] += 1
     _STATS["bytes"] += used
     for event in self.event:
@@ -326,5 +329,6 @@ def unbind(mr_module) -> None:
 
 
 def stats() -> dict:
-    """Calls written by this process (rank 0) and their total bytes: per-step RPC size."""
+    """Calls written by this process (rank 0), their total bytes and the host seconds spent
+    serialising them: per-step RPC size and cost."""
     return dict(_STATS)

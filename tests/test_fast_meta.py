@@ -1,6 +1,8 @@
 """device-side decode metadata. CPU part: the host packing; GPU part: the kernel
-against the restated builders (byox_vllm_b200.metadata, pinned by the reference's own expectations
-in tests/test_prepare_funcs.py:83-143,169-206 — see tests/test_metadata.py) — bit-exact."""
+against the restated builders (tools/metadata_ref.py, pinned by the reference's own expectations
+in tests/test_prepare_funcs.py:83-143,169-206 — see tests/test_metadata.py) and against the
+reference's OWN ModelRunner._prepare_decode / _prepare_prefill (baseline/_ref, through
+ModelRunner.__new__) — bit-exact."""
 import random
 
 import numpy as np
@@ -199,3 +201,147 @@ def test_prepare_prefill_block256_batches(cuda_dev):
     _check_prefill(cuda_dev, [S(16384, [rng.randrange(1 << 20) for _ in range(64)])], 256)
     many = [S(rng.randint(1, 40), [rng.randrange(1 << 20)]) for _ in range(1024)]
     _check_prefill(cuda_dev, many, 256)
+
+
+# ---- against the reference's OWN builders (baseline/_ref, unmodified) --------------------------------
+def _reference_runner():
+    """ModelRunner.__new__ (no __init__: no process group, no model): the reference's
+    _prepare_decode / _prepare_prefill need only `block_size` (model_runner.py:152-226)."""
+    import sys
+    from pathlib import Path
+
+    ref = Path(__file__).resolve().parents[1] / "baseline" / "_ref"
+    if not (ref / "nanovllm").is_dir():
+        pytest.skip("baseline/_ref (the installed reference) is not present")
+    if str(ref) not in sys.path:
+        sys.path.insert(0, str(ref))
+    from byox_vllm_b200 import install
+
+    # only the attention module is swapped (so that flash_attn / triton are not needed to import
+    # the engine); the reference's builders stay as they are
+    install.install(fuse_qkv=False, fast_meta=False, fast_rpc=False)
+    from nanovllm.engine.model_runner import ModelRunner
+    from nanovllm.engine.sequence import Sequence
+    from nanovllm.utils.context import get_context, reset_context
+
+    return ModelRunner, Sequence, get_context, reset_context, install
+
+
+def _ref_seq(Sequence, rng, n, block_size, cached_blocks=0):
+    s = Sequence([rng.randrange(30000) for _ in range(n)], block_size)
+    s.block_table = [rng.randrange(1 << 20) for _ in range(s.num_blocks)]
+    s.num_cached_tokens = cached_blocks * block_size
+    return s
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("block_size", [16, 256])
+def test_device_builders_match_reference_model_runner(cuda_dev, block_size):
+    """The decode and prefill metadata built on the device (fast_meta stagers, one copy + one
+    launch) against what the reference's own ModelRunner._prepare_decode / _prepare_prefill put
+    into the Context for the same Sequence objects: bit-exact, field by field."""
+    ModelRunner, Sequence, get_context, reset_context, install = _reference_runner()
+    try:
+        runner = ModelRunner.__new__(ModelRunner)
+        runner.block_size = block_size
+        rng = random.Random(block_size)
+        for B in (1, 3, 17, 64):
+            seqs = [_ref_seq(Sequence, rng, rng.randint(1, 40 * block_size), block_size)
+                    for _ in range(B)]
+            ids_r, pos_r = ModelRunner._prepare_decode(runner, seqs)
+            ctx = get_context()
+            W = ctx.block_tables.size(1)
+            cap = B + 5
+            gv = [torch.full((cap,), 99, dtype=torch.int64, device=cuda_dev),
+                  torch.full((cap,), 99, dtype=torch.int64, device=cuda_dev),
+                  torch.full((cap,), 99, dtype=torch.int32, device=cuda_dev),
+                  torch.full((cap,), 99, dtype=torch.int32, device=cuda_dev),
+                  torch.full((cap, W + 3), 99, dtype=torch.int32, device=cuda_dev)]
+            st = fm.DecodeMetaStager(*gv, block_size)
+            b, w = st.stage([s.last_token for s in seqs], [s.num_tokens for s in seqs],
+                            [s.block_table for s in seqs])
+            torch.cuda.synchronize()
+            assert (b, w) == (B, W)
+            assert torch.equal(gv[0][:B], ids_r) and torch.equal(gv[1][:B], pos_r)
+            assert torch.equal(gv[2][:B], ctx.slot_mapping)
+            assert torch.equal(gv[3][:B], ctx.context_lens)
+            assert torch.equal(gv[4][:B, :W], ctx.block_tables)
+            reset_context()
+        for B in (1, 4, 23):
+            seqs = []
+            for _ in range(B):
+                n = rng.randint(1, 12 * block_size)
+                seqs.append(_ref_seq(Sequence, rng, n, block_size,
+                                     cached_blocks=rng.randint(0, (n - 1) // block_size)))
+            ids_r, pos_r = ModelRunner._prepare_prefill(runner, seqs)
+            ctx = get_context()
+            pst = fm.PrefillMetaStager(cuda_dev, block_size)
+            pos, slot, cu_q, cu_k = pst.stage([s.num_tokens for s in seqs],
+                                              [s.num_cached_tokens for s in seqs],
+                                              [s.block_table for s in seqs])
+            torch.cuda.synchronize()
+            assert torch.equal(pos, pos_r)
+            assert torch.equal(slot, ctx.slot_mapping)
+            assert torch.equal(cu_q, ctx.cu_seqlens_q) and torch.equal(cu_k, ctx.cu_seqlens_k)
+            assert ids_r.tolist() == [t for s in seqs for t in s[s.num_cached_tokens:]]
+            reset_context()
+    finally:
+        install.uninstall()
+
+
+@pytest.mark.gpu
+def test_bound_drop_ins_on_reference_model_runner(cuda_dev):
+    """install(fast_meta=True) rebinds ModelRunner._prepare_decode / _run_model; on a runner with
+    graph buffers (ModelRunner.__new__ + the attributes _capture_cudagraph would set) a decode step
+    fills the graph inputs with exactly what the reference's own builder + refresh copies
+    (model_runner.py:206-254) would have put there, and replays the graph."""
+    ModelRunner, Sequence, get_context, reset_context, install = _reference_runner()
+    install.uninstall()
+    install.install(fuse_qkv=False, fast_meta=True, fast_rpc=False)
+    try:
+        from nanovllm.engine.model_runner import ModelRunner as MR
+
+        assert MR._prepare_decode is fm.prepare_decode and MR._run_model is fm.run_model
+        orig_prepare = fm._ORIG["_prepare_decode"]
+        cap, width, bs = 16, 12, 256
+        dev = cuda_dev
+        gv = dict(input_ids=torch.zeros(cap, dtype=torch.int64, device=dev),
+                  positions=torch.zeros(cap, dtype=torch.int64, device=dev),
+                  slot_mapping=torch.zeros(cap, dtype=torch.int32, device=dev),
+                  context_lens=torch.zeros(cap, dtype=torch.int32, device=dev),
+                  block_tables=torch.zeros(cap, width, dtype=torch.int32, device=dev),
+                  outputs=torch.arange(cap, dtype=torch.float32, device=dev).view(cap, 1))
+        replays = []
+
+        class Graph:
+            def replay(self):
+                replays.append({k: v.clone() for k, v in gv.items()})
+
+        runner = MR.__new__(MR)
+        runner.block_size, runner.enforce_eager, runner.rank, runner.world_size = bs, False, 0, 1
+        runner.graph_vars, runner.graph_bs = gv, [1, 2, 4, 8, 16]
+        runner.graphs = {b: Graph() for b in runner.graph_bs}
+        runner.model = type("M", (), {"compute_logits": staticmethod(lambda x: x)})()
+        rng = random.Random(9)
+        for B in (3, 8, 1, 11):
+            seqs = [_ref_seq(Sequence, rng, rng.randint(1, 10 * bs), bs) for _ in range(B)]
+            ids, pos = MR._prepare_decode(runner, seqs)
+            out = MR._run_model(runner, ids, pos, False)
+            torch.cuda.synchronize()
+            assert out.shape == (B, 1)
+            seen = replays[-1]
+            # the reference's own path for the same sequences
+            ids_r, pos_r = orig_prepare(runner, seqs)
+            ctx = get_context()
+            W = ctx.block_tables.size(1)
+            assert torch.equal(seen["input_ids"][:B], ids_r)
+            assert torch.equal(seen["positions"][:B], pos_r)
+            assert torch.equal(seen["slot_mapping"][:B], ctx.slot_mapping)
+            assert bool((seen["slot_mapping"][B:] == -1).all())
+            assert torch.equal(seen["context_lens"][:B], ctx.context_lens)
+            assert bool((seen["context_lens"][B:] == 0).all())
+            assert torch.equal(seen["block_tables"][:B, :W], ctx.block_tables)
+            reset_context()
+        assert len(replays) == 4
+    finally:
+        install.uninstall()

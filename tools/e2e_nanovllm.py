@@ -34,6 +34,10 @@ sys.path.insert(0, str(ROOT / "baseline" / "_ref"))
 os.environ.setdefault("TOKENIZERS_PARALLELISM", "false")
 
 MODELS = {
+    # two layers of the 0.6B geometry with a small vocabulary: engine-level parity tests
+    "tiny": dict(hidden_size=1024, num_hidden_layers=2, num_attention_heads=16,
+                 num_key_value_heads=8, intermediate_size=3072, tie_word_embeddings=True,
+                 vocab_size=32000),
     "0.6b": dict(hidden_size=1024, num_hidden_layers=28, num_attention_heads=16,
                  num_key_value_heads=8, intermediate_size=3072, tie_word_embeddings=True),
     "8b": dict(hidden_size=4096, num_hidden_layers=36, num_attention_heads=32,
@@ -50,7 +54,10 @@ def make_model_dir(name: str) -> str:
                hidden_act="silu", vocab_size=151936, max_position_embeddings=40960,
                rms_norm_eps=1e-6, rope_theta=1000000, attention_bias=False,
                torch_dtype="bfloat16", dtype="bfloat16", bos_token_id=151643,
-               eos_token_id=151645, **MODELS[name])
+               eos_token_id=151645)
+    cfg.update(MODELS[name])
+    if cfg["vocab_size"] < 151936:
+        cfg.update(bos_token_id=1, eos_token_id=2)
     (d / "config.json").write_text(json.dumps(cfg))
     if not (d / "tokenizer.json").exists():
         from tokenizers import Tokenizer, models, pre_tokenizers
@@ -68,7 +75,9 @@ def make_model_dir(name: str) -> str:
 
 
 def patch_reference(impl: str) -> None:
-    """Harness shims applied identically to both arms, plus the drop-in for `ours`."""
+    """Harness shims (synthetic weights, rope_scaling dict) applied identically to both arms, the
+    drop-in for `ours`, and - for the reference arm only - the tensor-parallel transport fixes the
+    unmodified reference needs to take a step at TP > 1 (ours: byox_vllm_b200.fast_rpc)."""
     if impl == "ours":
         from byox_vllm_b200 import install
 
@@ -98,10 +107,14 @@ def patch_reference(impl: str) -> None:
                 p.data.normal_(0.0, 0.02, generator=g)
 
     mr.load_model = seeded_load_model
+    if impl == "ours" and os.environ.get("B200ATTN_FAST_RPC", "1") != "0":
+        # install(fast_rpc=True) has replaced the transport (compact per-step records in a block
+        # sized from the engine limits) and ModelRunner.run: no harness shim on this arm.
+        return
 
     # TP control plane: the reference pickles whole Sequences (all token ids) into
-    # a 1 MiB shared-memory block every step, which overflows at the BASELINE batch sizes. Both
-    # arms get the same two harness fixes: a larger block, and decode steps ship token-free copies
+    # a 1 MiB shared-memory block every step, which overflows at the BASELINE batch sizes. The
+    # reference arm gets two harness fixes: a larger block, and decode steps ship token-free copies
     # (the workers' _prepare_decode reads only last_token / num_tokens / block_table).
     import copy
     from multiprocessing.shared_memory import SharedMemory as _SharedMemory
@@ -263,6 +276,7 @@ def main():
         "shared_prefix": args.shared_prefix, "cascade_env": os.environ.get("B200ATTN_CASCADE"),
         "fuse_qkv_env": os.environ.get("B200ATTN_FUSE_QKV"),
         "fast_meta_env": os.environ.get("B200ATTN_FAST_META"),
+        "fast_rpc_env": os.environ.get("B200ATTN_FAST_RPC"),
         "cuda_graphs": not args.eager, "total_output_tokens": total, "seconds": t,
         "tokens_per_s": total / t, "init_s": t_init,
         "decode_tokens_per_s": phase["decode_tokens"] / max(phase["decode_s"], 1e-9),
@@ -280,6 +294,13 @@ def main():
         from byox_vllm_b200 import _lib
 
         line["libb200attn_launches"] = int(_lib.load().b200attn_launch_count())
+        if args.tp > 1:
+            from byox_vllm_b200 import fast_rpc
+
+            st = fast_rpc.stats()
+            line["rpc_calls"] = st["steps"]
+            line["rpc_bytes_per_call"] = st["bytes"] / max(st["steps"], 1)
+            line["rpc_host_us_per_call"] = st.get("host_s", 0.0) * 1e6 / max(st["steps"], 1)
     print(json.dumps(line), flush=True)
     if args.out:
         Path(args.out).parent.mkdir(parents=True, exist_ok=True)
