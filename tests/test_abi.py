@@ -58,3 +58,22 @@ def test_sass_is_sm100a_only(built_lib):
                          text=True).stdout
     archs = set(re.findall(r"sm_(\d+a?)", out))
     assert archs == {"100a"}, archs
+
+
+def test_sass_uses_the_blackwell_paths(built_lib):
+    """tcgen05 / TMEM / TMA opcodes are present in the kernels DESIGN.md says use them
+    (tools/sass_summary.py; the committed table is profiles/r02_sass_opcodes.txt)."""
+    from tools import sass_summary
+
+    table = sass_summary.kernel_opcodes(built_lib)
+    names = sass_summary.demangle(table.keys())
+    by_kernel = {}
+    for (_, counts), n in zip(table.items(), names):
+        by_kernel.setdefault(sass_summary.short(n).split("<")[0], []).append(counts)
+    for c in by_kernel["prefill_tc_kernel"]:
+        for op in ("UTCHMMA", "LDTM", "STTM", "UTCBAR", "UTMALDG"):
+            assert c[op] > 0, f"prefill_tc_kernel without {op}"
+    for c in by_kernel["decode_stream_kernel"]:
+        assert c["UTMALDG"] > 0 and c["HMMA"] > 0 and c["LDSM"] > 0
+    for c in by_kernel["qk_norm_rope_bulk_kernel"]:
+        assert c["UBLKCP"] > 0
