@@ -572,7 +572,8 @@ int b200attn_prefill_varlen(const void* q, const void* key, int64_t key_row_stri
     const int mode = prefill_mode_from_env();
     const int group = num_q_heads / num_kv_heads;
     const bool tc_ok = scale > 0.f && (!paged || block_size % 128 == 0) && 128 % group == 0 &&
-                       static_cast<int64_t>(num_blocks) * block_size < (1LL << 31);
+                       static_cast<int64_t>(num_blocks) * block_size < (1LL << 31) &&
+                       num_seqs <= b200::kTcMaxSeqs;
     // With GQA-packed rows the tcgen05 kernel wins at every measured shape, short query blocks
     // included (profiles/r01_microbench_prefill_v4.log); mma.sync is the shape fallback only.
     bool use_tc = tc_ok;

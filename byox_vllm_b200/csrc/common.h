@@ -193,6 +193,11 @@ cudaError_t launch_prefill(const PrefillParams& p, cudaStream_t stream);
 
 // ---- prefill_tc.cu (tcgen05 / TMEM / TMA) ----------------------------------------------------
 // q_map / k_map / v_map: 3-D tensor maps (128 dims, heads, rows), box 64 x 1 x 128, SWIZZLE_128B.
+// Persistent over a cost-ordered item list every CTA builds in shared memory: at most kTcMaxSeqs
+// sequences per call (more -> the caller takes the mma.sync shape fallback); batches with more
+// than kTcMaxItems 256-row pairs per KV head run in descending index order instead of sorted.
+constexpr int kTcMaxSeqs = 4095;
+constexpr int kTcMaxItems = 4096;
 cudaError_t launch_prefill_tc(const PrefillParams& p, const CUtensorMap& q_map,
                               const CUtensorMap& k_map, const CUtensorMap& v_map,
                               cudaStream_t stream);

@@ -2,11 +2,18 @@
 // Replaces flash_attn_varlen_func on the prefill branch of Attention.forward
 // (reference nanovllm/layers/attention.py:72-86), dense and paged-prefix K/V.
 //
-// One CTA = 256 query rows (two 128-row sub-tiles) of one (sequence, q-head); 12 warps (the last
-// warpgroup gives most of its registers to the softmax groups with setmaxnreg):
+// Work item = 256 query rows (two 128-row sub-tiles) of one (sequence, KV head); a row is a (query
+// token, group head) pair. PERSISTENT: one CTA per SM walks a cost-ordered item list that every
+// CTA derives identically from cu_seqlens in its prologue (pair counts -> scan -> bitonic sort of
+// (KV tiles, item) keys in shared memory, heaviest first); CTA c takes positions c, 2P-1-c, 2P+c,
+// ... of the list (zig-zag), so the shares are balanced without a global counter and nothing has
+// to be allocated or reset. All barriers, the TMEM allocation and the K/V rings live across items:
+// the producer prefetches the next item's first K/V tiles and (once the last S MMA of the current
+// item has retired) its Q tiles while the current item's last softmax / PV / epilogue run.
+// 12 warps (the last warpgroup gives most of its registers to the softmax groups, setmaxnreg):
 //   warps 0-3   softmax group 0: one thread per query row of sub-tile 0 (TMEM lane = row)
 //   warps 4-7   softmax group 1: sub-tile 1
-//   warp  8     TMA producer: Q once, then 128-token K and V tiles through two 2-stage rings
+//   warp  8     TMA producer: Q per item, 128-token K and V tiles through two 2-stage rings
 //               (cp.async.bulk.tensor, SWIZZLE_128B boxes of 64 dims x 128 rows, mbarrier tx)
 //   warp  9     MMA issuer (one elected lane) + TMEM owner
 // TMEM (512 columns x 128 lanes of fp32): S0 | S1 | O0 | O1, 128 columns each.
@@ -16,7 +23,10 @@
 //   O_i += P_i . V_j       tcgen05.mma TS: A = P from TMEM, B = V tile MN-major in smem
 // The issuer interleaves the two sub-tiles (PV_0[j], S_0[j+1], PV_1[j], S_1[j+1], ...) so the
 // tensor pipe works on one sub-tile while the other one is in softmax. tcgen05.mma executes in
-// issue order, so S_i[j+1] may overwrite P_i[j] as soon as it is issued after PV_i[j].
+// issue order, so S_i[j+1] may overwrite P_i[j] as soon as it is issued after PV_i[j]; the same
+// argument carries over item boundaries (S_i[0] of the next item is issued after PV_i[last], and
+// its first PV — which overwrites O_i — only after the softmax group has finished the epilogue
+// reads of O_i and signalled the next P).
 // O is only rescaled when a row maximum grows by more than 2^8 (lazy rescale); the row sum uses
 // the same stale maximum, so O / l is exact at the end.
 //
@@ -49,19 +59,32 @@ static_assert(256 * kRegsSoftmax + 128 * kRegsControl <= kTcThreads * kRegsLaunc
 constexpr uint32_t kTmemCols = 512;
 constexpr float kRescaleThreshold = 8.0f;      // log2 domain
 
+// Item schedule (persistent varlen prefill): exclusive scan of the 256-row pairs per sequence and
+// the sorted keys, both in shared memory. Batches beyond kTcMaxSeqs take the shape fallback
+// (api.cu); beyond kTcMaxItems pairs they run unsorted.
+constexpr int kSchedKeyBits = 13;                       // item index inside a key
+constexpr uint32_t kSchedCostMax = (1u << (32 - kSchedKeyBits)) - 1;
+
 constexpr int kSmemQ = 0;
 constexpr int kSmemK = kSmemQ + 2 * kTileBytes;
 constexpr int kSmemV = kSmemK + kStages * kTileBytes;
 constexpr int kSmemBar = kSmemV + kStages * kTileBytes;
-constexpr int kTcSmemBytes = kSmemBar + 256 + 1024;
+constexpr int kSmemPairStart = kSmemBar + 256;                              // int32[kTcMaxSeqs + 1]
+constexpr int kSmemKeys = kSmemPairStart + (kTcMaxSeqs + 1) * 4;            // uint32[kTcMaxItems]
+constexpr int kTcSmemBytes = kSmemKeys + kTcMaxItems * 4 + 1024;
+static_assert(kTcMaxItems <= (1 << kSchedKeyBits), "item index does not fit the key");
+static_assert(kTcSmemBytes <= 232448, "more shared memory than an sm_100 CTA can opt into");
 
 struct Barriers {
-    uint64_t q_full;
+    uint64_t q_full, q_empty;
     uint64_t k_full[kStages], k_empty[kStages];
     uint64_t v_full[kStages], v_empty[kStages];
     uint64_t s_full[2], p_full[2], o_full[2];
     uint32_t tmem_base;
+    int32_t num_pairs;   // 256-row pairs over all sequences (items per KV head)
+    int32_t use_keys;    // 1: keys[] holds the cost-sorted order; 0: descending item index
 };
+static_assert(sizeof(Barriers) <= 256, "barrier block overflows its shared-memory slot");
 
 // Bounded spin: a protocol bug traps (launch error) instead of hanging the GPU.
 __device__ __forceinline__ void wait_bar(uint64_t* bar, uint32_t parity) {
@@ -71,13 +94,167 @@ __device__ __forceinline__ void wait_bar(uint64_t* bar, uint32_t parity) {
     }
 }
 
-// kCascade = false: varlen causal prefill, CTA = (pair of 128-row tiles, KV head, sequence);
-//   a tile row is (query token r / G, group head r % G).
+// One work item: two 128-row sub-tiles of one (sequence, KV head) — or, in cascade mode, of the
+// batch rows of one KV head against one chunk of the shared prefix.
+struct Item {
+    int seq, kvh, q_begin, Lq, Lk, k_begin, offset;
+    int j0;       // first 128-token KV tile (cascade: start of the chunk)
+    int chunk;    // cascade: prefix chunk = workspace slot ws_slot0 + chunk
+    int q_c1;     // TMA head coordinate of the Q boxes
+    int row0[2], n_kv[2], q_c2[2];
+    int n_max;
+};
+
+// KV tiles the heavier sub-tile of pair `pair` of a sequence visits (the sort key).
+__device__ __forceinline__ int pair_cost(int pair, int Lq, int Lk, int toks_per_sub) {
+    const int toks_end = min(Lq, (pair * 2 + 2) * toks_per_sub);
+    const int vis = min(Lk, toks_end + (Lk - Lq));
+    return vis > 0 ? (vis + kTN - 1) / kTN : 0;
+}
+
+// The k-th item of this CTA (false: no more). Every role of the CTA walks the same sequence.
+template <bool kCascade>
+__device__ __forceinline__ bool fetch_item(int k, const PrefillParams& p, const Barriers* bar,
+                                           const int32_t* pair_start, const uint32_t* keys,
+                                           Item& it) {
+    if constexpr (kCascade) {
+        if (k > 0) return false;
+        const PrefixChunks pc = prefix_chunks_of(p.plan[0], p.block_size, p.prefix_chunks);
+        it.chunk = blockIdx.y;  // < pc.valid (checked at kernel entry)
+        it.kvh = blockIdx.z;
+        it.seq = p.plan[1];     // row whose table names the shared pages
+        it.j0 = it.chunk * pc.per;
+        it.q_begin = it.Lq = it.k_begin = it.offset = 0;
+        it.Lk = 0;
+        const int n = min(pc.per, pc.tiles - it.j0);
+        const int rows_per_sub = kTM / p.group;
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            it.row0[i] = (static_cast<int>(blockIdx.x) * 2 + i) * rows_per_sub;  // first batch row
+            it.n_kv[i] = it.row0[i] < p.batch ? n : 0;
+            it.q_c2[i] = it.row0[i];
+        }
+    } else {
+        // zig-zag over the cost-ordered list: round k runs left to right, round k+1 right to left
+        const int P = gridDim.x, c = blockIdx.x;
+        const int64_t g = static_cast<int64_t>(k) * P + ((k & 1) ? P - 1 - c : c);
+        const int T = bar->num_pairs;
+        if (g >= static_cast<int64_t>(T) * p.num_kv_heads) return false;
+        const int li = static_cast<int>(g / p.num_kv_heads);
+        it.kvh = static_cast<int>(g - static_cast<int64_t>(li) * p.num_kv_heads);
+        const int t = bar->use_keys ? static_cast<int>(keys[li] & ((1u << kSchedKeyBits) - 1u))
+                                    : T - 1 - li;
+        int lo = 0, hi = p.num_seqs;  // largest seq with pair_start[seq] <= t
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (pair_start[mid] <= t) lo = mid; else hi = mid;
+        }
+        it.seq = lo;
+        const int pair = t - pair_start[lo];
+        it.q_begin = __ldg(p.cu_seqlens_q + lo);
+        it.Lq = __ldg(p.cu_seqlens_q + lo + 1) - it.q_begin;
+        it.k_begin = __ldg(p.cu_seqlens_k + lo);
+        it.Lk = __ldg(p.cu_seqlens_k + lo + 1) - it.k_begin;
+        it.offset = it.Lk - it.Lq;  // token i sees keys j <= i + offset
+        it.j0 = 0;
+        it.chunk = 0;
+        // GQA packing: a 128-row sub-tile = 128/G query tokens x the G heads of one KV head
+        // (row r = token r / G, head r % G; one TMA box 64 dims x G heads x 128/G tokens), so a
+        // K/V tile is loaded once per KV head and short query blocks still fill the tile.
+        const int toks_per_sub = kTM / p.group;
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            it.row0[i] = (pair * 2 + i) * toks_per_sub;  // first query token of the sub-tile
+            const int toks_end = min(it.Lq, it.row0[i] + toks_per_sub);
+            const int vis = it.row0[i] < it.Lq ? min(it.Lk, toks_end + it.offset) : 0;
+            it.n_kv[i] = vis > 0 ? (vis + kTN - 1) / kTN : 0;  // visible keys [0, vis)
+            it.q_c2[i] = it.q_begin + it.row0[i];
+        }
+    }
+    it.q_c1 = it.kvh * p.group;
+    it.n_max = max(it.n_kv[0], it.n_kv[1]);
+    return true;
+}
+
+// Prologue of the persistent prefill: pair_start[0..S] = exclusive scan of the 256-row pairs per
+// sequence; keys[] = item indices ordered by descending cost (KV tiles), ties by index — a
+// bitonic sort of unique keys, so every CTA ends with the identical list. All threads call it.
+__device__ void build_schedule(const PrefillParams& p, Barriers* bar, int32_t* pair_start,
+                               uint32_t* keys) {
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int S = p.num_seqs;
+    const int toks_per_pair = 2 * kTM / p.group;
+    if (tid < 32) {
+        int running = 0;
+        for (int base = 0; base < S; base += 32) {
+            const int s = base + lane;
+            int n = 0;
+            if (s < S) {
+                const int lq = __ldg(p.cu_seqlens_q + s + 1) - __ldg(p.cu_seqlens_q + s);
+                n = lq > 0 ? (lq + toks_per_pair - 1) / toks_per_pair : 0;
+            }
+            int incl = n;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int up = __shfl_up_sync(0xffffffffu, incl, d);
+                if (lane >= d) incl += up;
+            }
+            if (s < S) pair_start[s] = running + incl - n;
+            running += __shfl_sync(0xffffffffu, incl, 31);
+        }
+        if (lane == 0) {
+            pair_start[S] = running;
+            bar->num_pairs = running;
+            bar->use_keys = (S > 1 && running <= kTcMaxItems) ? 1 : 0;
+        }
+    }
+    __syncthreads();
+    const int T = bar->num_pairs;
+    if (!bar->use_keys) return;  // one sequence (cost is monotone in the pair index) or too many
+    int n2 = 1;
+    while (n2 < T) n2 <<= 1;
+    for (int t = tid; t < n2; t += kTcThreads) {
+        uint32_t key = 0xffffffffu;
+        if (t < T) {
+            int lo = 0, hi = S;
+            while (hi - lo > 1) {
+                const int mid = (lo + hi) >> 1;
+                if (pair_start[mid] <= t) lo = mid; else hi = mid;
+            }
+            const int qb = __ldg(p.cu_seqlens_q + lo), kb = __ldg(p.cu_seqlens_k + lo);
+            const int lq = __ldg(p.cu_seqlens_q + lo + 1) - qb;
+            const int lk = __ldg(p.cu_seqlens_k + lo + 1) - kb;
+            const uint32_t cost = min(static_cast<uint32_t>(
+                pair_cost(t - pair_start[lo], lq, lk, kTM / p.group)), kSchedCostMax - 1);
+            key = ((kSchedCostMax - 1 - cost) << kSchedKeyBits) | static_cast<uint32_t>(t);
+        }
+        keys[t] = key;
+    }
+    __syncthreads();
+    for (int k = 2; k <= n2; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int idx = tid; idx < n2; idx += kTcThreads) {
+                const int ixj = idx ^ j;
+                if (ixj > idx) {
+                    const uint32_t a = keys[idx], b = keys[ixj];
+                    if ((a > b) == ((idx & k) == 0)) {
+                        keys[idx] = b;
+                        keys[ixj] = a;
+                    }
+                }
+            }
+            __syncthreads();
+        }
+    }
+}
+
+// kCascade = false: varlen causal prefill, persistent over (pair of 128-row tiles, KV head,
+//   sequence) items; a tile row is (query token r / G, group head r % G).
 // kCascade = true:  shared-prefix pass of the cascade decode (cascade.cu). CTA = (pair of 128-row
-//   tiles of the B*G query rows of one KV head, prefix chunk, KV head). A tile row r is
-//   (batch row r / G, group head r % G): the TMA box 64 dims x G heads x 128/G batch rows of
-//   q [B, Hq, 128] lands in shared memory in exactly that order. Keys are the tiles of this
-//   chunk of the P shared pages (block ids from row b0's table), all visible: no masking. The
+//   tiles of the B*G query rows of one KV head, prefix chunk, KV head), one item per CTA. A tile
+//   row r is (batch row r / G, group head r % G): the TMA box 64 dims x G heads x 128/G batch
+//   rows of q [B, Hq, 128] lands in shared memory in exactly that order. Keys are the tiles of
+//   this chunk of the P shared pages (block ids from row b0's table), all visible: no masking. The
 //   epilogue writes normalised fp32 partials + log2-sum-exp for the decode merge.
 // kEmu of every 4 exponential pairs are evaluated on the FMA pipe (tc::exp2_fma_pipe), the rest on
 // the MUFU.
@@ -86,69 +263,28 @@ __global__ void __launch_bounds__(kTcThreads, 1)
 prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
                   const __grid_constant__ CUtensorMap k_map,
                   const __grid_constant__ CUtensorMap v_map, const PrefillParams p) {
-    int seq = 0, h = 0, kvh = 0, q_begin = 0, Lq = 0, k_begin = 0, Lk = 0, offset = 0;
-    int j0 = 0;       // first 128-token KV tile of this CTA (cascade: start of the chunk)
-    int chunk = 0;    // cascade: prefix chunk = workspace slot ws_slot0 + chunk
-    int q_c1 = 0;     // TMA head coordinate of the Q boxes
-    int row0[2], n_kv[2], q_c2[2];
     if constexpr (kCascade) {
         // Let the dependent grid (the streaming decode over the per-row remainders, launched
         // with programmatic stream serialization) start now; it waits on this grid only where it
         // reads the partials written below.
         asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
         const PrefixChunks pc = prefix_chunks_of(p.plan[0], p.block_size, p.prefix_chunks);
-        chunk = blockIdx.y;
-        if (chunk >= pc.valid) return;  // uniform for the whole CTA (also: no shared prefix)
-        kvh = blockIdx.z;
-        seq = p.plan[1];                // row whose table names the shared pages
-        j0 = chunk * pc.per;
-        const int n = min(pc.per, pc.tiles - j0);
-        const int rows_per_sub = kTM / p.group;
-#pragma unroll
-        for (int i = 0; i < 2; ++i) {
-            row0[i] = (static_cast<int>(blockIdx.x) * 2 + i) * rows_per_sub;  // first batch row
-            n_kv[i] = row0[i] < p.batch ? n : 0;
-            q_c2[i] = row0[i];
-        }
-        q_c1 = kvh * p.group;
-    } else {
-        // GQA packing: a 128-row sub-tile = 128/G query tokens x the G heads of one KV head
-        // (row r = token r / G, head r % G; one TMA box 64 dims x G heads x 128/G tokens), so a
-        // K/V tile is loaded once per KV head and short query blocks still fill the tile.
-        seq = blockIdx.z;
-        kvh = blockIdx.y;
-        q_begin = p.cu_seqlens_q[seq];
-        Lq = p.cu_seqlens_q[seq + 1] - q_begin;
-        k_begin = p.cu_seqlens_k[seq];
-        Lk = p.cu_seqlens_k[seq + 1] - k_begin;
-        const int toks_per_sub = kTM / p.group;
-        const int n_pairs = (Lq + 2 * toks_per_sub - 1) / (2 * toks_per_sub);
-        if (static_cast<int>(blockIdx.x) >= n_pairs) return;  // uniform for the whole CTA
-        const int pair = n_pairs - 1 - blockIdx.x;            // heaviest (last) tokens first
-        offset = Lk - Lq;                                     // token i sees keys j <= i + offset
-#pragma unroll
-        for (int i = 0; i < 2; ++i) {
-            row0[i] = (pair * 2 + i) * toks_per_sub;          // first query token of the sub-tile
-            const int toks_end = min(Lq, row0[i] + toks_per_sub);
-            const int vis = row0[i] < Lq ? min(Lk, toks_end + offset) : 0;  // visible keys [0, vis)
-            n_kv[i] = vis > 0 ? (vis + kTN - 1) / kTN : 0;
-            q_c2[i] = q_begin + row0[i];
-        }
-        q_c1 = kvh * p.group;
+        if (static_cast<int>(blockIdx.y) >= pc.valid) return;  // uniform (also: no shared prefix)
     }
     const int g_shift = __ffs(p.group) - 1;  // G is a power of two (128 % G == 0)
-    (void)h;
-    const int n_max = max(n_kv[0], n_kv[1]);
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>(
         (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
     Barriers* bar = reinterpret_cast<Barriers*>(smem + kSmemBar);
+    const int32_t* pair_start = reinterpret_cast<const int32_t*>(smem + kSmemPairStart);
+    const uint32_t* keys = reinterpret_cast<const uint32_t*>(smem + kSmemKeys);
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
 
     if (threadIdx.x == 0) {
         mbar_init(&bar->q_full, 1);
+        mbar_init(&bar->q_empty, 1);
 #pragma unroll
         for (int s = 0; s < kStages; ++s) {
             mbar_init(&bar->k_full[s], 1);
@@ -164,6 +300,9 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
         }
         fence_mbar_init();
     }
+    if constexpr (!kCascade)
+        build_schedule(p, bar, reinterpret_cast<int32_t*>(smem + kSmemPairStart),
+                       reinterpret_cast<uint32_t*>(smem + kSmemKeys));
     if (warp == kMmaWarp) tc::tmem_alloc(&bar->tmem_base, kTmemCols);
     tc::fence_before_sync();
     __syncthreads();
@@ -174,41 +313,56 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
     if (warp == kProducerWarp) {
         // ============================ TMA producer ============================
         tc::reg_dec<kRegsControl>();
-        if (lane == 0 && n_max > 0) {
+        if (lane == 0) {
             tma_prefetch_desc(&q_map);
             tma_prefetch_desc(&k_map);
             tma_prefetch_desc(&v_map);
-            const int n_q = n_kv[1] > 0 ? 2 : 1;  // sub-tile 0 is loaded whenever anything runs
-            mbar_expect_tx(&bar->q_full, n_q * kTileBytes);
-            for (int i = 0; i < n_q; ++i) {
-                uint8_t* dst = smem + kSmemQ + i * kTileBytes;
-                tma_load_3d(dst, &q_map, &bar->q_full, 0, q_c1, q_c2[i]);
-                tma_load_3d(dst + kHalfBytes, &q_map, &bar->q_full, 64, q_c1, q_c2[i]);
-            }
             const bool paged = kCascade || p.block_tables != nullptr;
-            const int32_t* table =
-                paged ? p.block_tables + static_cast<int64_t>(seq) * p.table_row_stride : nullptr;
-            for (int j = 0; j < n_max; ++j) {
-                const int s = j % kStages;
-                const uint32_t ph = (j / kStages) & 1u;
-                const int tok0 = (j0 + j) * kTN;
-                int slot;
-                if (paged) {
-                    // a 128-token tile never straddles a page (block_size % 128 == 0)
-                    slot = table[tok0 / p.block_size] * p.block_size + tok0 % p.block_size;
-                } else {
-                    slot = k_begin + tok0;
+            uint32_t kv_it = 0;   // K/V tiles issued so far (ring position, across items)
+            uint32_t q_it = 0;    // items with work so far (Q buffer phase)
+            Item it;
+            for (int k = 0; fetch_item<kCascade>(k, p, bar, pair_start, keys, it); ++k) {
+                if (it.n_max == 0) continue;
+                const int32_t* table =
+                    paged ? p.block_tables + static_cast<int64_t>(it.seq) * p.table_row_stride
+                          : nullptr;
+                for (int j = 0; j < it.n_max; ++j, ++kv_it) {
+                    const int s = kv_it % kStages;
+                    const uint32_t ph = (kv_it / kStages) & 1u;
+                    const int tok0 = (it.j0 + j) * kTN;
+                    int slot;
+                    if (paged) {
+                        // a 128-token tile never straddles a page (block_size % 128 == 0)
+                        slot = __ldg(table + tok0 / p.block_size) * p.block_size +
+                               tok0 % p.block_size;
+                    } else {
+                        slot = it.k_begin + tok0;
+                    }
+                    wait_bar(&bar->k_empty[s], ph ^ 1u);
+                    mbar_expect_tx(&bar->k_full[s], kTileBytes);
+                    uint8_t* kd = smem + kSmemK + s * kTileBytes;
+                    tma_load_3d(kd, &k_map, &bar->k_full[s], 0, it.kvh, slot);
+                    tma_load_3d(kd + kHalfBytes, &k_map, &bar->k_full[s], 64, it.kvh, slot);
+                    wait_bar(&bar->v_empty[s], ph ^ 1u);
+                    mbar_expect_tx(&bar->v_full[s], kTileBytes);
+                    uint8_t* vd = smem + kSmemV + s * kTileBytes;
+                    tma_load_3d(vd, &v_map, &bar->v_full[s], 0, it.kvh, slot);
+                    tma_load_3d(vd + kHalfBytes, &v_map, &bar->v_full[s], 64, it.kvh, slot);
+                    if (j == 0) {
+                        // Q after the item's first K/V tile: those ring slots free up earlier
+                        // than the Q buffer (released by the previous item's LAST S MMA).
+                        wait_bar(&bar->q_empty, (q_it & 1u) ^ 1u);
+                        const int n_q = it.n_kv[1] > 0 ? 2 : 1;  // sub-tile 0 always has rows
+                        mbar_expect_tx(&bar->q_full, n_q * kTileBytes);
+                        for (int i = 0; i < n_q; ++i) {
+                            uint8_t* dst = smem + kSmemQ + i * kTileBytes;
+                            tma_load_3d(dst, &q_map, &bar->q_full, 0, it.q_c1, it.q_c2[i]);
+                            tma_load_3d(dst + kHalfBytes, &q_map, &bar->q_full, 64, it.q_c1,
+                                        it.q_c2[i]);
+                        }
+                        ++q_it;
+                    }
                 }
-                wait_bar(&bar->k_empty[s], ph ^ 1u);
-                mbar_expect_tx(&bar->k_full[s], kTileBytes);
-                uint8_t* kd = smem + kSmemK + s * kTileBytes;
-                tma_load_3d(kd, &k_map, &bar->k_full[s], 0, kvh, slot);
-                tma_load_3d(kd + kHalfBytes, &k_map, &bar->k_full[s], 64, kvh, slot);
-                wait_bar(&bar->v_empty[s], ph ^ 1u);
-                mbar_expect_tx(&bar->v_full[s], kTileBytes);
-                uint8_t* vd = smem + kSmemV + s * kTileBytes;
-                tma_load_3d(vd, &v_map, &bar->v_full[s], 0, kvh, slot);
-                tma_load_3d(vd + kHalfBytes, &v_map, &bar->v_full[s], 64, kvh, slot);
             }
         }
     } else if (warp == kMmaWarp) {
@@ -247,53 +401,64 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
             __syncwarp();
         };
 
-        if (n_max > 0) {
-            wait_bar(&bar->q_full, 0);
-            wait_bar(&bar->k_full[0], 0);
+        uint32_t kv_it = 0, q_it = 0;
+        uint32_t sp_it[2] = {0, 0};  // S/P rounds per sub-tile so far (s_full / p_full phases)
+        Item it;
+        for (int k = 0; fetch_item<kCascade>(k, p, bar, pair_start, keys, it); ++k) {
+            const int n_max = it.n_max;
+            if (n_max == 0) continue;
+            wait_bar(&bar->q_full, q_it & 1u);
+            ++q_it;
+            wait_bar(&bar->k_full[kv_it % kStages], (kv_it / kStages) & 1u);
             tc::fence_after_sync();
 #pragma unroll
             for (int i = 0; i < 2; ++i)
-                if (n_kv[i] > 0) issue_s(i, 0);
-            if (lane == 0) tc::commit(&bar->k_empty[0]);
+                if (it.n_kv[i] > 0) issue_s(i, kv_it % kStages);
+            if (lane == 0) {
+                tc::commit(&bar->k_empty[kv_it % kStages]);
+                if (n_max == 1) tc::commit(&bar->q_empty);  // the item's last S has been issued
+            }
             __syncwarp();
-        }
-        for (int j = 0; j < n_max; ++j) {
-            const int s = j % kStages;
-            wait_bar(&bar->v_full[s], (j / kStages) & 1u);
-            // Rows at or beyond Lk inside the tile are masked (P = 0), but 0 * NaN would still
-            // poison O: clear those V rows (unwritten cache slots may hold anything).
-            const int valid = kCascade ? kTN : Lk - j * kTN;  // shared pages are full
-            if (valid < kTN) {
-                uint8_t* vs = smem + kSmemV + s * kTileBytes;
-                const int r_lo = max(valid, 0);
-                for (int idx = r_lo * 16 + lane; idx < kTN * 16; idx += 32) {
-                    const int r = idx >> 4, c = idx & 15;
-                    *reinterpret_cast<int4*>(vs + (c >> 3) * kHalfBytes + r * 128 + (c & 7) * 16) =
-                        make_int4(0, 0, 0, 0);
+            for (int j = 0; j < n_max; ++j, ++kv_it) {
+                const int s = kv_it % kStages;
+                wait_bar(&bar->v_full[s], (kv_it / kStages) & 1u);
+                // Rows at or beyond Lk inside the tile are masked (P = 0), but 0 * NaN would still
+                // poison O: clear those V rows (unwritten cache slots may hold anything).
+                const int valid = kCascade ? kTN : it.Lk - j * kTN;  // shared pages are full
+                if (valid < kTN) {
+                    uint8_t* vs = smem + kSmemV + s * kTileBytes;
+                    const int r_lo = max(valid, 0);
+                    for (int idx = r_lo * 16 + lane; idx < kTN * 16; idx += 32) {
+                        const int r = idx >> 4, c = idx & 15;
+                        *reinterpret_cast<int4*>(vs + (c >> 3) * kHalfBytes + r * 128 +
+                                                 (c & 7) * 16) = make_int4(0, 0, 0, 0);
+                    }
+                    fence_proxy_async();
+                    __syncwarp();
                 }
-                fence_proxy_async();
+                const int sn = (kv_it + 1) % kStages;
+                if (j + 1 < n_max) wait_bar(&bar->k_full[sn], ((kv_it + 1) / kStages) & 1u);
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    if (j < it.n_kv[i]) {
+                        wait_bar(&bar->p_full[i], sp_it[i] & 1u);
+                        ++sp_it[i];
+                        tc::fence_after_sync();
+                        issue_pv(i, s, j > 0);
+                        if (j == it.n_kv[i] - 1) {
+                            if (lane == 0) tc::commit(&bar->o_full[i]);
+                            __syncwarp();
+                        }
+                    }
+                    if (j + 1 < it.n_kv[i]) issue_s(i, sn);
+                }
+                if (lane == 0) {
+                    tc::commit(&bar->v_empty[s]);
+                    if (j + 1 < n_max) tc::commit(&bar->k_empty[sn]);
+                    if (j + 2 == n_max) tc::commit(&bar->q_empty);  // last S issued in this step
+                }
                 __syncwarp();
             }
-            const int sn = (j + 1) % kStages;
-            if (j + 1 < n_max) wait_bar(&bar->k_full[sn], ((j + 1) / kStages) & 1u);
-#pragma unroll
-            for (int i = 0; i < 2; ++i) {
-                if (j < n_kv[i]) {
-                    wait_bar(&bar->p_full[i], j & 1u);
-                    tc::fence_after_sync();
-                    issue_pv(i, s, j > 0);
-                    if (j == n_kv[i] - 1) {
-                        if (lane == 0) tc::commit(&bar->o_full[i]);
-                        __syncwarp();
-                    }
-                }
-                if (j + 1 < n_kv[i]) issue_s(i, sn);
-            }
-            if (lane == 0) {
-                tc::commit(&bar->v_empty[s]);
-                if (j + 1 < n_max) tc::commit(&bar->k_empty[sn]);
-            }
-            __syncwarp();
         }
     } else if (warp < kProducerWarp) {
         // ============================ softmax / correction / epilogue ============================
@@ -303,15 +468,20 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
         const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
         const uint32_t s_tmem = tmem + lane_base + i * kTN;
         const uint32_t o_tmem = tmem + lane_base + 2 * kTN + i * kHeadDim;
-        const int row = row0[i] + (r >> g_shift);      // query token (cascade: batch row)
-        const int head = kvh * p.group + (r & (p.group - 1));
-        const int n = n_kv[i];
         const float c = p.scale_log2;
+        uint32_t sp_it = 0;   // S/P rounds of this sub-tile so far
+        uint32_t o_it = 0;    // items of this sub-tile with work so far
+        Item it;
+        for (int k = 0; fetch_item<kCascade>(k, p, bar, pair_start, keys, it); ++k) {
+        const int row = it.row0[i] + (r >> g_shift);   // query token (cascade: batch row)
+        const int head = it.kvh * p.group + (r & (p.group - 1));
+        const int n = it.n_kv[i];
+        const int Lk = it.Lk, offset = it.offset;
         float m_ref = -INFINITY;  // scaled (log2-domain) reference maximum of this row
         float l = 0.f;
 
-        for (int j = 0; j < n; ++j) {
-            wait_bar(&bar->s_full[i], j & 1u);
+        for (int j = 0; j < n; ++j, ++sp_it) {
+            wait_bar(&bar->s_full[i], sp_it & 1u);
             tc::fence_after_sync();
             uint32_t sr[128];
             tc::tmem_ld128(s_tmem, sr);
@@ -388,11 +558,12 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
             // ---- epilogue: normalised fp32 partial + log2-sum-exp of this prefix chunk ----
             const int b = row;
             if (n > 0) {  // warp-uniform: n depends on the sub-tile only
-                wait_bar(&bar->o_full[i], 0);
+                wait_bar(&bar->o_full[i], o_it & 1u);
+                ++o_it;
                 tc::fence_after_sync();
                 const int64_t qrow =
                     static_cast<int64_t>(b) * p.num_q_heads + head;
-                const int64_t slot = qrow * p.ws_slots + p.ws_slot0 + chunk;
+                const int64_t slot = qrow * p.ws_slots + p.ws_slot0 + it.chunk;
                 const float inv = l > 0.f ? 1.f / l : 0.f;
                 float* og = p.ws_o + slot * kHeadDim;
 #pragma unroll
@@ -415,11 +586,12 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
             }
         } else {
         // ---- epilogue: O / l -> bf16 -> global (row-predicated 16-byte stores) ----
-        const bool row_ok = row < Lq;
+        const bool row_ok = row < it.Lq;
         uint8_t* orow_g = static_cast<uint8_t*>(p.out) +
-                          ((static_cast<int64_t>(q_begin) + row) * p.num_q_heads + head) * 256;
+                          ((static_cast<int64_t>(it.q_begin) + row) * p.num_q_heads + head) * 256;
         if (n > 0) {
-            wait_bar(&bar->o_full[i], 0);
+            wait_bar(&bar->o_full[i], o_it & 1u);
+            ++o_it;
             tc::fence_after_sync();
             const float inv = l > 0.f ? 1.f / l : 0.f;
 #pragma unroll
@@ -442,12 +614,16 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
                     }
                 }
             }
+            // the next item's first PV overwrites O_i: order these TMEM reads before the P
+            // signal that releases it
+            tc::fence_before_sync();
         } else if (row_ok) {
             // no visible key for this sub-tile (only possible when Lk < Lq): zeros, as flash-attn
 #pragma unroll
             for (int v = 0; v < 16; ++v) st_v4(orow_g + v * 16, make_int4(0, 0, 0, 0));
         }
         }  // !kCascade
+        }  // items
     }
 
     else {
@@ -475,16 +651,21 @@ int exp_emu_from_env(int dflt) {
     return v < 0 ? dflt : v;
 }
 
+constexpr int kMaxDevices = 64;
+
 template <bool kCascade, int kEmu>
 cudaError_t launch_tc(dim3 grid, const PrefillParams& p, const CUtensorMap& q_map,
                       const CUtensorMap& k_map, const CUtensorMap& v_map, cudaStream_t stream) {
-    static bool configured = false;
-    if (!configured) {
+    // the opt-in shared-memory size is a per-device function attribute
+    static bool configured[kMaxDevices] = {};
+    int dev = 0;
+    if (cudaError_t e = cudaGetDevice(&dev); e != cudaSuccess) return e;
+    if (dev < 0 || dev >= kMaxDevices || !configured[dev]) {
         cudaError_t e = cudaFuncSetAttribute(prefill_tc_kernel<kCascade, kEmu>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              kTcSmemBytes);
         if (e != cudaSuccess) return e;
-        configured = true;
+        if (dev >= 0 && dev < kMaxDevices) configured[dev] = true;
     }
     prefill_tc_kernel<kCascade, kEmu><<<grid, kTcThreads, kTcSmemBytes, stream>>>(q_map, k_map,
                                                                                   v_map, p);
@@ -504,6 +685,19 @@ cudaError_t launch_tc_emu(int emu, dim3 grid, const PrefillParams& p, const CUte
     }
 }
 
+int device_sm_count() {
+    static int sms[kMaxDevices] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return 148;
+    if (sms[dev] == 0) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+            n = 148;
+        sms[dev] = n;
+    }
+    return sms[dev];
+}
+
 }  // namespace
 
 constexpr int kDefaultExpEmu = 0;
@@ -511,8 +705,14 @@ constexpr int kDefaultExpEmu = 0;
 cudaError_t launch_prefill_tc(const PrefillParams& p, const CUtensorMap& q_map,
                               const CUtensorMap& k_map, const CUtensorMap& v_map,
                               cudaStream_t stream) {
-    const int rows = p.max_seqlen_q * p.group;  // query rows per KV head of the longest sequence
-    dim3 grid((rows + 2 * kTM - 1) / (2 * kTM), p.num_kv_heads, p.num_seqs);
+    // Persistent: one CTA per SM (1 CTA/SM by shared memory), never more CTAs than items can exist
+    // (256-row pairs over all sequences <= total_q / tokens-per-pair + num_seqs, per KV head).
+    const int toks_per_pair = 2 * kTM / p.group;
+    const int64_t bound =
+        (static_cast<int64_t>(p.total_q) / toks_per_pair + p.num_seqs) * p.num_kv_heads;
+    const int sms = device_sm_count();
+    const int ctas = static_cast<int>(bound < sms ? bound : sms);
+    dim3 grid(ctas > 0 ? ctas : 1, 1, 1);
     return launch_tc_emu<false>(exp_emu_from_env(kDefaultExpEmu), grid, p, q_map, k_map, v_map,
                                 stream);
 }
