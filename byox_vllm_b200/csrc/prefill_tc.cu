@@ -52,8 +52,8 @@ constexpr int kTcThreads = 384;                // 3 warpgroups: softmax 0, softm
 // setmaxnreg budgets. The pool is what the CTA got at launch (168 regs x 384 threads), not the
 // whole register file: an inc that does not fit waits forever.
 constexpr int kRegsLaunch = 168;
-constexpr int kRegsSoftmax = 224;
-constexpr int kRegsControl = 48;
+constexpr int kRegsSoftmax = 216;
+constexpr int kRegsControl = 72;
 static_assert(256 * kRegsSoftmax + 128 * kRegsControl <= kTcThreads * kRegsLaunch,
               "setmaxnreg budgets exceed the registers the CTA owns");
 constexpr uint32_t kTmemCols = 512;
@@ -473,9 +473,10 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
         uint32_t o_it = 0;    // items of this sub-tile with work so far
         Item it;
         for (int k = 0; fetch_item<kCascade>(k, p, bar, pair_start, keys, it); ++k) {
-        const int row = it.row0[i] + (r >> g_shift);   // query token (cascade: batch row)
+        // (selects, not it.row0[i]: a runtime index would push the item into local memory)
+        const int row = (i ? it.row0[1] : it.row0[0]) + (r >> g_shift);  // token (cascade: batch row)
         const int head = it.kvh * p.group + (r & (p.group - 1));
-        const int n = it.n_kv[i];
+        const int n = i ? it.n_kv[1] : it.n_kv[0];
         const int Lk = it.Lk, offset = it.offset;
         float m_ref = -INFINITY;  // scaled (log2-domain) reference maximum of this row
         float l = 0.f;
