@@ -62,6 +62,55 @@ def test_prefill_more_shapes_vs_oracle(cuda_dev, Hq, Hkv):
     assert_close(got, want, f"paged prefix {Hq}/{Hkv}")
 
 
+SCHEDULE_CASES = [
+    # name, lens, cached, Hq, Hkv: the persistent kernel's item list (csrc/prefill_tc.cu)
+    ("many_short_16_8", "rand:220:1:90", None, 16, 8),          # > 148 CTAs' worth of 1-tile items
+    ("bench_prompts_16_8", "rand:40:100:1024", None, 16, 8),     # the reference bench's prefill mix
+    ("long_and_short_32_8", [2300, 3, 700, 1, 129, 64, 1500, 31], None, 32, 8),
+    ("cached_mix_8_1", [600, 300, 1300, 200, 2049], [512, 0, 1024, 0, 1792], 8, 1),
+    ("mha_4_4", [513, 77, 256, 1030], None, 4, 4),               # G = 1: 128 tokens per sub-tile
+    ("gqa8_one_seq_8_1", [3000], None, 8, 1),                    # single sequence: unsorted list
+]
+
+
+def _schedule_lens(spec, seed):
+    if not isinstance(spec, str):
+        return list(spec)
+    import random
+
+    _, n, lo, hi = spec.split(":")
+    rng = random.Random(seed)
+    return [rng.randint(int(lo), int(hi)) for _ in range(int(n))]
+
+
+@pytest.mark.parametrize("case", SCHEDULE_CASES, ids=[c[0] for c in SCHEDULE_CASES])
+def test_prefill_persistent_schedule(cuda_dev, case):
+    """Every (sequence, pair, KV head) item is visited exactly once whatever the mix: all rows of
+    all sequences match the oracle (a skipped item leaves rows of the poisoned output untouched, a
+    doubled one is harmless but a wrong barrier phase is not), twice in a row (no state between
+    launches)."""
+    from byox_vllm_b200.attention import prefill_varlen
+
+    name, spec, cached, Hq, Hkv = case
+    lens = _schedule_lens(spec, seed=len(name))
+    c = synth.prefill_case(lens, Hq, Hkv, cached=cached, seed=90 + len(name))
+    got, d = _forward(cuda_dev, c, Hq, Hkv)
+    ctx = type("Ctx", (), dict(c.meta))()
+    want = orc.attention_forward_ref(c.q, c.k, c.v, c.k_cache, c.v_cache, ctx, c.scale)
+    assert_close(got, want, f"{name} vs oracle")
+    m = c.meta
+    paged = m.get("block_tables") is not None
+    out = torch.full_like(d["q"], float("nan"))
+    for _ in range(2):
+        prefill_varlen(d["q"], d["k_cache"] if paged else d["k"], d["v_cache"] if paged else d["v"],
+                       m["cu_seqlens_q"].to(cuda_dev), m["cu_seqlens_k"].to(cuda_dev),
+                       m["max_seqlen_q"], m["max_seqlen_k"], c.scale,
+                       block_tables=m["block_tables"].to(cuda_dev) if paged else None, out=out)
+        torch.cuda.synchronize()
+        assert torch.equal(out.view(torch.int16), got.view(torch.int16)), name
+        out.fill_(float("nan"))
+
+
 def test_warmup_path_without_cache(cuda_dev):
     """_warmup_model (model_runner.py:102-113): empty caches, no slots, dense attention."""
     from byox_vllm_b200.attention import Attention
