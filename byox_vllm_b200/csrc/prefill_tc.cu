@@ -15,14 +15,14 @@
 //   warps 4-7   softmax group 1: sub-tile 1
 //   warp  8     TMA producer: Q per item, 128-token K and V tiles through two 2-stage rings
 //               (cp.async.bulk.tensor, SWIZZLE_128B boxes of 64 dims x 128 rows, mbarrier tx)
-//   warp  9     MMA issuer (one elected lane) + TMEM owner
+//   warps 9,10  MMA issuers (one elected lane each), one per sub-tile; warp 9 owns TMEM
 // TMEM (512 columns x 128 lanes of fp32): S0 | S1 | O0 | O1, 128 columns each.
 //   S_i = Q_i . K_j^T      tcgen05.mma SS, M128 N128 K16 x 8, both operands K-major in smem
 //   P_i = exp2(S_i*c - m)  softmax thread reads its S row with tcgen05.ld, writes bf16 P over the
 //                          first 64 columns of S_i with tcgen05.st (fp32 max/sum in registers)
 //   O_i += P_i . V_j       tcgen05.mma TS: A = P from TMEM, B = V tile MN-major in smem
-// The issuer interleaves the two sub-tiles (PV_0[j], S_0[j+1], PV_1[j], S_1[j+1], ...) so the
-// tensor pipe works on one sub-tile while the other one is in softmax. tcgen05.mma executes in
+// Each sub-tile has its own issuing warp (PV_i[j], S_i[j+1], ...), so the tensor pipe works on
+// one sub-tile while the other one is in softmax. tcgen05.mma of one thread executes in
 // issue order, so S_i[j+1] may overwrite P_i[j] as soon as it is issued after PV_i[j]; the same
 // argument carries over item boundaries (S_i[0] of the next item is issued after PV_i[last], and
 // its first PV — which overwrites O_i — only after the softmax group has finished the epilogue
@@ -48,7 +48,7 @@ constexpr int kHalfBytes = 128 * 128;          // [128 rows][64 dims] bf16, 128-
 constexpr int kTileBytes = 2 * kHalfBytes;     // 32 KiB: dims 0-63 | dims 64-127
 constexpr int kProducerWarp = 8;
 constexpr int kMmaWarp = 9;
-constexpr int kTcThreads = 384;                // 3 warpgroups: softmax 0, softmax 1, {TMA, MMA, 2 idle}
+constexpr int kTcThreads = 384;                // 3 warpgroups: softmax 0, softmax 1, {TMA, 2 MMA, 1 idle}
 // setmaxnreg budgets. The pool is what the CTA got at launch (168 regs x 384 threads), not the
 // whole register file: an inc that does not fit waits forever.
 constexpr int kRegsLaunch = 168;
@@ -79,6 +79,7 @@ struct Barriers {
     uint64_t q_full, q_empty;
     uint64_t k_full[kStages], k_empty[kStages];
     uint64_t v_full[kStages], v_empty[kStages];
+    uint64_t v_zeroed[kStages];  // issuer 0 -> issuer 1: masked V rows of the slot are cleared
     uint64_t s_full[2], p_full[2], o_full[2];
     uint32_t tmem_base;
     int32_t num_pairs;   // 256-row pairs over all sequences (items per KV head)
@@ -284,13 +285,14 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
 
     if (threadIdx.x == 0) {
         mbar_init(&bar->q_full, 1);
-        mbar_init(&bar->q_empty, 1);
+        mbar_init(&bar->q_empty, 2);  // both issuers
 #pragma unroll
         for (int s = 0; s < kStages; ++s) {
             mbar_init(&bar->k_full[s], 1);
-            mbar_init(&bar->k_empty[s], 1);
+            mbar_init(&bar->k_empty[s], 2);
             mbar_init(&bar->v_full[s], 1);
-            mbar_init(&bar->v_empty[s], 1);
+            mbar_init(&bar->v_empty[s], 2);
+            mbar_init(&bar->v_zeroed[s], 1);
         }
 #pragma unroll
         for (int i = 0; i < 2; ++i) {
@@ -365,36 +367,44 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
                 }
             }
         }
-    } else if (warp == kMmaWarp) {
-        // ============================ MMA issuer ============================
+    } else if (warp == kMmaWarp || warp == kMmaWarp + 1) {
+        // ============================ MMA issuers ============================
+        // One issuing warp per sub-tile: the S_i -> P_i -> PV_i chain of a sub-tile only depends on
+        // MMAs of the same warp (tcgen05.mma of one thread execute in issue order), and neither
+        // sub-tile's MMAs queue behind a wait for the other one's softmax. A single issuer also
+        // spends ~60 clk of dependent scalar work per 64-clk MMA (descriptor arithmetic, R2UR):
+        // two warps halve that. K/V ring slots and the Q buffer are released by BOTH issuers
+        // (arrival count 2; an issuer without work for a tile commits at once).
         tc::reg_dec<kRegsControl>();
+        const int i = warp - kMmaWarp;  // sub-tile of this issuer
         constexpr uint32_t idesc_s = tc::idesc_bf16_f32(kTM, kTN, false);
         constexpr uint32_t idesc_o = tc::idesc_bf16_f32(kTM, kHeadDim, true);
-        const uint32_t q_addr = smem_u32(smem + kSmemQ);
-        const uint32_t k_addr = smem_u32(smem + kSmemK);
-        const uint32_t v_addr = smem_u32(smem + kSmemV);
+        // descriptors of the tile bases; an address offset adds (bytes >> 4) to the start-address
+        // field (14 bits of 16-byte units: shared memory is < 256 KiB, no carry out of the field)
+        const uint64_t q_desc = tc::desc_kmajor(smem_u32(smem + kSmemQ) + i * kTileBytes);
+        const uint64_t k_desc = tc::desc_kmajor(smem_u32(smem + kSmemK));
+        const uint64_t v_desc = tc::desc_mnmajor(smem_u32(smem + kSmemV), kHalfBytes);
+        const uint32_t s_tmem = tmem + i * kTN;
+        const uint32_t o_tmem = tmem + 2 * kTN + i * kHeadDim;
 
-        auto issue_s = [&](int i, int stage) {  // S_i = Q_i . K^T   (head_dim 128 = 2 halves x 4)
+        auto issue_s = [&](int stage) {  // S_i = Q_i . K^T   (head_dim 128 = 2 halves x 4)
             if (lane == 0) {
-                const uint32_t a0 = q_addr + i * kTileBytes;
-                const uint32_t b0 = k_addr + stage * kTileBytes;
+                const uint64_t kb = k_desc + static_cast<uint64_t>((stage * kTileBytes) >> 4);
 #pragma unroll
                 for (int kk = 0; kk < 8; ++kk) {
-                    const uint32_t off = (kk >> 2) * kHalfBytes + (kk & 3) * 32;
-                    tc::mma_ss(tmem + i * kTN, tc::desc_kmajor(a0 + off), tc::desc_kmajor(b0 + off),
-                               idesc_s, kk > 0);
+                    const uint64_t off = ((kk >> 2) * kHalfBytes + (kk & 3) * 32) >> 4;
+                    tc::mma_ss(s_tmem, q_desc + off, kb + off, idesc_s, kk > 0);
                 }
                 tc::commit(&bar->s_full[i]);
             }
             __syncwarp();
         };
-        auto issue_pv = [&](int i, int stage, bool accumulate) {  // O_i (+)= P_i . V
+        auto issue_pv = [&](int stage, bool accumulate) {  // O_i (+)= P_i . V
             if (lane == 0) {
-                const uint32_t b0 = v_addr + stage * kTileBytes;
+                const uint64_t vb = v_desc + static_cast<uint64_t>((stage * kTileBytes) >> 4);
 #pragma unroll
                 for (int kk = 0; kk < 8; ++kk) {  // 16 tokens per instruction
-                    tc::mma_ts(tmem + 2 * kTN + i * kHeadDim, tmem + i * kTN + kk * 8,
-                               tc::desc_mnmajor(b0 + kk * 16 * 128, kHalfBytes), idesc_o,
+                    tc::mma_ts(o_tmem, s_tmem + kk * 8, vb + ((kk * 16 * 128) >> 4), idesc_o,
                                accumulate || kk > 0);
                 }
             }
@@ -402,18 +412,19 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
         };
 
         uint32_t kv_it = 0, q_it = 0;
-        uint32_t sp_it[2] = {0, 0};  // S/P rounds per sub-tile so far (s_full / p_full phases)
+        uint32_t sp_it = 0;          // S/P rounds of this sub-tile so far (p_full phase)
+        static_assert(kStages == 2, "vz_it is two scalars");
+        uint32_t vz_it0 = 0, vz_it1 = 0;  // V tiles of each ring slot that needed zeroed rows so far
         Item it;
         for (int k = 0; fetch_item<kCascade>(k, p, bar, pair_start, keys, it); ++k) {
             const int n_max = it.n_max;
             if (n_max == 0) continue;
+            const int n_mine = i ? it.n_kv[1] : it.n_kv[0];
             wait_bar(&bar->q_full, q_it & 1u);
             ++q_it;
             wait_bar(&bar->k_full[kv_it % kStages], (kv_it / kStages) & 1u);
             tc::fence_after_sync();
-#pragma unroll
-            for (int i = 0; i < 2; ++i)
-                if (it.n_kv[i] > 0) issue_s(i, kv_it % kStages);
+            if (n_mine > 0) issue_s(kv_it % kStages);
             if (lane == 0) {
                 tc::commit(&bar->k_empty[kv_it % kStages]);
                 if (n_max == 1) tc::commit(&bar->q_empty);  // the item's last S has been issued
@@ -423,35 +434,41 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
                 const int s = kv_it % kStages;
                 wait_bar(&bar->v_full[s], (kv_it / kStages) & 1u);
                 // Rows at or beyond Lk inside the tile are masked (P = 0), but 0 * NaN would still
-                // poison O: clear those V rows (unwritten cache slots may hold anything).
+                // poison O: clear those V rows (unwritten cache slots may hold anything). Issuer 0
+                // clears, issuer 1 waits for it.
                 const int valid = kCascade ? kTN : it.Lk - j * kTN;  // shared pages are full
                 if (valid < kTN) {
-                    uint8_t* vs = smem + kSmemV + s * kTileBytes;
-                    const int r_lo = max(valid, 0);
-                    for (int idx = r_lo * 16 + lane; idx < kTN * 16; idx += 32) {
-                        const int r = idx >> 4, c = idx & 15;
-                        *reinterpret_cast<int4*>(vs + (c >> 3) * kHalfBytes + r * 128 +
-                                                 (c & 7) * 16) = make_int4(0, 0, 0, 0);
+                    if (i == 0) {
+                        uint8_t* vs = smem + kSmemV + s * kTileBytes;
+                        const int r_lo = max(valid, 0);
+                        for (int idx = r_lo * 16 + lane; idx < kTN * 16; idx += 32) {
+                            const int r = idx >> 4, c = idx & 15;
+                            *reinterpret_cast<int4*>(vs + (c >> 3) * kHalfBytes + r * 128 +
+                                                     (c & 7) * 16) = make_int4(0, 0, 0, 0);
+                        }
+                        fence_proxy_async();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(&bar->v_zeroed[s]);
+                    } else {
+                        wait_bar(&bar->v_zeroed[s], (s ? vz_it1 : vz_it0) & 1u);
                     }
-                    fence_proxy_async();
-                    __syncwarp();
+                    if (s) ++vz_it1; else ++vz_it0;
                 }
                 const int sn = (kv_it + 1) % kStages;
+                // (also when this issuer has no S for the tile: its release below must not land in
+                // the slot's previous phase, and a filled slot proves that phase is over)
                 if (j + 1 < n_max) wait_bar(&bar->k_full[sn], ((kv_it + 1) / kStages) & 1u);
-#pragma unroll
-                for (int i = 0; i < 2; ++i) {
-                    if (j < it.n_kv[i]) {
-                        wait_bar(&bar->p_full[i], sp_it[i] & 1u);
-                        ++sp_it[i];
-                        tc::fence_after_sync();
-                        issue_pv(i, s, j > 0);
-                        if (j == it.n_kv[i] - 1) {
-                            if (lane == 0) tc::commit(&bar->o_full[i]);
-                            __syncwarp();
-                        }
+                if (j < n_mine) {
+                    wait_bar(&bar->p_full[i], sp_it & 1u);
+                    ++sp_it;
+                    tc::fence_after_sync();
+                    issue_pv(s, j > 0);
+                    if (j == n_mine - 1) {
+                        if (lane == 0) tc::commit(&bar->o_full[i]);
+                        __syncwarp();
                     }
-                    if (j + 1 < it.n_kv[i]) issue_s(i, sn);
                 }
+                if (j + 1 < n_mine) issue_s(sn);
                 if (lane == 0) {
                     tc::commit(&bar->v_empty[s]);
                     if (j + 1 < n_max) tc::commit(&bar->k_empty[sn]);
