@@ -188,6 +188,7 @@ struct PrefillParams {
     int32_t prefix_chunks; // split-KV chunks over the shared prefix (grid.y)
     int32_t ws_slot0;      // chunk c writes slot ws_slot0 + c
     int32_t ws_slots;
+    int32_t sched_mode;    // prefill_tc.cu: 0 clc (work stealing), 1 static zig-zag, 2 one item per CTA
 };
 cudaError_t launch_prefill(const PrefillParams& p, cudaStream_t stream);
 

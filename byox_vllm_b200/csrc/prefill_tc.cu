@@ -3,11 +3,16 @@
 // (reference nanovllm/layers/attention.py:72-86), dense and paged-prefix K/V.
 //
 // Work item = 256 query rows (two 128-row sub-tiles) of one (sequence, KV head); a row is a (query
-// token, group head) pair. PERSISTENT: one CTA per SM walks a cost-ordered item list that every
-// CTA derives identically from cu_seqlens in its prologue (pair counts -> scan -> bitonic sort of
-// (KV tiles, item) keys in shared memory, heaviest first); CTA c takes positions c, 2P-1-c, 2P+c,
-// ... of the list (zig-zag), so the shares are balanced without a global counter and nothing has
-// to be allocated or reset. All barriers, the TMEM allocation and the K/V rings live across items:
+// token, group head) pair. PERSISTENT: a CTA walks a cost-ordered item list that every CTA derives
+// identically from cu_seqlens in its prologue (pair counts -> scan -> bitonic sort of (KV tiles,
+// item) keys in shared memory, heaviest first). Which positions of the list a CTA takes:
+//   clc     (default) the grid has one CTA per possible item; a running CTA takes its own
+//           blockIdx first and then STEALS the index of a not-yet-launched CTA with
+//           clusterlaunchcontrol.try_cancel (the hardware work queue of sm_100: dynamic, needs no
+//           global counter, nothing to allocate or reset) until the grid is drained;
+//   static  grid = SM count, CTA c takes positions c, 2P-1-c, 2P+c, ... (zig-zag);
+//   grid    one item per CTA, no stealing (the round-1 behaviour; B200ATTN_PREFILL_SCHED picks).
+// All barriers, the TMEM allocation and the K/V rings live across items:
 // the producer prefetches the next item's first K/V tiles and (once the last S MMA of the current
 // item has retired) its Q tiles while the current item's last softmax / PV / epilogue run.
 // 12 warps (the last warpgroup gives most of its registers to the softmax groups, setmaxnreg):
@@ -15,14 +20,14 @@
 //   warps 4-7   softmax group 1: sub-tile 1
 //   warp  8     TMA producer: Q per item, 128-token K and V tiles through two 2-stage rings
 //               (cp.async.bulk.tensor, SWIZZLE_128B boxes of 64 dims x 128 rows, mbarrier tx)
-//   warps 9,10  MMA issuers (one elected lane each), one per sub-tile; warp 9 owns TMEM
+//   warp  9     MMA issuer (one elected lane) + TMEM owner
 // TMEM (512 columns x 128 lanes of fp32): S0 | S1 | O0 | O1, 128 columns each.
 //   S_i = Q_i . K_j^T      tcgen05.mma SS, M128 N128 K16 x 8, both operands K-major in smem
 //   P_i = exp2(S_i*c - m)  softmax thread reads its S row with tcgen05.ld, writes bf16 P over the
 //                          first 64 columns of S_i with tcgen05.st (fp32 max/sum in registers)
 //   O_i += P_i . V_j       tcgen05.mma TS: A = P from TMEM, B = V tile MN-major in smem
-// Each sub-tile has its own issuing warp (PV_i[j], S_i[j+1], ...), so the tensor pipe works on
-// one sub-tile while the other one is in softmax. tcgen05.mma of one thread executes in
+// The issuer interleaves the two sub-tiles (PV_0[j], S_0[j+1], PV_1[j], S_1[j+1], ...) so the
+// tensor pipe works on one sub-tile while the other one is in softmax. tcgen05.mma executes in
 // issue order, so S_i[j+1] may overwrite P_i[j] as soon as it is issued after PV_i[j]; the same
 // argument carries over item boundaries (S_i[0] of the next item is issued after PV_i[last], and
 // its first PV — which overwrites O_i — only after the softmax group has finished the epilogue
@@ -48,7 +53,7 @@ constexpr int kHalfBytes = 128 * 128;          // [128 rows][64 dims] bf16, 128-
 constexpr int kTileBytes = 2 * kHalfBytes;     // 32 KiB: dims 0-63 | dims 64-127
 constexpr int kProducerWarp = 8;
 constexpr int kMmaWarp = 9;
-constexpr int kTcThreads = 384;                // 3 warpgroups: softmax 0, softmax 1, {TMA, 2 MMA, 1 idle}
+constexpr int kTcThreads = 384;                // 3 warpgroups: softmax 0, softmax 1, {TMA, MMA, 2 idle}
 // setmaxnreg budgets. The pool is what the CTA got at launch (168 regs x 384 threads), not the
 // whole register file: an inc that does not fit waits forever.
 constexpr int kRegsLaunch = 168;
@@ -69,7 +74,9 @@ constexpr int kSmemQ = 0;
 constexpr int kSmemK = kSmemQ + 2 * kTileBytes;
 constexpr int kSmemV = kSmemK + kStages * kTileBytes;
 constexpr int kSmemBar = kSmemV + kStages * kTileBytes;
-constexpr int kSmemPairStart = kSmemBar + 256;                              // int32[kTcMaxSeqs + 1]
+constexpr int kClcSlots = 8;                                               // ticket ring
+constexpr int kSmemClc = kSmemBar + 256;                                    // 16-byte responses
+constexpr int kSmemPairStart = kSmemClc + kClcSlots * 16;                   // int32[kTcMaxSeqs + 1]
 constexpr int kSmemKeys = kSmemPairStart + (kTcMaxSeqs + 1) * 4;            // uint32[kTcMaxItems]
 constexpr int kTcSmemBytes = kSmemKeys + kTcMaxItems * 4 + 1024;
 static_assert(kTcMaxItems <= (1 << kSchedKeyBits), "item index does not fit the key");
@@ -79,8 +86,8 @@ struct Barriers {
     uint64_t q_full, q_empty;
     uint64_t k_full[kStages], k_empty[kStages];
     uint64_t v_full[kStages], v_empty[kStages];
-    uint64_t v_zeroed[kStages];  // issuer 0 -> issuer 1: masked V rows of the slot are cleared
     uint64_t s_full[2], p_full[2], o_full[2];
+    uint64_t sched_full[kClcSlots];  // try_cancel response k+1 has landed in slot k % kClcSlots
     uint32_t tmem_base;
     int32_t num_pairs;   // 256-row pairs over all sequences (items per KV head)
     int32_t use_keys;    // 1: keys[] holds the cost-sorted order; 0: descending item index
@@ -113,11 +120,39 @@ __device__ __forceinline__ int pair_cost(int pair, int Lq, int Lk, int toks_per_
     return vis > 0 ? (vis + kTN - 1) / kTN : 0;
 }
 
-// The k-th item of this CTA (false: no more). Every role of the CTA walks the same sequence.
+// clusterlaunchcontrol: ask the hardware scheduler to cancel a CTA of this grid that has not
+// started yet; the 16-byte response (cancelled? + its blockIdx) lands in shared memory and
+// completes 16 bytes on the mbarrier.
+__device__ __forceinline__ void clc_try_cancel(void* resp, uint64_t* bar) {
+    asm volatile(
+        "clusterlaunchcontrol.try_cancel.async.shared::cta.mbarrier::complete_tx::bytes.b128 "
+        "[%0], [%1];" ::"r"(smem_u32(resp)), "r"(smem_u32(bar))
+        : "memory");
+}
+// Block index handed over by a successful cancellation, -1 when nothing was left to cancel.
+__device__ __forceinline__ int clc_decode(const void* resp) {
+    const ulonglong2 r = *reinterpret_cast<const ulonglong2*>(resp);
+    uint32_t ok, x;
+    asm volatile(
+        "{\n\t.reg .b128 r;\n\t.reg .pred p;\n\t"
+        "mov.b128 r, {%2, %3};\n\t"
+        "clusterlaunchcontrol.query_cancel.is_canceled.pred.b128 p, r;\n\t"
+        "selp.b32 %0, 1, 0, p;\n\t"
+        "mov.b32 %1, 0;\n\t"
+        "@p clusterlaunchcontrol.query_cancel.get_first_ctaid::x.b32.b128 %1, r;\n\t}"
+        : "=r"(ok), "=r"(x)
+        : "l"(r.x), "l"(r.y));
+    return ok ? static_cast<int>(x) : -1;
+}
+
+enum : int { kSchedClc = 0, kSchedStatic = 1, kSchedGrid = 2 };
+
+// The k-th item of this CTA (false: no more). Every role of the CTA walks the same sequence; an
+// item may be empty (n_max == 0: a ticket beyond the real item count, or no visible key).
 template <bool kCascade>
-__device__ __forceinline__ bool fetch_item(int k, const PrefillParams& p, const Barriers* bar,
-                                           const int32_t* pair_start, const uint32_t* keys,
-                                           Item& it) {
+__device__ __forceinline__ bool fetch_item(int k, const PrefillParams& p, Barriers* bar,
+                                           const uint8_t* clc, const int32_t* pair_start,
+                                           const uint32_t* keys, Item& it) {
     if constexpr (kCascade) {
         if (k > 0) return false;
         const PrefixChunks pc = prefix_chunks_of(p.plan[0], p.block_size, p.prefix_chunks);
@@ -136,11 +171,30 @@ __device__ __forceinline__ bool fetch_item(int k, const PrefillParams& p, const 
             it.q_c2[i] = it.row0[i];
         }
     } else {
-        // zig-zag over the cost-ordered list: round k runs left to right, round k+1 right to left
-        const int P = gridDim.x, c = blockIdx.x;
-        const int64_t g = static_cast<int64_t>(k) * P + ((k & 1) ? P - 1 - c : c);
         const int T = bar->num_pairs;
-        if (g >= static_cast<int64_t>(T) * p.num_kv_heads) return false;
+        const int64_t total = static_cast<int64_t>(T) * p.num_kv_heads;
+        int64_t g;
+        if (p.sched_mode == kSchedStatic) {
+            // zig-zag: round k runs left to right over the CTAs, round k+1 right to left
+            const int P = gridDim.x, c = blockIdx.x;
+            g = static_cast<int64_t>(k) * P + ((k & 1) ? P - 1 - c : c);
+            if (g >= total) return false;
+        } else if (k == 0) {
+            g = blockIdx.x;
+        } else {
+            if (p.sched_mode == kSchedGrid) return false;
+            const int slot = (k - 1) % kClcSlots;
+            wait_bar(&bar->sched_full[slot], ((k - 1) / kClcSlots) & 1u);
+            const int t = clc_decode(clc + slot * 16);
+            if (t < 0) return false;  // grid drained
+            g = t;
+        }
+        if (g >= total) {  // surplus ticket (the grid is sized from an upper bound): no rows
+            it.n_kv[0] = it.n_kv[1] = it.n_max = 0;
+            it.kvh = it.q_begin = it.Lq = it.Lk = it.offset = 0;
+            it.row0[0] = it.row0[1] = 0;
+            return true;
+        }
         const int li = static_cast<int>(g / p.num_kv_heads);
         it.kvh = static_cast<int>(g - static_cast<int64_t>(li) * p.num_kv_heads);
         const int t = bar->use_keys ? static_cast<int>(keys[li] & ((1u << kSchedKeyBits) - 1u))
@@ -278,6 +332,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
     uint8_t* smem = reinterpret_cast<uint8_t*>(
         (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
     Barriers* bar = reinterpret_cast<Barriers*>(smem + kSmemBar);
+    const uint8_t* clc = smem + kSmemClc;
     const int32_t* pair_start = reinterpret_cast<const int32_t*>(smem + kSmemPairStart);
     const uint32_t* keys = reinterpret_cast<const uint32_t*>(smem + kSmemKeys);
     const int warp = threadIdx.x >> 5;
@@ -285,14 +340,13 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
 
     if (threadIdx.x == 0) {
         mbar_init(&bar->q_full, 1);
-        mbar_init(&bar->q_empty, 2);  // both issuers
+        mbar_init(&bar->q_empty, 1);
 #pragma unroll
         for (int s = 0; s < kStages; ++s) {
             mbar_init(&bar->k_full[s], 1);
-            mbar_init(&bar->k_empty[s], 2);
+            mbar_init(&bar->k_empty[s], 1);
             mbar_init(&bar->v_full[s], 1);
-            mbar_init(&bar->v_empty[s], 2);
-            mbar_init(&bar->v_zeroed[s], 1);
+            mbar_init(&bar->v_empty[s], 1);
         }
 #pragma unroll
         for (int i = 0; i < 2; ++i) {
@@ -300,6 +354,8 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
             mbar_init(&bar->p_full[i], kTM);
             mbar_init(&bar->o_full[i], 1);
         }
+#pragma unroll
+        for (int t = 0; t < kClcSlots; ++t) mbar_init(&bar->sched_full[t], 1);
         fence_mbar_init();
     }
     if constexpr (!kCascade)
@@ -323,7 +379,14 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
             uint32_t kv_it = 0;   // K/V tiles issued so far (ring position, across items)
             uint32_t q_it = 0;    // items with work so far (Q buffer phase)
             Item it;
-            for (int k = 0; fetch_item<kCascade>(k, p, bar, pair_start, keys, it); ++k) {
+            for (int k = 0; fetch_item<kCascade>(k, p, bar, clc, pair_start, keys, it); ++k) {
+                if (!kCascade && p.sched_mode == kSchedClc) {
+                    // ticket k was good: ask for ticket k + 1 now, it lands while item k runs.
+                    // (Never after a failed request: fetch_item ends the loop on the first one.)
+                    const int slot = k % kClcSlots;
+                    mbar_expect_tx(&bar->sched_full[slot], 16);
+                    clc_try_cancel(smem + kSmemClc + slot * 16, &bar->sched_full[slot]);
+                }
                 if (it.n_max == 0) continue;
                 const int32_t* table =
                     paged ? p.block_tables + static_cast<int64_t>(it.seq) * p.table_row_stride
@@ -367,64 +430,55 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
                 }
             }
         }
-    } else if (warp == kMmaWarp || warp == kMmaWarp + 1) {
-        // ============================ MMA issuers ============================
-        // One issuing warp per sub-tile: the S_i -> P_i -> PV_i chain of a sub-tile only depends on
-        // MMAs of the same warp (tcgen05.mma of one thread execute in issue order), and neither
-        // sub-tile's MMAs queue behind a wait for the other one's softmax. A single issuer also
-        // spends ~60 clk of dependent scalar work per 64-clk MMA (descriptor arithmetic, R2UR):
-        // two warps halve that. K/V ring slots and the Q buffer are released by BOTH issuers
-        // (arrival count 2; an issuer without work for a tile commits at once).
+    } else if (warp == kMmaWarp) {
+        // ============================ MMA issuer ============================
         tc::reg_dec<kRegsControl>();
-        const int i = warp - kMmaWarp;  // sub-tile of this issuer
         constexpr uint32_t idesc_s = tc::idesc_bf16_f32(kTM, kTN, false);
         constexpr uint32_t idesc_o = tc::idesc_bf16_f32(kTM, kHeadDim, true);
         // descriptors of the tile bases; an address offset adds (bytes >> 4) to the start-address
         // field (14 bits of 16-byte units: shared memory is < 256 KiB, no carry out of the field)
-        const uint64_t q_desc = tc::desc_kmajor(smem_u32(smem + kSmemQ) + i * kTileBytes);
+        const uint64_t q_desc = tc::desc_kmajor(smem_u32(smem + kSmemQ));
         const uint64_t k_desc = tc::desc_kmajor(smem_u32(smem + kSmemK));
         const uint64_t v_desc = tc::desc_mnmajor(smem_u32(smem + kSmemV), kHalfBytes);
-        const uint32_t s_tmem = tmem + i * kTN;
-        const uint32_t o_tmem = tmem + 2 * kTN + i * kHeadDim;
 
-        auto issue_s = [&](int stage) {  // S_i = Q_i . K^T   (head_dim 128 = 2 halves x 4)
+        auto issue_s = [&](int i, int stage) {  // S_i = Q_i . K^T   (head_dim 128 = 2 halves x 4)
             if (lane == 0) {
-                const uint64_t kb = k_desc + static_cast<uint64_t>((stage * kTileBytes) >> 4);
+                const uint64_t a0 = q_desc + static_cast<uint64_t>((i * kTileBytes) >> 4);
+                const uint64_t b0 = k_desc + static_cast<uint64_t>((stage * kTileBytes) >> 4);
 #pragma unroll
                 for (int kk = 0; kk < 8; ++kk) {
                     const uint64_t off = ((kk >> 2) * kHalfBytes + (kk & 3) * 32) >> 4;
-                    tc::mma_ss(s_tmem, q_desc + off, kb + off, idesc_s, kk > 0);
+                    tc::mma_ss(tmem + i * kTN, a0 + off, b0 + off, idesc_s, kk > 0);
                 }
                 tc::commit(&bar->s_full[i]);
             }
             __syncwarp();
         };
-        auto issue_pv = [&](int stage, bool accumulate) {  // O_i (+)= P_i . V
+        auto issue_pv = [&](int i, int stage, bool accumulate) {  // O_i (+)= P_i . V
             if (lane == 0) {
-                const uint64_t vb = v_desc + static_cast<uint64_t>((stage * kTileBytes) >> 4);
+                const uint64_t b0 = v_desc + static_cast<uint64_t>((stage * kTileBytes) >> 4);
 #pragma unroll
                 for (int kk = 0; kk < 8; ++kk) {  // 16 tokens per instruction
-                    tc::mma_ts(o_tmem, s_tmem + kk * 8, vb + ((kk * 16 * 128) >> 4), idesc_o,
-                               accumulate || kk > 0);
+                    tc::mma_ts(tmem + 2 * kTN + i * kHeadDim, tmem + i * kTN + kk * 8,
+                               b0 + ((kk * 16 * 128) >> 4), idesc_o, accumulate || kk > 0);
                 }
             }
             __syncwarp();
         };
 
         uint32_t kv_it = 0, q_it = 0;
-        uint32_t sp_it = 0;          // S/P rounds of this sub-tile so far (p_full phase)
-        static_assert(kStages == 2, "vz_it is two scalars");
-        uint32_t vz_it0 = 0, vz_it1 = 0;  // V tiles of each ring slot that needed zeroed rows so far
+        uint32_t sp_it[2] = {0, 0};  // S/P rounds per sub-tile so far (s_full / p_full phases)
         Item it;
-        for (int k = 0; fetch_item<kCascade>(k, p, bar, pair_start, keys, it); ++k) {
+        for (int k = 0; fetch_item<kCascade>(k, p, bar, clc, pair_start, keys, it); ++k) {
             const int n_max = it.n_max;
             if (n_max == 0) continue;
-            const int n_mine = i ? it.n_kv[1] : it.n_kv[0];
             wait_bar(&bar->q_full, q_it & 1u);
             ++q_it;
             wait_bar(&bar->k_full[kv_it % kStages], (kv_it / kStages) & 1u);
             tc::fence_after_sync();
-            if (n_mine > 0) issue_s(kv_it % kStages);
+#pragma unroll
+            for (int i = 0; i < 2; ++i)
+                if (it.n_kv[i] > 0) issue_s(i, kv_it % kStages);
             if (lane == 0) {
                 tc::commit(&bar->k_empty[kv_it % kStages]);
                 if (n_max == 1) tc::commit(&bar->q_empty);  // the item's last S has been issued
@@ -434,41 +488,35 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
                 const int s = kv_it % kStages;
                 wait_bar(&bar->v_full[s], (kv_it / kStages) & 1u);
                 // Rows at or beyond Lk inside the tile are masked (P = 0), but 0 * NaN would still
-                // poison O: clear those V rows (unwritten cache slots may hold anything). Issuer 0
-                // clears, issuer 1 waits for it.
+                // poison O: clear those V rows (unwritten cache slots may hold anything).
                 const int valid = kCascade ? kTN : it.Lk - j * kTN;  // shared pages are full
                 if (valid < kTN) {
-                    if (i == 0) {
-                        uint8_t* vs = smem + kSmemV + s * kTileBytes;
-                        const int r_lo = max(valid, 0);
-                        for (int idx = r_lo * 16 + lane; idx < kTN * 16; idx += 32) {
-                            const int r = idx >> 4, c = idx & 15;
-                            *reinterpret_cast<int4*>(vs + (c >> 3) * kHalfBytes + r * 128 +
-                                                     (c & 7) * 16) = make_int4(0, 0, 0, 0);
-                        }
-                        fence_proxy_async();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(&bar->v_zeroed[s]);
-                    } else {
-                        wait_bar(&bar->v_zeroed[s], (s ? vz_it1 : vz_it0) & 1u);
+                    uint8_t* vs = smem + kSmemV + s * kTileBytes;
+                    const int r_lo = max(valid, 0);
+                    for (int idx = r_lo * 16 + lane; idx < kTN * 16; idx += 32) {
+                        const int r = idx >> 4, c = idx & 15;
+                        *reinterpret_cast<int4*>(vs + (c >> 3) * kHalfBytes + r * 128 +
+                                                 (c & 7) * 16) = make_int4(0, 0, 0, 0);
                     }
-                    if (s) ++vz_it1; else ++vz_it0;
+                    fence_proxy_async();
+                    __syncwarp();
                 }
                 const int sn = (kv_it + 1) % kStages;
-                // (also when this issuer has no S for the tile: its release below must not land in
-                // the slot's previous phase, and a filled slot proves that phase is over)
                 if (j + 1 < n_max) wait_bar(&bar->k_full[sn], ((kv_it + 1) / kStages) & 1u);
-                if (j < n_mine) {
-                    wait_bar(&bar->p_full[i], sp_it & 1u);
-                    ++sp_it;
-                    tc::fence_after_sync();
-                    issue_pv(s, j > 0);
-                    if (j == n_mine - 1) {
-                        if (lane == 0) tc::commit(&bar->o_full[i]);
-                        __syncwarp();
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    if (j < it.n_kv[i]) {
+                        wait_bar(&bar->p_full[i], sp_it[i] & 1u);
+                        ++sp_it[i];
+                        tc::fence_after_sync();
+                        issue_pv(i, s, j > 0);
+                        if (j == it.n_kv[i] - 1) {
+                            if (lane == 0) tc::commit(&bar->o_full[i]);
+                            __syncwarp();
+                        }
                     }
+                    if (j + 1 < it.n_kv[i]) issue_s(i, sn);
                 }
-                if (j + 1 < n_mine) issue_s(sn);
                 if (lane == 0) {
                     tc::commit(&bar->v_empty[s]);
                     if (j + 1 < n_max) tc::commit(&bar->k_empty[sn]);
@@ -489,7 +537,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
         uint32_t sp_it = 0;   // S/P rounds of this sub-tile so far
         uint32_t o_it = 0;    // items of this sub-tile with work so far
         Item it;
-        for (int k = 0; fetch_item<kCascade>(k, p, bar, pair_start, keys, it); ++k) {
+        for (int k = 0; fetch_item<kCascade>(k, p, bar, clc, pair_start, keys, it); ++k) {
         // (selects, not it.row0[i]: a runtime index would push the item into local memory)
         const int row = (i ? it.row0[1] : it.row0[0]) + (r >> g_shift);  // token (cascade: batch row)
         const int head = it.kvh * p.group + (r & (p.group - 1));
@@ -604,7 +652,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
             }
         } else {
         // ---- epilogue: O / l -> bf16 -> global (row-predicated 16-byte stores) ----
-        const bool row_ok = row < it.Lq;
+        const bool row_ok = row < it.Lq;  // (surplus ticket: Lq = 0)
         uint8_t* orow_g = static_cast<uint8_t*>(p.out) +
                           ((static_cast<int64_t>(it.q_begin) + row) * p.num_q_heads + head) * 256;
         if (n > 0) {
@@ -720,17 +768,31 @@ int device_sm_count() {
 
 constexpr int kDefaultExpEmu = 0;
 
-cudaError_t launch_prefill_tc(const PrefillParams& p, const CUtensorMap& q_map,
+// B200ATTN_PREFILL_SCHED=clc|static|grid (default clc), see the header comment.
+int sched_mode_from_env() {
+    static int v = [] {
+        const char* e = std::getenv("B200ATTN_PREFILL_SCHED");
+        if (e && e[0] == 's') return static_cast<int>(kSchedStatic);
+        if (e && e[0] == 'g') return static_cast<int>(kSchedGrid);
+        return static_cast<int>(kSchedClc);
+    }();
+    return v;
+}
+
+cudaError_t launch_prefill_tc(const PrefillParams& p_in, const CUtensorMap& q_map,
                               const CUtensorMap& k_map, const CUtensorMap& v_map,
                               cudaStream_t stream) {
-    // Persistent: one CTA per SM (1 CTA/SM by shared memory), never more CTAs than items can exist
-    // (256-row pairs over all sequences <= total_q / tokens-per-pair + num_seqs, per KV head).
+    // Items = 256-row pairs over all sequences (<= total_q / tokens-per-pair + num_seqs) x KV
+    // heads; the exact count is device data. clc / grid: one CTA per possible item (surplus
+    // tickets are empty); static: one CTA per SM.
+    PrefillParams p = p_in;
+    p.sched_mode = sched_mode_from_env();
     const int toks_per_pair = 2 * kTM / p.group;
     const int64_t bound =
         (static_cast<int64_t>(p.total_q) / toks_per_pair + p.num_seqs) * p.num_kv_heads;
-    const int sms = device_sm_count();
-    const int ctas = static_cast<int>(bound < sms ? bound : sms);
-    dim3 grid(ctas > 0 ? ctas : 1, 1, 1);
+    int64_t ctas = bound;
+    if (p.sched_mode == kSchedStatic && ctas > device_sm_count()) ctas = device_sm_count();
+    dim3 grid(static_cast<unsigned>(ctas > 0 ? ctas : 1), 1, 1);
     return launch_tc_emu<false>(exp_emu_from_env(kDefaultExpEmu), grid, p, q_map, k_map, v_map,
                                 stream);
 }
