@@ -74,7 +74,7 @@ constexpr int kSmemQ = 0;
 constexpr int kSmemK = kSmemQ + 2 * kTileBytes;
 constexpr int kSmemV = kSmemK + kStages * kTileBytes;
 constexpr int kSmemBar = kSmemV + kStages * kTileBytes;
-constexpr int kClcSlots = 8;                                               // ticket ring
+constexpr int kClcSlots = 4;                                               // ticket ring
 constexpr int kSmemClc = kSmemBar + 256;                                    // 16-byte responses
 constexpr int kSmemPairStart = kSmemClc + kClcSlots * 16;                   // int32[kTcMaxSeqs + 1]
 constexpr int kSmemKeys = kSmemPairStart + (kTcMaxSeqs + 1) * 4;            // uint32[kTcMaxItems]
@@ -87,18 +87,23 @@ struct Barriers {
     uint64_t k_full[kStages], k_empty[kStages];
     uint64_t v_full[kStages], v_empty[kStages];
     uint64_t s_full[2], p_full[2], o_full[2];
-    uint64_t sched_full[kClcSlots];  // try_cancel response k+1 has landed in slot k % kClcSlots
+    uint64_t sched_full[kClcSlots];   // try_cancel response k+1 has landed in slot k % kClcSlots
+    uint64_t sched_empty[kClcSlots];  // ... and the issuer + the 8 softmax warps have read it
     uint32_t tmem_base;
     int32_t num_pairs;   // 256-row pairs over all sequences (items per KV head)
     int32_t use_keys;    // 1: keys[] holds the cost-sorted order; 0: descending item index
 };
+constexpr int kTicketReaders = 1 + kProducerWarp;  // MMA warp + softmax warps (lane 0 arrives)
 static_assert(sizeof(Barriers) <= 256, "barrier block overflows its shared-memory slot");
 
-// Bounded spin: a protocol bug traps (launch error) instead of hanging the GPU.
+// Bounded wait: a protocol bug traps (launch error) after ~2 s instead of hanging the GPU
+// (mbarrier.try_wait itself may block for a while, so the bound is on the clock, not on spins).
 __device__ __forceinline__ void wait_bar(uint64_t* bar, uint32_t parity) {
+    if (mbar_try_wait(bar, parity)) return;
+    const long long t0 = clock64();
     uint32_t spins = 0;
     while (!mbar_try_wait(bar, parity)) {
-        if (++spins > (1u << 28)) __trap();
+        if ((++spins & 1023u) == 0 && clock64() - t0 > 4000000000LL) __trap();
     }
 }
 
@@ -149,7 +154,9 @@ enum : int { kSchedClc = 0, kSchedStatic = 1, kSchedGrid = 2 };
 
 // The k-th item of this CTA (false: no more). Every role of the CTA walks the same sequence; an
 // item may be empty (n_max == 0: a ticket beyond the real item count, or no visible key).
-template <bool kCascade>
+// kReader: the calling WARP is one of the kTicketReaders consumers of the ticket ring (all its
+// lanes call; lane 0 hands the slot back to the producer once every lane has decoded it).
+template <bool kCascade, bool kReader>
 __device__ __forceinline__ bool fetch_item(int k, const PrefillParams& p, Barriers* bar,
                                            const uint8_t* clc, const int32_t* pair_start,
                                            const uint32_t* keys, Item& it) {
@@ -186,6 +193,10 @@ __device__ __forceinline__ bool fetch_item(int k, const PrefillParams& p, Barrie
             const int slot = (k - 1) % kClcSlots;
             wait_bar(&bar->sched_full[slot], ((k - 1) / kClcSlots) & 1u);
             const int t = clc_decode(clc + slot * 16);
+            if constexpr (kReader) {
+                __syncwarp();
+                if ((threadIdx.x & 31) == 0) mbar_arrive(&bar->sched_empty[slot]);
+            }
             if (t < 0) return false;  // grid drained
             g = t;
         }
@@ -355,7 +366,10 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
             mbar_init(&bar->o_full[i], 1);
         }
 #pragma unroll
-        for (int t = 0; t < kClcSlots; ++t) mbar_init(&bar->sched_full[t], 1);
+        for (int t = 0; t < kClcSlots; ++t) {
+            mbar_init(&bar->sched_full[t], 1);
+            mbar_init(&bar->sched_empty[t], kTicketReaders);
+        }
         fence_mbar_init();
     }
     if constexpr (!kCascade)
@@ -379,11 +393,15 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
             uint32_t kv_it = 0;   // K/V tiles issued so far (ring position, across items)
             uint32_t q_it = 0;    // items with work so far (Q buffer phase)
             Item it;
-            for (int k = 0; fetch_item<kCascade>(k, p, bar, clc, pair_start, keys, it); ++k) {
+            for (int k = 0; fetch_item<kCascade, false>(k, p, bar, clc, pair_start, keys, it); ++k) {
                 if (!kCascade && p.sched_mode == kSchedClc) {
                     // ticket k was good: ask for ticket k + 1 now, it lands while item k runs.
                     // (Never after a failed request: fetch_item ends the loop on the first one.)
+                    // The slot's previous ticket must have been read by every consumer: empty
+                    // items couple the roles through nothing else.
                     const int slot = k % kClcSlots;
+                    if (k >= kClcSlots)
+                        wait_bar(&bar->sched_empty[slot], ((k / kClcSlots) - 1) & 1u);
                     mbar_expect_tx(&bar->sched_full[slot], 16);
                     clc_try_cancel(smem + kSmemClc + slot * 16, &bar->sched_full[slot]);
                 }
@@ -469,7 +487,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
         uint32_t kv_it = 0, q_it = 0;
         uint32_t sp_it[2] = {0, 0};  // S/P rounds per sub-tile so far (s_full / p_full phases)
         Item it;
-        for (int k = 0; fetch_item<kCascade>(k, p, bar, clc, pair_start, keys, it); ++k) {
+        for (int k = 0; fetch_item<kCascade, true>(k, p, bar, clc, pair_start, keys, it); ++k) {
             const int n_max = it.n_max;
             if (n_max == 0) continue;
             wait_bar(&bar->q_full, q_it & 1u);
@@ -537,7 +555,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
         uint32_t sp_it = 0;   // S/P rounds of this sub-tile so far
         uint32_t o_it = 0;    // items of this sub-tile with work so far
         Item it;
-        for (int k = 0; fetch_item<kCascade>(k, p, bar, clc, pair_start, keys, it); ++k) {
+        for (int k = 0; fetch_item<kCascade, true>(k, p, bar, clc, pair_start, keys, it); ++k) {
         // (selects, not it.row0[i]: a runtime index would push the item into local memory)
         const int row = (i ? it.row0[1] : it.row0[0]) + (r >> g_shift);  // token (cascade: batch row)
         const int head = it.kvh * p.group + (r & (p.group - 1));
