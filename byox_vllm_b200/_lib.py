@@ -32,6 +32,7 @@ PROTOTYPES = {
     "b200attn_decode_pick_splits": (_i32, [_i32, _i32, _i32, _i32, _i32]),
     "b200attn_decode_partition_host": (_i32, [_vp, _i32, _i32, _i32, _i32, _i32, _vp, _i32]),
     "b200attn_debug_decode_trace": (None, [_vp]),
+    "b200attn_debug_prefill_trace": (None, [_vp]),
     "b200attn_set_decode_overlap": (_i32, [_i32]),
     "b200attn_decode_workspace_bytes": (_sz, [_i32, _i32, _i32, _i32, _i32]),
     "b200attn_decode": (

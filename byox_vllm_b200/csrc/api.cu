@@ -167,6 +167,7 @@ struct SplitCounters {
 };
 static SplitCounters g_split_counters[64];
 static unsigned long long* g_decode_trace = nullptr;  // b200attn_debug_decode_trace
+static unsigned long long* g_prefill_trace = nullptr; // b200attn_debug_prefill_trace
 static std::atomic<int> g_decode_overlap{0};          // b200attn_set_decode_overlap
 static std::mutex g_split_counters_mu;
 
@@ -566,6 +567,7 @@ int b200attn_prefill_varlen(const void* q, const void* key, int64_t key_row_stri
     p.group = num_q_heads / num_kv_heads;
     p.block_size = block_size;
     p.scale_log2 = scale * 1.4426950408889634f;
+    p.trace = g_prefill_trace;
     // Kernel choice from host-visible sizes only. The tcgen05 kernel works on pairs of 128-row
     // tiles of (token, group head) rows and 128-token KV tiles: it needs pages that are multiples
     // of 128 tokens and a GQA group that divides 128.
@@ -745,6 +747,10 @@ int b200attn_set_decode_overlap(int on) {
 
 void b200attn_debug_decode_trace(void* stamps) {
     g_decode_trace = static_cast<unsigned long long*>(stamps);
+}
+
+void b200attn_debug_prefill_trace(void* stamps) {
+    g_prefill_trace = static_cast<unsigned long long*>(stamps);
 }
 
 int b200attn_set_split_counters(void* counters, int64_t count) {

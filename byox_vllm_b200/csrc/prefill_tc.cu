@@ -324,7 +324,11 @@ __device__ void build_schedule(const PrefillParams& p, Barriers* bar, int32_t* p
 //   epilogue writes normalised fp32 partials + log2-sum-exp for the decode merge.
 // kEmu of every 4 exponential pairs are evaluated on the FMA pipe (tc::exp2_fma_pipe), the rest on
 // the MUFU.
-template <bool kCascade, int kEmu>
+// kTrace: debug build (b200attn_debug_prefill_trace) — the first kTraceCtas CTAs stamp clock64 at
+// the phase boundaries of their first kTraceSteps tile steps: stream 0/1 = softmax group 0/1
+// {S ready, S row loaded, P computed, P signalled}, stream 2 = issuer {tiles ready, P_0 ready,
+// P_1 ready, step issued}; layout [cta][stream][step][4] uint64 (tools/trace_prefill.py).
+template <bool kCascade, int kEmu, bool kTrace = false>
 __global__ void __launch_bounds__(kTcThreads, 1)
 prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
                   const __grid_constant__ CUtensorMap k_map,
@@ -380,6 +384,12 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
     __syncthreads();
     tc::fence_after_sync();
     const uint32_t tmem = bar->tmem_base;
+    unsigned long long* trace = nullptr;  // this CTA's stamps (kTrace only)
+    if constexpr (kTrace) {
+        if (p.trace != nullptr && blockIdx.x < kTraceCtas)
+            trace = p.trace + static_cast<size_t>(blockIdx.x) * 3 * kTraceSteps * 4;
+    }
+    uint32_t tr_step = 0;  // tile steps this role has stamped
 
     // setmaxnreg sits inside each role branch so ptxas budgets every role separately.
     if (warp == kProducerWarp) {
@@ -504,6 +514,12 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
             __syncwarp();
             for (int j = 0; j < n_max; ++j, ++kv_it) {
                 const int s = kv_it % kStages;
+                unsigned long long* tr = nullptr;
+                if constexpr (kTrace) {
+                    if (trace != nullptr && lane == 0 && tr_step < kTraceSteps)
+                        tr = trace + (2 * kTraceSteps + tr_step) * 4;
+                    ++tr_step;
+                }
                 wait_bar(&bar->v_full[s], (kv_it / kStages) & 1u);
                 // Rows at or beyond Lk inside the tile are masked (P = 0), but 0 * NaN would still
                 // poison O: clear those V rows (unwritten cache slots may hold anything).
@@ -521,10 +537,12 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
                 }
                 const int sn = (kv_it + 1) % kStages;
                 if (j + 1 < n_max) wait_bar(&bar->k_full[sn], ((kv_it + 1) / kStages) & 1u);
+                if (kTrace && tr) tr[0] = clock64();
 #pragma unroll
                 for (int i = 0; i < 2; ++i) {
                     if (j < it.n_kv[i]) {
                         wait_bar(&bar->p_full[i], sp_it[i] & 1u);
+                        if (kTrace && tr) tr[1 + i] = clock64();
                         ++sp_it[i];
                         tc::fence_after_sync();
                         issue_pv(i, s, j > 0);
@@ -540,6 +558,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
                     if (j + 1 < n_max) tc::commit(&bar->k_empty[sn]);
                     if (j + 2 == n_max) tc::commit(&bar->q_empty);  // last S issued in this step
                 }
+                if (kTrace && tr) tr[3] = clock64();
                 __syncwarp();
             }
         }
@@ -565,10 +584,18 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
         float l = 0.f;
 
         for (int j = 0; j < n; ++j, ++sp_it) {
+            unsigned long long* tr = nullptr;
+            if constexpr (kTrace) {
+                if (trace != nullptr && r == 0 && tr_step < kTraceSteps)
+                    tr = trace + (i * kTraceSteps + tr_step) * 4;
+                ++tr_step;
+            }
             wait_bar(&bar->s_full[i], sp_it & 1u);
             tc::fence_after_sync();
+            if (kTrace && tr) tr[0] = clock64();
             uint32_t sr[128];
             tc::tmem_ld128(s_tmem, sr);
+            if (kTrace && tr) tr[1] = clock64();
 
             const int key0 = j * kTN;
             // columns <= lim are visible (cascade: every key of the shared prefix is)
@@ -634,8 +661,10 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
             }
             l += (ls[0].x + ls[0].y) + (ls[1].x + ls[1].y);
             tc::wait_st();
+            if (kTrace && tr) tr[2] = clock64();
             tc::fence_before_sync();
             mbar_arrive(&bar->p_full[i]);
+            if (kTrace && tr) tr[3] = clock64();
         }
 
         if constexpr (kCascade) {
@@ -736,8 +765,9 @@ int exp_emu_from_env(int dflt) {
 }
 
 constexpr int kMaxDevices = 64;
+constexpr int kDefaultExpEmu = 0;
 
-template <bool kCascade, int kEmu>
+template <bool kCascade, int kEmu, bool kTrace = false>
 cudaError_t launch_tc(dim3 grid, const PrefillParams& p, const CUtensorMap& q_map,
                       const CUtensorMap& k_map, const CUtensorMap& v_map, cudaStream_t stream) {
     // the opt-in shared-memory size is a per-device function attribute
@@ -745,14 +775,14 @@ cudaError_t launch_tc(dim3 grid, const PrefillParams& p, const CUtensorMap& q_ma
     int dev = 0;
     if (cudaError_t e = cudaGetDevice(&dev); e != cudaSuccess) return e;
     if (dev < 0 || dev >= kMaxDevices || !configured[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(prefill_tc_kernel<kCascade, kEmu>,
+        cudaError_t e = cudaFuncSetAttribute(prefill_tc_kernel<kCascade, kEmu, kTrace>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              kTcSmemBytes);
         if (e != cudaSuccess) return e;
         if (dev >= 0 && dev < kMaxDevices) configured[dev] = true;
     }
-    prefill_tc_kernel<kCascade, kEmu><<<grid, kTcThreads, kTcSmemBytes, stream>>>(q_map, k_map,
-                                                                                  v_map, p);
+    prefill_tc_kernel<kCascade, kEmu, kTrace><<<grid, kTcThreads, kTcSmemBytes, stream>>>(
+        q_map, k_map, v_map, p);
     count_launch();
     return cudaGetLastError();
 }
@@ -784,8 +814,6 @@ int device_sm_count() {
 
 }  // namespace
 
-constexpr int kDefaultExpEmu = 0;
-
 // B200ATTN_PREFILL_SCHED=clc|static|grid (default clc), see the header comment.
 int sched_mode_from_env() {
     static int v = [] {
@@ -811,6 +839,8 @@ cudaError_t launch_prefill_tc(const PrefillParams& p_in, const CUtensorMap& q_ma
     int64_t ctas = bound;
     if (p.sched_mode == kSchedStatic && ctas > device_sm_count()) ctas = device_sm_count();
     dim3 grid(static_cast<unsigned>(ctas > 0 ? ctas : 1), 1, 1);
+    if (p.trace != nullptr)  // debug build, default exponentials only
+        return launch_tc<false, kDefaultExpEmu, true>(grid, p, q_map, k_map, v_map, stream);
     return launch_tc_emu<false>(exp_emu_from_env(kDefaultExpEmu), grid, p, q_map, k_map, v_map,
                                 stream);
 }

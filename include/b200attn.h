@@ -140,6 +140,12 @@ int b200attn_set_decode_overlap(int on);
  * NULL (the default) restores the product kernel. Not thread-safe, not for production. */
 void b200attn_debug_decode_trace(void* stamps);
 
+/* Debug only: with a device buffer of 8 CTAs x 3 streams x 128 steps x 4 uint64 registered,
+ * b200attn_prefill_varlen launches an instrumented build of the tcgen05 kernel whose first 8 CTAs
+ * stamp their SM clock at the phase boundaries of every tile step (tools/trace_prefill.py); NULL
+ * (the default) restores the product kernel. Not thread-safe, not for production. */
+void b200attn_debug_prefill_trace(void* stamps);
+
 /* Bytes of fp32 workspace the decode entry points need: two partial-piece slots per work item that
  * can hold a cut row when num_splits > 1 (at most num_splits + num_q_heads items), plus batch * num_q_heads * prefix_chunks shared-prefix partials for the cascade
  * (prefix_chunks = 0 otherwise). 0 when num_splits <= 1 and prefix_chunks == 0. */
