@@ -86,7 +86,7 @@ struct Barriers {
     uint64_t q_full, q_empty;
     uint64_t k_full[kStages], k_empty[kStages];
     uint64_t v_full[kStages], v_empty[kStages];
-    uint64_t s_full[2], p_full[2], o_full[2];
+    uint64_t s_full[2], p_half[2], p_full[2], o_full[2];
     uint64_t sched_full[kClcSlots];   // try_cancel response k+1 has landed in slot k % kClcSlots
     uint64_t sched_empty[kClcSlots];  // ... and the issuer + the 8 softmax warps have read it
     uint32_t tmem_base;
@@ -327,7 +327,7 @@ __device__ void build_schedule(const PrefillParams& p, Barriers* bar, int32_t* p
 // kTrace: debug build (b200attn_debug_prefill_trace) — the first kTraceCtas CTAs stamp clock64 at
 // the phase boundaries of their first kTraceSteps tile steps: stream 0/1 = softmax group 0/1
 // {S ready, S row loaded, P computed, P signalled}, stream 2 = issuer {tiles ready, P_0 ready,
-// P_1 ready, step issued}; layout [cta][stream][step][4] uint64 (tools/trace_prefill.py).
+// PV_0 issued, S_0 of the next tile issued}; layout [cta][stream][step][4] uint64 (tools/trace_prefill.py).
 template <bool kCascade, int kEmu, bool kTrace = false>
 __global__ void __launch_bounds__(kTcThreads, 1)
 prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
@@ -366,6 +366,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
 #pragma unroll
         for (int i = 0; i < 2; ++i) {
             mbar_init(&bar->s_full[i], 1);
+            mbar_init(&bar->p_half[i], kTM);
             mbar_init(&bar->p_full[i], kTM);
             mbar_init(&bar->o_full[i], 1);
         }
@@ -482,12 +483,15 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
             }
             __syncwarp();
         };
-        auto issue_pv = [&](int i, int stage, bool accumulate) {  // O_i (+)= P_i . V
+        // O_i (+)= P_i . V over the tokens [16 * kk0, 16 * kk0 + 64) of the tile
+        auto issue_pv = [&](int i, int stage, bool accumulate, int kk0) {
             if (lane == 0) {
-                const uint64_t b0 = v_desc + static_cast<uint64_t>((stage * kTileBytes) >> 4);
+                const uint64_t b0 = v_desc + static_cast<uint64_t>((stage * kTileBytes) >> 4) +
+                                    static_cast<uint64_t>((kk0 * 16 * 128) >> 4);
+                const uint32_t a0 = tmem + i * kTN + kk0 * 8;
 #pragma unroll
-                for (int kk = 0; kk < 8; ++kk) {  // 16 tokens per instruction
-                    tc::mma_ts(tmem + 2 * kTN + i * kHeadDim, tmem + i * kTN + kk * 8,
+                for (int kk = 0; kk < 4; ++kk) {  // 16 tokens per instruction
+                    tc::mma_ts(tmem + 2 * kTN + i * kHeadDim, a0 + kk * 8,
                                b0 + ((kk * 16 * 128) >> 4), idesc_o, accumulate || kk > 0);
                 }
             }
@@ -541,24 +545,30 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
 #pragma unroll
                 for (int i = 0; i < 2; ++i) {
                     if (j < it.n_kv[i]) {
+                        // P arrives in two halves of 64 tokens: the PV MMAs of the first half are
+                        // issued while the softmax group still computes the second one
+                        wait_bar(&bar->p_half[i], sp_it[i] & 1u);
+                        if (kTrace && tr && i == 0) tr[1] = clock64();
+                        tc::fence_after_sync();
+                        issue_pv(i, s, j > 0, 0);
                         wait_bar(&bar->p_full[i], sp_it[i] & 1u);
-                        if (kTrace && tr) tr[1 + i] = clock64();
                         ++sp_it[i];
                         tc::fence_after_sync();
-                        issue_pv(i, s, j > 0);
+                        issue_pv(i, s, true, 4);
+                        if (kTrace && tr && i == 0) tr[2] = clock64();
                         if (j == it.n_kv[i] - 1) {
                             if (lane == 0) tc::commit(&bar->o_full[i]);
                             __syncwarp();
                         }
                     }
                     if (j + 1 < it.n_kv[i]) issue_s(i, sn);
+                    if (kTrace && tr && i == 0) tr[3] = clock64();
                 }
                 if (lane == 0) {
                     tc::commit(&bar->v_empty[s]);
                     if (j + 1 < n_max) tc::commit(&bar->k_empty[sn]);
                     if (j + 2 == n_max) tc::commit(&bar->q_empty);  // last S issued in this step
                 }
-                if (kTrace && tr) tr[3] = clock64();
                 __syncwarp();
             }
         }
@@ -658,6 +668,11 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
                     pr[t] = pack_bf16x2(x.x, x.y);
                 }
                 tc::tmem_st32(s_tmem + hh * 32, pr);
+                if (hh == 0) {  // first 64 tokens of P are in TMEM: their PV MMAs may start
+                    tc::wait_st();
+                    tc::fence_before_sync();
+                    mbar_arrive(&bar->p_half[i]);
+                }
             }
             l += (ls[0].x + ls[0].y) + (ls[1].x + ls[1].y);
             tc::wait_st();

@@ -2,7 +2,7 @@
 
 The first 8 CTAs stamp their SM clock at the phase boundaries of every tile step, per role:
   softmax group i : S ready | S row loaded | P computed + stored | P signalled
-  issuer          : tiles ready | P_0 ready | P_1 ready | step issued
+  issuer          : tiles ready | P_0 ready | PV_0 issued | S_0 of the next tile issued
 This prints, per shape, the median clocks of each phase and of the step period, i.e. where the
 S -> softmax -> PV chain spends its time.
 
@@ -88,8 +88,8 @@ def main():
             rec["issuer"] = {
                 "steps": int(ok.sum()),
                 "wait_P0": med((m[:, :, 1] - m[:, :, 0])[ok]),
-                "issue0_then_wait_P1": med((m[:, :, 2] - m[:, :, 1])[ok]),
-                "issue1": med((m[:, :, 3] - m[:, :, 2])[ok]),
+                "issue_PV0_8mma": med((m[:, :, 2] - m[:, :, 1])[ok]),
+                "issue_S0_8mma_commit": med((m[:, :, 3] - m[:, :, 2])[ok]),
                 "period": med((m[:, 1:, 0] - m[:, :-1, 0])[ok[:, 1:] & ok[:, :-1]]),
             }
             # stagger between the two softmax groups: S ready of group 1 minus S ready of group 0
