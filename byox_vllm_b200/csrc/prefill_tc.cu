@@ -41,6 +41,7 @@
 #include "tcgen05.cuh"
 
 #include <cstdlib>
+#include <type_traits>
 
 namespace b200 {
 
@@ -70,6 +71,7 @@ constexpr float kRescaleThreshold = 8.0f;      // log2 domain
 constexpr int kSchedKeyBits = 13;                       // item index inside a key
 constexpr uint32_t kSchedCostMax = (1u << (32 - kSchedKeyBits)) - 1;
 
+constexpr uint32_t kSmemWindowBase = 0x400;  // first 1 KiB of the window is reserved by the system
 constexpr int kSmemQ = 0;
 constexpr int kSmemK = kSmemQ + 2 * kTileBytes;
 constexpr int kSmemV = kSmemK + kStages * kTileBytes;
@@ -86,7 +88,7 @@ struct Barriers {
     uint64_t q_full, q_empty;
     uint64_t k_full[kStages], k_empty[kStages];
     uint64_t v_full[kStages], v_empty[kStages];
-    uint64_t s_full[2], p_half[2], p_full[2], o_full[2];
+    uint64_t s_full[2], p_full[2], o_full[2];
     uint64_t sched_full[kClcSlots];   // try_cancel response k+1 has landed in slot k % kClcSlots
     uint64_t sched_empty[kClcSlots];  // ... and the issuer + the 8 softmax warps have read it
     uint32_t tmem_base;
@@ -366,7 +368,6 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
 #pragma unroll
         for (int i = 0; i < 2; ++i) {
             mbar_init(&bar->s_full[i], 1);
-            mbar_init(&bar->p_half[i], kTM);
             mbar_init(&bar->p_full[i], kTM);
             mbar_init(&bar->o_full[i], 1);
         }
@@ -464,39 +465,69 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
         tc::reg_dec<kRegsControl>();
         constexpr uint32_t idesc_s = tc::idesc_bf16_f32(kTM, kTN, false);
         constexpr uint32_t idesc_o = tc::idesc_bf16_f32(kTM, kHeadDim, true);
-        // descriptors of the tile bases; an address offset adds (bytes >> 4) to the start-address
-        // field (14 bits of 16-byte units: shared memory is < 256 KiB, no carry out of the field)
-        const uint64_t q_desc = tc::desc_kmajor(smem_u32(smem + kSmemQ));
-        const uint64_t k_desc = tc::desc_kmajor(smem_u32(smem + kSmemK));
-        const uint64_t v_desc = tc::desc_mnmajor(smem_u32(smem + kSmemV), kHalfBytes);
-
-        auto issue_s = [&](int i, int stage) {  // S_i = Q_i . K^T   (head_dim 128 = 2 halves x 4)
-            if (lane == 0) {
-                const uint64_t a0 = q_desc + static_cast<uint64_t>((i * kTileBytes) >> 4);
-                const uint64_t b0 = k_desc + static_cast<uint64_t>((stage * kTileBytes) >> 4);
+        // Every tcgen05.mma operand below is a COMPILE-TIME constant, so an MMA is a few uniform
+        // moves + UTCHMMA. With run-time descriptors ptxas cannot prove warp-uniformity and emits
+        // ~13 dependent vector instructions per MMA (ELECT / R2UR broadcast loop), 75-84 clk for
+        // a 64-clk MMA — which made this warp the bottleneck of the kernel
+        // (profiles/r02_trace_prefill_*.json). Hence: the ring stage and the accumulate flag are
+        // template parameters selected by (warp-uniform) branches; the TMEM base is 0 (this CTA
+        // owns all 512 columns of the SM's TMEM); the tiles sit at kSmemWindowBase, where the
+        // dynamic shared memory of a kernel without static shared memory starts on sm_100
+        // (descriptors only carry address bits 4..17). Both are checked: a different layout
+        // traps instead of computing garbage.
+        if (tmem != 0 || (smem_u32(smem) & 0x3FFFFu) != kSmemWindowBase) __trap();
+        constexpr uint32_t smem_base = kSmemWindowBase;
+        auto issue_s = [&](auto i_c, auto stage_c) {  // S_i = Q_i . K^T (head_dim 128 = 2 x 4 x 16)
+            constexpr int i = decltype(i_c)::value, stage = decltype(stage_c)::value;
+            {
+                const uint64_t a0 = tc::desc_kmajor(smem_base + kSmemQ + i * kTileBytes);
+                const uint64_t b0 = tc::desc_kmajor(smem_base + kSmemK + stage * kTileBytes);
+                // (bytes >> 4) added to the 14-bit start-address field: smem < 256 KiB, no carry
+                auto off = [](int kk) -> uint64_t {
+                    return static_cast<uint64_t>(((kk >> 2) * kHalfBytes + (kk & 3) * 32) >> 4);
+                };
+                tc::mma_ss_static<i * kTN, false>(a0 + off(0), b0 + off(0), idesc_s);
 #pragma unroll
-                for (int kk = 0; kk < 8; ++kk) {
-                    const uint64_t off = ((kk >> 2) * kHalfBytes + (kk & 3) * 32) >> 4;
-                    tc::mma_ss(tmem + i * kTN, a0 + off, b0 + off, idesc_s, kk > 0);
-                }
-                tc::commit(&bar->s_full[i]);
+                for (int kk = 1; kk < 8; ++kk)
+                    tc::mma_ss_static<i * kTN, true>(a0 + off(kk), b0 + off(kk), idesc_s);
+                if (lane == 0) tc::commit(&bar->s_full[i]);
             }
             __syncwarp();
         };
-        // O_i (+)= P_i . V over the tokens [16 * kk0, 16 * kk0 + 64) of the tile
-        auto issue_pv = [&](int i, int stage, bool accumulate, int kk0) {
-            if (lane == 0) {
-                const uint64_t b0 = v_desc + static_cast<uint64_t>((stage * kTileBytes) >> 4) +
-                                    static_cast<uint64_t>((kk0 * 16 * 128) >> 4);
-                const uint32_t a0 = tmem + i * kTN + kk0 * 8;
-#pragma unroll
-                for (int kk = 0; kk < 4; ++kk) {  // 16 tokens per instruction
-                    tc::mma_ts(tmem + 2 * kTN + i * kHeadDim, a0 + kk * 8,
-                               b0 + ((kk * 16 * 128) >> 4), idesc_o, accumulate || kk > 0);
-                }
+        auto issue_pv = [&](auto i_c, auto stage_c, auto acc_c) {  // O_i (+)= P_i . V
+            constexpr int i = decltype(i_c)::value, stage = decltype(stage_c)::value;
+            constexpr bool acc = decltype(acc_c)::value;
+            {
+                const uint64_t b0 =
+                    tc::desc_mnmajor(smem_base + kSmemV + stage * kTileBytes, kHalfBytes);
+                constexpr uint32_t d = 2 * kTN + i * kHeadDim, a = i * kTN;
+                constexpr uint64_t step = (16 * 128) >> 4;  // 16 tokens per instruction
+                tc::mma_ts_static<d, a + 0, acc>(b0 + 0 * step, idesc_o);
+                tc::mma_ts_static<d, a + 8, true>(b0 + 1 * step, idesc_o);
+                tc::mma_ts_static<d, a + 16, true>(b0 + 2 * step, idesc_o);
+                tc::mma_ts_static<d, a + 24, true>(b0 + 3 * step, idesc_o);
+                tc::mma_ts_static<d, a + 32, true>(b0 + 4 * step, idesc_o);
+                tc::mma_ts_static<d, a + 40, true>(b0 + 5 * step, idesc_o);
+                tc::mma_ts_static<d, a + 48, true>(b0 + 6 * step, idesc_o);
+                tc::mma_ts_static<d, a + 56, true>(b0 + 7 * step, idesc_o);
             }
             __syncwarp();
         };
+        using std::integral_constant;
+        auto issue_s_rt = [&](auto i_c, int stage) {
+            if (stage == 0) issue_s(i_c, integral_constant<int, 0>{});
+            else issue_s(i_c, integral_constant<int, 1>{});
+        };
+        auto issue_pv_rt = [&](auto i_c, int stage, bool acc) {
+            if (stage == 0) {
+                if (acc) issue_pv(i_c, integral_constant<int, 0>{}, integral_constant<bool, true>{});
+                else issue_pv(i_c, integral_constant<int, 0>{}, integral_constant<bool, false>{});
+            } else {
+                if (acc) issue_pv(i_c, integral_constant<int, 1>{}, integral_constant<bool, true>{});
+                else issue_pv(i_c, integral_constant<int, 1>{}, integral_constant<bool, false>{});
+            }
+        };
+        static_assert(kStages == 2, "the issue helpers enumerate two ring stages");
 
         uint32_t kv_it = 0, q_it = 0;
         uint32_t sp_it[2] = {0, 0};  // S/P rounds per sub-tile so far (s_full / p_full phases)
@@ -508,9 +539,8 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
             ++q_it;
             wait_bar(&bar->k_full[kv_it % kStages], (kv_it / kStages) & 1u);
             tc::fence_after_sync();
-#pragma unroll
-            for (int i = 0; i < 2; ++i)
-                if (it.n_kv[i] > 0) issue_s(i, kv_it % kStages);
+            if (it.n_kv[0] > 0) issue_s_rt(integral_constant<int, 0>{}, kv_it % kStages);
+            if (it.n_kv[1] > 0) issue_s_rt(integral_constant<int, 1>{}, kv_it % kStages);
             if (lane == 0) {
                 tc::commit(&bar->k_empty[kv_it % kStages]);
                 if (n_max == 1) tc::commit(&bar->q_empty);  // the item's last S has been issued
@@ -542,28 +572,25 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
                 const int sn = (kv_it + 1) % kStages;
                 if (j + 1 < n_max) wait_bar(&bar->k_full[sn], ((kv_it + 1) / kStages) & 1u);
                 if (kTrace && tr) tr[0] = clock64();
-#pragma unroll
-                for (int i = 0; i < 2; ++i) {
+                auto sub_tile = [&](auto i_c) {
+                    constexpr int i = decltype(i_c)::value;
                     if (j < it.n_kv[i]) {
-                        // P arrives in two halves of 64 tokens: the PV MMAs of the first half are
-                        // issued while the softmax group still computes the second one
-                        wait_bar(&bar->p_half[i], sp_it[i] & 1u);
-                        if (kTrace && tr && i == 0) tr[1] = clock64();
-                        tc::fence_after_sync();
-                        issue_pv(i, s, j > 0, 0);
                         wait_bar(&bar->p_full[i], sp_it[i] & 1u);
+                        if (kTrace && tr && i == 0) tr[1] = clock64();
                         ++sp_it[i];
                         tc::fence_after_sync();
-                        issue_pv(i, s, true, 4);
+                        issue_pv_rt(i_c, s, j > 0);
                         if (kTrace && tr && i == 0) tr[2] = clock64();
                         if (j == it.n_kv[i] - 1) {
                             if (lane == 0) tc::commit(&bar->o_full[i]);
                             __syncwarp();
                         }
                     }
-                    if (j + 1 < it.n_kv[i]) issue_s(i, sn);
+                    if (j + 1 < it.n_kv[i]) issue_s_rt(i_c, sn);
                     if (kTrace && tr && i == 0) tr[3] = clock64();
-                }
+                };
+                sub_tile(integral_constant<int, 0>{});
+                sub_tile(integral_constant<int, 1>{});
                 if (lane == 0) {
                     tc::commit(&bar->v_empty[s]);
                     if (j + 1 < n_max) tc::commit(&bar->k_empty[sn]);
@@ -668,11 +695,6 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
                     pr[t] = pack_bf16x2(x.x, x.y);
                 }
                 tc::tmem_st32(s_tmem + hh * 32, pr);
-                if (hh == 0) {  // first 64 tokens of P are in TMEM: their PV MMAs may start
-                    tc::wait_st();
-                    tc::fence_before_sync();
-                    mbar_arrive(&bar->p_half[i]);
-                }
             }
             l += (ls[0].x + ls[0].y) + (ls[1].x + ls[1].y);
             tc::wait_st();

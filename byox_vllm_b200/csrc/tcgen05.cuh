@@ -101,6 +101,33 @@ __device__ __forceinline__ void mma_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_
         ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate ? 1u : 0u)
         : "memory");
 }
+// Fully static forms: TMEM addresses and the accumulate flag are compile-time constants (the CTA
+// owns the whole TMEM, base 0), the descriptors are constant expressions of the caller. ptxas
+// then feeds UTCHMMA from uniform moves instead of an ELECT / R2UR broadcast loop per operand.
+// The WHOLE WARP must call these, converged: one lane is elected inside (elect.sync), so the
+// instruction is not under a divergent branch.
+template <uint32_t kDTmem, bool kAccumulate>
+__device__ __forceinline__ void mma_ss_static(uint64_t a_desc, uint64_t b_desc, uint32_t idesc) {
+    asm volatile(
+        "{\n\t.reg .pred p, e;\n\t.reg .b32 d;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "mov.b32 d, %0;\n\t"
+        "elect.sync _|e, 0xffffffff;\n\t"
+        "@e tcgen05.mma.cta_group::1.kind::f16 [d], %1, %2, %3, p;\n\t}"
+        ::"n"(kDTmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "n"(kAccumulate ? 1 : 0)
+        : "memory");
+}
+template <uint32_t kDTmem, uint32_t kATmem, bool kAccumulate>
+__device__ __forceinline__ void mma_ts_static(uint64_t b_desc, uint32_t idesc) {
+    asm volatile(
+        "{\n\t.reg .pred p, e;\n\t.reg .b32 d, a;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "mov.b32 d, %0;\n\tmov.b32 a, %1;\n\t"
+        "elect.sync _|e, 0xffffffff;\n\t"
+        "@e tcgen05.mma.cta_group::1.kind::f16 [d], [a], %2, %3, p;\n\t}"
+        ::"n"(kDTmem), "n"(kATmem), "l"(b_desc), "r"(idesc), "n"(kAccumulate ? 1 : 0)
+        : "memory");
+}
 
 // ----------------------------------------------------------------------------------------------
 // TMEM <-> registers, shape 32x32b: lane t of the warp touches TMEM lane (base lane + t), 32
