@@ -188,7 +188,8 @@ struct PrefillParams {
     int32_t prefix_chunks; // split-KV chunks over the shared prefix (grid.y)
     int32_t ws_slot0;      // chunk c writes slot ws_slot0 + c
     int32_t ws_slots;
-    int32_t sched_mode;    // prefill_tc.cu: 0 clc (work stealing), 1 static zig-zag, 2 one item per CTA    // debug: [kTraceCtas][3][kTraceSteps][4] uint64 stamps (b200attn_debug_prefill_trace); nullptr =
+    int32_t sched_mode;    // prefill_tc.cu: 0 clc (work stealing), 1 static zig-zag, 2 one item per CTA
+    // debug: [kTraceCtas][kTraceStreams][kTraceSteps][4] uint64 stamps (b200attn_debug_prefill_trace); nullptr =
     // the product kernel
     unsigned long long* trace;
 };
@@ -200,6 +201,7 @@ cudaError_t launch_prefill(const PrefillParams& p, cudaStream_t stream);
 // sequences per call (more -> the caller takes the mma.sync shape fallback); batches with more
 // than kTcMaxItems 256-row pairs per KV head run in descending index order instead of sorted.
 constexpr int kTraceCtas = 8;
+constexpr int kTraceStreams = 6;
 constexpr int kTraceSteps = 128;
 constexpr int kTcMaxSeqs = 4095;
 constexpr int kTcMaxItems = 4096;

@@ -329,7 +329,10 @@ __device__ void build_schedule(const PrefillParams& p, Barriers* bar, int32_t* p
 // kTrace: debug build (b200attn_debug_prefill_trace) — the first kTraceCtas CTAs stamp clock64 at
 // the phase boundaries of their first kTraceSteps tile steps: stream 0/1 = softmax group 0/1
 // {S ready, S row loaded, P computed, P signalled}, stream 2 = issuer {tiles ready, P_0 ready,
-// PV_0 issued, S_0 of the next tile issued}; layout [cta][stream][step][4] uint64 (tools/trace_prefill.py).
+// PV_0 issued, S_0 of the next tile issued}; per ITEM: stream 3 = issuer {item fetched, Q landed,
+// first S issued, last step issued}, stream 4 = producer {item fetched, first K/V issued, Q buffer
+// free, all tiles issued}, stream 5 = softmax group 0 {item fetched, last P signalled, O complete,
+// rows stored}; layout [cta][stream][step][4] uint64 (tools/trace_prefill.py).
 template <bool kCascade, int kEmu, bool kTrace = false>
 __global__ void __launch_bounds__(kTcThreads, 1)
 prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
@@ -389,7 +392,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
     unsigned long long* trace = nullptr;  // this CTA's stamps (kTrace only)
     if constexpr (kTrace) {
         if (p.trace != nullptr && blockIdx.x < kTraceCtas)
-            trace = p.trace + static_cast<size_t>(blockIdx.x) * 3 * kTraceSteps * 4;
+            trace = p.trace + static_cast<size_t>(blockIdx.x) * kTraceStreams * kTraceSteps * 4;
     }
     uint32_t tr_step = 0;  // tile steps this role has stamped
 
@@ -418,6 +421,12 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
                     clc_try_cancel(smem + kSmemClc + slot * 16, &bar->sched_full[slot]);
                 }
                 if (it.n_max == 0) continue;
+                unsigned long long* tri = nullptr;
+                if constexpr (kTrace) {
+                    if (trace != nullptr && q_it < kTraceSteps)
+                        tri = trace + (4 * kTraceSteps + q_it) * 4;
+                    if (tri) tri[0] = clock64();
+                }
                 const int32_t* table =
                     paged ? p.block_tables + static_cast<int64_t>(it.seq) * p.table_row_stride
                           : nullptr;
@@ -443,10 +452,12 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
                     uint8_t* vd = smem + kSmemV + s * kTileBytes;
                     tma_load_3d(vd, &v_map, &bar->v_full[s], 0, it.kvh, slot);
                     tma_load_3d(vd + kHalfBytes, &v_map, &bar->v_full[s], 64, it.kvh, slot);
+                    if (kTrace && tri && j == 0) tri[1] = clock64();
                     if (j == 0) {
                         // Q after the item's first K/V tile: those ring slots free up earlier
                         // than the Q buffer (released by the previous item's LAST S MMA).
                         wait_bar(&bar->q_empty, (q_it & 1u) ^ 1u);
+                        if (kTrace && tri) tri[2] = clock64();
                         const int n_q = it.n_kv[1] > 0 ? 2 : 1;  // sub-tile 0 always has rows
                         mbar_expect_tx(&bar->q_full, n_q * kTileBytes);
                         for (int i = 0; i < n_q; ++i) {
@@ -458,6 +469,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
                         ++q_it;
                     }
                 }
+                if (kTrace && tri) tri[3] = clock64();
             }
         }
     } else if (warp == kMmaWarp) {
@@ -535,7 +547,14 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
         for (int k = 0; fetch_item<kCascade, true>(k, p, bar, clc, pair_start, keys, it); ++k) {
             const int n_max = it.n_max;
             if (n_max == 0) continue;
+            unsigned long long* tri = nullptr;
+            if constexpr (kTrace) {
+                if (trace != nullptr && lane == 0 && q_it < kTraceSteps)
+                    tri = trace + (3 * kTraceSteps + q_it) * 4;
+                if (tri) tri[0] = clock64();
+            }
             wait_bar(&bar->q_full, q_it & 1u);
+            if (kTrace && tri) tri[1] = clock64();
             ++q_it;
             wait_bar(&bar->k_full[kv_it % kStages], (kv_it / kStages) & 1u);
             tc::fence_after_sync();
@@ -545,6 +564,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
                 tc::commit(&bar->k_empty[kv_it % kStages]);
                 if (n_max == 1) tc::commit(&bar->q_empty);  // the item's last S has been issued
             }
+            if (kTrace && tri) tri[2] = clock64();
             __syncwarp();
             for (int j = 0; j < n_max; ++j, ++kv_it) {
                 const int s = kv_it % kStages;
@@ -598,6 +618,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
                 }
                 __syncwarp();
             }
+            if (kTrace && tri) tri[3] = clock64();
         }
     } else if (warp < kProducerWarp) {
         // ============================ softmax / correction / epilogue ============================
@@ -619,6 +640,12 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
         const int Lk = it.Lk, offset = it.offset;
         float m_ref = -INFINITY;  // scaled (log2-domain) reference maximum of this row
         float l = 0.f;
+        unsigned long long* tri = nullptr;
+        if constexpr (kTrace) {
+            if (trace != nullptr && i == 0 && r == 0 && n > 0 && o_it < kTraceSteps)
+                tri = trace + (5 * kTraceSteps + o_it) * 4;
+            if (tri) tri[0] = clock64();
+        }
 
         for (int j = 0; j < n; ++j, ++sp_it) {
             unsigned long long* tr = nullptr;
@@ -736,6 +763,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
             }
         } else {
         // ---- epilogue: O / l -> bf16 -> global (row-predicated 16-byte stores) ----
+        if (kTrace && tri) tri[1] = clock64();
         const bool row_ok = row < it.Lq;  // (surplus ticket: Lq = 0)
         uint8_t* orow_g = static_cast<uint8_t*>(p.out) +
                           ((static_cast<int64_t>(it.q_begin) + row) * p.num_q_heads + head) * 256;
@@ -743,6 +771,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
             wait_bar(&bar->o_full[i], o_it & 1u);
             ++o_it;
             tc::fence_after_sync();
+            if (kTrace && tri) tri[2] = clock64();
             const float inv = l > 0.f ? 1.f / l : 0.f;
 #pragma unroll
             for (int q4 = 0; q4 < 4; ++q4) {
@@ -767,6 +796,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
             // the next item's first PV overwrites O_i: order these TMEM reads before the P
             // signal that releases it
             tc::fence_before_sync();
+            if (kTrace && tri) tri[3] = clock64();
         } else if (row_ok) {
             // no visible key for this sub-tile (only possible when Lk < Lq): zeros, as flash-attn
 #pragma unroll

@@ -140,7 +140,7 @@ int b200attn_set_decode_overlap(int on);
  * NULL (the default) restores the product kernel. Not thread-safe, not for production. */
 void b200attn_debug_decode_trace(void* stamps);
 
-/* Debug only: with a device buffer of 8 CTAs x 3 streams x 128 steps x 4 uint64 registered,
+/* Debug only: with a device buffer of 8 CTAs x 6 streams x 128 steps x 4 uint64 registered,
  * b200attn_prefill_varlen launches an instrumented build of the tcgen05 kernel whose first 8 CTAs
  * stamp their SM clock at the phase boundaries of every tile step (tools/trace_prefill.py); NULL
  * (the default) restores the product kernel. Not thread-safe, not for production. */

@@ -21,7 +21,7 @@ sys.path.insert(0, str(ROOT))
 
 import torch  # noqa: E402
 
-CTAS, STEPS = 8, 128
+CTAS, STREAMS, STEPS = 8, 6, 128
 SHAPES = [  # name, lens, Hq, Hkv
     ("1x16384 32/8", [16384], 32, 8),
     ("4x4096 32/8", [4096] * 4, 32, 8),
@@ -60,7 +60,7 @@ def main():
             for _ in range(2):
                 prefill_varlen(q, k, v, cu, cu, max(lens), max(lens), scale, out=o)
             torch.cuda.synchronize()
-            trace = torch.zeros(CTAS * 3 * STEPS * 4, dtype=torch.int64, device="cuda")
+            trace = torch.zeros(CTAS * STREAMS * STEPS * 4, dtype=torch.int64, device="cuda")
             lib.b200attn_debug_prefill_trace(ctypes.c_void_p(trace.data_ptr()))
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
@@ -68,7 +68,7 @@ def main():
             e1.record()
             torch.cuda.synchronize()
             lib.b200attn_debug_prefill_trace(ctypes.c_void_p(0))
-            t = trace.view(CTAS, 3, STEPS, 4).cpu().numpy()
+            t = trace.view(CTAS, STREAMS, STEPS, 4).cpu().numpy()
             rec = {"shape": name, "event_us": round(e0.elapsed_time(e1) * 1e3, 1)}
             for i in (0, 1):
                 a = t[:, i]
@@ -100,8 +100,11 @@ def main():
             rec["cta0_first_steps"] = [
                 {"s0": [int(x - base) for x in t[0, 0, n]], "s1": [int(x - base) for x in t[0, 1, n]],
                  "mma": [int(x - base) for x in t[0, 2, n]]} for n in range(10)]
+            rec["cta0_items"] = [
+                {"issuer": [int(x - base) for x in t[0, 3, n]], "producer": [int(x - base) for x in t[0, 4, n]],
+                 "softmax0": [int(x - base) for x in t[0, 5, n]]} for n in range(8)]
             rows.append(rec)
-            print(json.dumps({k2: v2 for k2, v2 in rec.items() if k2 != "cta0_first_steps"}), flush=True)
+            print(json.dumps({k2: v2 for k2, v2 in rec.items() if k2 not in ("cta0_first_steps", "cta0_items")}), flush=True)
     (ROOT / "gpurun_out").mkdir(exist_ok=True)
     (ROOT / "gpurun_out" / "trace_prefill.json").write_text(json.dumps(rows, indent=1))
 
