@@ -203,7 +203,7 @@ cudaError_t launch_prefill(const PrefillParams& p, cudaStream_t stream);
 constexpr int kTraceCtas = 8;
 constexpr int kTraceStreams = 6;
 constexpr int kTraceSteps = 128;
-constexpr int kTcMaxSeqs = 4095;
+constexpr int kTcMaxSeqs = 1023;
 constexpr int kTcMaxItems = 4096;
 cudaError_t launch_prefill_tc(const PrefillParams& p, const CUtensorMap& q_map,
                               const CUtensorMap& k_map, const CUtensorMap& v_map,

@@ -78,8 +78,11 @@ constexpr int kSmemV = kSmemK + kStages * kTileBytes;
 constexpr int kSmemBar = kSmemV + kStages * kTileBytes;
 constexpr int kClcSlots = 4;                                               // ticket ring
 constexpr int kSmemClc = kSmemBar + 256;                                    // 16-byte responses
-constexpr int kSmemPairStart = kSmemClc + kClcSlots * 16;                   // int32[kTcMaxSeqs + 1]
-constexpr int kSmemKeys = kSmemPairStart + (kTcMaxSeqs + 1) * 4;            // uint32[kTcMaxItems]
+// cu_seqlens_q | cu_seqlens_k | pair_start, int32[kTcMaxSeqs + 1] each: the item walk never touches
+// global memory (a load issued behind an epilogue's stores waits for all of them in the LSU)
+constexpr int kSchedStride = kTcMaxSeqs + 1;
+constexpr int kSmemPairStart = kSmemClc + kClcSlots * 16;
+constexpr int kSmemKeys = kSmemPairStart + 3 * kSchedStride * 4;            // uint32[kTcMaxItems]
 constexpr int kTcSmemBytes = kSmemKeys + kTcMaxItems * 4 + 1024;
 static_assert(kTcMaxItems <= (1 << kSchedKeyBits), "item index does not fit the key");
 static_assert(kTcSmemBytes <= 232448, "more shared memory than an sm_100 CTA can opt into");
@@ -212,6 +215,8 @@ __device__ __forceinline__ bool fetch_item(int k, const PrefillParams& p, Barrie
         it.kvh = static_cast<int>(g - static_cast<int64_t>(li) * p.num_kv_heads);
         const int t = bar->use_keys ? static_cast<int>(keys[li] & ((1u << kSchedKeyBits) - 1u))
                                     : T - 1 - li;
+        const int32_t* cu_q = pair_start - 2 * kSchedStride;  // shared-memory copies
+        const int32_t* cu_k = pair_start - kSchedStride;
         int lo = 0, hi = p.num_seqs;  // largest seq with pair_start[seq] <= t
         while (hi - lo > 1) {
             const int mid = (lo + hi) >> 1;
@@ -219,10 +224,10 @@ __device__ __forceinline__ bool fetch_item(int k, const PrefillParams& p, Barrie
         }
         it.seq = lo;
         const int pair = t - pair_start[lo];
-        it.q_begin = __ldg(p.cu_seqlens_q + lo);
-        it.Lq = __ldg(p.cu_seqlens_q + lo + 1) - it.q_begin;
-        it.k_begin = __ldg(p.cu_seqlens_k + lo);
-        it.Lk = __ldg(p.cu_seqlens_k + lo + 1) - it.k_begin;
+        it.q_begin = cu_q[lo];
+        it.Lq = cu_q[lo + 1] - it.q_begin;
+        it.k_begin = cu_k[lo];
+        it.Lk = cu_k[lo + 1] - it.k_begin;
         it.offset = it.Lk - it.Lq;  // token i sees keys j <= i + offset
         it.j0 = 0;
         it.chunk = 0;
@@ -252,13 +257,20 @@ __device__ void build_schedule(const PrefillParams& p, Barriers* bar, int32_t* p
     const int tid = threadIdx.x, lane = tid & 31;
     const int S = p.num_seqs;
     const int toks_per_pair = 2 * kTM / p.group;
+    int32_t* cu_q = pair_start - 2 * kSchedStride;
+    int32_t* cu_k = pair_start - kSchedStride;
+    for (int s = tid; s <= S; s += kTcThreads) {
+        cu_q[s] = __ldg(p.cu_seqlens_q + s);
+        cu_k[s] = __ldg(p.cu_seqlens_k + s);
+    }
+    __syncthreads();
     if (tid < 32) {
         int running = 0;
         for (int base = 0; base < S; base += 32) {
             const int s = base + lane;
             int n = 0;
             if (s < S) {
-                const int lq = __ldg(p.cu_seqlens_q + s + 1) - __ldg(p.cu_seqlens_q + s);
+                const int lq = cu_q[s + 1] - cu_q[s];
                 n = lq > 0 ? (lq + toks_per_pair - 1) / toks_per_pair : 0;
             }
             int incl = n;
@@ -289,9 +301,8 @@ __device__ void build_schedule(const PrefillParams& p, Barriers* bar, int32_t* p
                 const int mid = (lo + hi) >> 1;
                 if (pair_start[mid] <= t) lo = mid; else hi = mid;
             }
-            const int qb = __ldg(p.cu_seqlens_q + lo), kb = __ldg(p.cu_seqlens_k + lo);
-            const int lq = __ldg(p.cu_seqlens_q + lo + 1) - qb;
-            const int lk = __ldg(p.cu_seqlens_k + lo + 1) - kb;
+            const int lq = cu_q[lo + 1] - cu_q[lo];
+            const int lk = cu_k[lo + 1] - cu_k[lo];
             const uint32_t cost = min(static_cast<uint32_t>(
                 pair_cost(t - pair_start[lo], lq, lk, kTM / p.group)), kSchedCostMax - 1);
             key = ((kSchedCostMax - 1 - cost) << kSchedKeyBits) | static_cast<uint32_t>(t);
@@ -353,7 +364,8 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
         (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
     Barriers* bar = reinterpret_cast<Barriers*>(smem + kSmemBar);
     const uint8_t* clc = smem + kSmemClc;
-    const int32_t* pair_start = reinterpret_cast<const int32_t*>(smem + kSmemPairStart);
+    const int32_t* pair_start =
+        reinterpret_cast<const int32_t*>(smem + kSmemPairStart) + 2 * kSchedStride;
     const uint32_t* keys = reinterpret_cast<const uint32_t*>(smem + kSmemKeys);
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -382,7 +394,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
         fence_mbar_init();
     }
     if constexpr (!kCascade)
-        build_schedule(p, bar, reinterpret_cast<int32_t*>(smem + kSmemPairStart),
+        build_schedule(p, bar, reinterpret_cast<int32_t*>(smem + kSmemPairStart) + 2 * kSchedStride,
                        reinterpret_cast<uint32_t*>(smem + kSmemKeys));
     if (warp == kMmaWarp) tc::tmem_alloc(&bar->tmem_base, kTmemCols);
     tc::fence_before_sync();
@@ -779,17 +791,13 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
                 tc::tmem_ld32(o_tmem + q4 * 32, orow);
                 if (row_ok) {
 #pragma unroll
-                    for (int v4 = 0; v4 < 4; ++v4) {
-                        int4 pk;
-                        pk.x = pack_bf16x2(__uint_as_float(orow[v4 * 8 + 0]) * inv,
-                                           __uint_as_float(orow[v4 * 8 + 1]) * inv);
-                        pk.y = pack_bf16x2(__uint_as_float(orow[v4 * 8 + 2]) * inv,
-                                           __uint_as_float(orow[v4 * 8 + 3]) * inv);
-                        pk.z = pack_bf16x2(__uint_as_float(orow[v4 * 8 + 4]) * inv,
-                                           __uint_as_float(orow[v4 * 8 + 5]) * inv);
-                        pk.w = pack_bf16x2(__uint_as_float(orow[v4 * 8 + 6]) * inv,
-                                           __uint_as_float(orow[v4 * 8 + 7]) * inv);
-                        st_v4(orow_g + q4 * 64 + v4 * 16, pk);
+                    for (int v8 = 0; v8 < 2; ++v8) {  // 32-byte stores: whole sectors, half the
+                        uint32_t pk[8];               // LSU work of 16-byte ones
+#pragma unroll
+                        for (int w = 0; w < 8; ++w)
+                            pk[w] = pack_bf16x2(__uint_as_float(orow[v8 * 16 + 2 * w]) * inv,
+                                                __uint_as_float(orow[v8 * 16 + 2 * w + 1]) * inv);
+                        st_v8(orow_g + q4 * 64 + v8 * 32, pk);
                     }
                 }
             }
