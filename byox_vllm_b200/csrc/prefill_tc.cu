@@ -81,7 +81,10 @@ constexpr int kSmemClc = kSmemBar + 256;                                    // 1
 // cu_seqlens_q | cu_seqlens_k | pair_start, int32[kTcMaxSeqs + 1] each: the item walk never touches
 // global memory (a load issued behind an epilogue's stores waits for all of them in the LSU)
 constexpr int kSchedStride = kTcMaxSeqs + 1;
-constexpr int kSmemPairStart = kSmemClc + kClcSlots * 16;
+constexpr int kItemSlots = 4;                                               // decoded-item ring
+constexpr int kItemWords = 20;                                              // int32 per slot
+constexpr int kSmemItems = kSmemClc + kClcSlots * 16;
+constexpr int kSmemPairStart = kSmemItems + kItemSlots * kItemWords * 4;
 constexpr int kSmemKeys = kSmemPairStart + 3 * kSchedStride * 4;            // uint32[kTcMaxItems]
 constexpr int kTcSmemBytes = kSmemKeys + kTcMaxItems * 4 + 1024;
 static_assert(kTcMaxItems <= (1 << kSchedKeyBits), "item index does not fit the key");
@@ -93,12 +96,13 @@ struct Barriers {
     uint64_t v_full[kStages], v_empty[kStages];
     uint64_t s_full[2], p_full[2], o_full[2];
     uint64_t sched_full[kClcSlots];   // try_cancel response k+1 has landed in slot k % kClcSlots
-    uint64_t sched_empty[kClcSlots];  // ... and the issuer + the 8 softmax warps have read it
+    uint64_t item_full[kItemSlots];   // the producer has published item k in slot k % kItemSlots
+    uint64_t item_empty[kItemSlots];  // ... and the issuer + the 8 softmax warps have read it
     uint32_t tmem_base;
     int32_t num_pairs;   // 256-row pairs over all sequences (items per KV head)
     int32_t use_keys;    // 1: keys[] holds the cost-sorted order; 0: descending item index
 };
-constexpr int kTicketReaders = 1 + kProducerWarp;  // MMA warp + softmax warps (lane 0 arrives)
+constexpr int kItemReaders = 1 + kProducerWarp;  // MMA warp + softmax warps (lane 0 arrives)
 static_assert(sizeof(Barriers) <= 256, "barrier block overflows its shared-memory slot");
 
 // Bounded wait: a protocol bug traps (launch error) after ~2 s instead of hanging the GPU
@@ -157,11 +161,11 @@ __device__ __forceinline__ int clc_decode(const void* resp) {
 
 enum : int { kSchedClc = 0, kSchedStatic = 1, kSchedGrid = 2 };
 
-// The k-th item of this CTA (false: no more). Every role of the CTA walks the same sequence; an
-// item may be empty (n_max == 0: a ticket beyond the real item count, or no visible key).
-// kReader: the calling WARP is one of the kTicketReaders consumers of the ticket ring (all its
-// lanes call; lane 0 hands the slot back to the producer once every lane has decoded it).
-template <bool kCascade, bool kReader>
+// The k-th item of this CTA (false: no more); an item may be empty (n_max == 0: a ticket beyond
+// the real item count, or no visible key). Only the producer thread runs this: it publishes the
+// decoded item to the other roles through a shared-memory ring (publish_item / consume_item), so
+// the ticket decode, the searches and their (cold) code are paid once per item, ahead of time.
+template <bool kCascade>
 __device__ __forceinline__ bool fetch_item(int k, const PrefillParams& p, Barriers* bar,
                                            const uint8_t* clc, const int32_t* pair_start,
                                            const uint32_t* keys, Item& it) {
@@ -198,10 +202,6 @@ __device__ __forceinline__ bool fetch_item(int k, const PrefillParams& p, Barrie
             const int slot = (k - 1) % kClcSlots;
             wait_bar(&bar->sched_full[slot], ((k - 1) / kClcSlots) & 1u);
             const int t = clc_decode(clc + slot * 16);
-            if constexpr (kReader) {
-                __syncwarp();
-                if ((threadIdx.x & 31) == 0) mbar_arrive(&bar->sched_empty[slot]);
-            }
             if (t < 0) return false;  // grid drained
             g = t;
         }
@@ -247,6 +247,36 @@ __device__ __forceinline__ bool fetch_item(int k, const PrefillParams& p, Barrie
     it.q_c1 = it.kvh * p.group;
     it.n_max = max(it.n_kv[0], it.n_kv[1]);
     return true;
+}
+
+// Producer thread: item k (or the end marker) into slot k % kItemSlots, once the slot's previous
+// item has been read by every consumer warp.
+__device__ __forceinline__ void publish_item(int k, bool more, const Item& it, Barriers* bar,
+                                             int32_t* items) {
+    const int slot = k % kItemSlots;
+    if (k >= kItemSlots) wait_bar(&bar->item_empty[slot], ((k / kItemSlots) - 1) & 1u);
+    int4* dst = reinterpret_cast<int4*>(items + slot * kItemWords);
+    dst[0] = make_int4(it.seq, it.kvh, it.q_begin, it.Lq);
+    dst[1] = make_int4(it.Lk, it.k_begin, it.offset, it.j0);
+    dst[2] = make_int4(it.chunk, it.q_c1, it.row0[0], it.row0[1]);
+    dst[3] = make_int4(it.n_kv[0], it.n_kv[1], it.q_c2[0], it.q_c2[1]);
+    dst[4] = make_int4(it.n_max, more ? 1 : 0, 0, 0);
+    mbar_arrive(&bar->item_full[slot]);  // release: the stores above are visible to the waiters
+}
+// Consumer warps (all lanes call): item k of this CTA, false at the end marker.
+__device__ __forceinline__ bool consume_item(int k, Barriers* bar, const int32_t* items, Item& it) {
+    const int slot = k % kItemSlots;
+    wait_bar(&bar->item_full[slot], (k / kItemSlots) & 1u);
+    const int4* src = reinterpret_cast<const int4*>(items + slot * kItemWords);
+    const int4 a = src[0], b = src[1], c = src[2], d = src[3], e = src[4];
+    it.seq = a.x; it.kvh = a.y; it.q_begin = a.z; it.Lq = a.w;
+    it.Lk = b.x; it.k_begin = b.y; it.offset = b.z; it.j0 = b.w;
+    it.chunk = c.x; it.q_c1 = c.y; it.row0[0] = c.z; it.row0[1] = c.w;
+    it.n_kv[0] = d.x; it.n_kv[1] = d.y; it.q_c2[0] = d.z; it.q_c2[1] = d.w;
+    it.n_max = e.x;
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) mbar_arrive(&bar->item_empty[slot]);
+    return e.y != 0;
 }
 
 // Prologue of the persistent prefill: pair_start[0..S] = exclusive scan of the 256-row pairs per
@@ -364,6 +394,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
         (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
     Barriers* bar = reinterpret_cast<Barriers*>(smem + kSmemBar);
     const uint8_t* clc = smem + kSmemClc;
+    int32_t* items = reinterpret_cast<int32_t*>(smem + kSmemItems);
     const int32_t* pair_start =
         reinterpret_cast<const int32_t*>(smem + kSmemPairStart) + 2 * kSchedStride;
     const uint32_t* keys = reinterpret_cast<const uint32_t*>(smem + kSmemKeys);
@@ -389,7 +420,11 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
 #pragma unroll
         for (int t = 0; t < kClcSlots; ++t) {
             mbar_init(&bar->sched_full[t], 1);
-            mbar_init(&bar->sched_empty[t], kTicketReaders);
+        }
+#pragma unroll
+        for (int t = 0; t < kItemSlots; ++t) {
+            mbar_init(&bar->item_full[t], 1);
+            mbar_init(&bar->item_empty[t], kItemReaders);
         }
         fence_mbar_init();
     }
@@ -420,15 +455,15 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
             uint32_t kv_it = 0;   // K/V tiles issued so far (ring position, across items)
             uint32_t q_it = 0;    // items with work so far (Q buffer phase)
             Item it;
-            for (int k = 0; fetch_item<kCascade, false>(k, p, bar, clc, pair_start, keys, it); ++k) {
+            for (int k = 0;; ++k) {
+                const bool more = fetch_item<kCascade>(k, p, bar, clc, pair_start, keys, it);
+                publish_item(k, more, it, bar, items);
+                if (!more) break;
                 if (!kCascade && p.sched_mode == kSchedClc) {
                     // ticket k was good: ask for ticket k + 1 now, it lands while item k runs.
-                    // (Never after a failed request: fetch_item ends the loop on the first one.)
-                    // The slot's previous ticket must have been read by every consumer: empty
-                    // items couple the roles through nothing else.
+                    // (Never after a failed request: the loop ends on the first one. This thread
+                    // is the only reader of the responses, so the slot is free.)
                     const int slot = k % kClcSlots;
-                    if (k >= kClcSlots)
-                        wait_bar(&bar->sched_empty[slot], ((k / kClcSlots) - 1) & 1u);
                     mbar_expect_tx(&bar->sched_full[slot], 16);
                     clc_try_cancel(smem + kSmemClc + slot * 16, &bar->sched_full[slot]);
                 }
@@ -556,7 +591,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
         uint32_t kv_it = 0, q_it = 0;
         uint32_t sp_it[2] = {0, 0};  // S/P rounds per sub-tile so far (s_full / p_full phases)
         Item it;
-        for (int k = 0; fetch_item<kCascade, true>(k, p, bar, clc, pair_start, keys, it); ++k) {
+        for (int k = 0; consume_item(k, bar, items, it); ++k) {
             const int n_max = it.n_max;
             if (n_max == 0) continue;
             unsigned long long* tri = nullptr;
@@ -644,7 +679,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
         uint32_t sp_it = 0;   // S/P rounds of this sub-tile so far
         uint32_t o_it = 0;    // items of this sub-tile with work so far
         Item it;
-        for (int k = 0; fetch_item<kCascade, true>(k, p, bar, clc, pair_start, keys, it); ++k) {
+        for (int k = 0; consume_item(k, bar, items, it); ++k) {
         // (selects, not it.row0[i]: a runtime index would push the item into local memory)
         const int row = (i ? it.row0[1] : it.row0[0]) + (r >> g_shift);  // token (cascade: batch row)
         const int head = it.kvh * p.group + (r & (p.group - 1));
