@@ -642,13 +642,24 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
         int cur_block = 0;
         ScatterPre cur_sc{};
         if (have) cur_block = load_window(cur);
-        // Overlap mode: up to here only step metadata was read. The new K/V rows, the cache and
-        // the scheduler counters belong to the stream order: wait for the preceding grid.
-        if (p.overlap) grid_dependency_wait();
-        if (have && with_store && cur.last) cur_sc = scatter_prefetch(p, cur.b, cur.kvh, lane);
+        // Overlap mode: up to here only step metadata was read. The new K/V rows and the scheduler
+        // counters belong to the stream order: wait for the preceding grid — the stream engine
+        // here, the rows engine only in front of the ONE tile of a row that holds the newest token
+        // (written by this step's scatter, fused or not). Every older tile was written by earlier
+        // steps, so its loads go out while the preceding grid (the previous layer's decode) is
+        // still draining: the ring is full when the consumers are released, and the first-tile
+        // latency (~2-4 us of a ~20 us launch at the TP=8 shapes) is off the critical path.
+        bool waited = !p.overlap;
+        if (!kRows && !waited) {
+            grid_dependency_wait();
+            waited = true;
+        }
+        if (have && with_store && cur.last && waited)
+            cur_sc = scatter_prefetch(p, cur.b, cur.kvh, lane);
         int it = 0;
         while (have) {
-            if (with_store && cur.last) scatter_finish(p, cur_sc, cur.b, cur.kvh, lane);
+            if (with_store && cur.last && waited)
+                scatter_finish(p, cur_sc, cur.b, cur.kvh, lane);
             const int32_t* table =
                 p.block_tables + static_cast<int64_t>(cur.b) * p.table_row_stride;
             const int last_page = idiv_rcp(cur.t_end - 1, tiles_per_page, rcp_tpp);
@@ -672,6 +683,14 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
                         nxt_block = load_window(nxt);
                         if (with_store && nxt.last)
                             nxt_sc = scatter_prefetch(p, nxt.b, nxt.kvh, lane);
+                    }
+                }
+                if (kRows && !waited && t == cur.tiles_total - 1) {
+                    grid_dependency_wait();
+                    waited = true;
+                    if (with_store && cur.last) {
+                        cur_sc = scatter_prefetch(p, cur.b, cur.kvh, lane);
+                        scatter_finish(p, cur_sc, cur.b, cur.kvh, lane);
                     }
                 }
                 if (page - page_base >= 32) {

@@ -126,9 +126,14 @@ int b200attn_decode_partition_host(const int32_t* context_lens, int32_t batch,
  * precedes it in the stream: the kernel's prologue - the scan of context_lens, its first work item
  * and that item's block-table window - runs while the preceding kernel drains, and
  * griddepcontrol.wait comes before q, the new K/V rows and the cache are read and before anything
- * is written. THE CALLER PROMISES that context_lens and block_tables are not written by the kernel
- * immediately before the decode launch in the stream (in nanovllm they are written once per step,
- * model_runner.py:206-226, many kernels earlier; byox_vllm_b200.install() switches overlap on).
+ * is written. One exception: the K/V tiles of a row that lie entirely before its newest token
+ * (position context_lens[b] - 1) are requested before the wait, so that the ring is full when the
+ * preceding kernel has drained. THE CALLER PROMISES that the kernel immediately before the decode
+ * launch in the stream writes neither context_lens / block_tables (in nanovllm they are written
+ * once per step, model_runner.py:206-226, many kernels earlier) nor any cache row other than the
+ * rows' newest tokens (in nanovllm that kernel is the qkv GEMM or store_kvcache of the same
+ * layer, attention.py:67-71, which writes exactly those); byox_vllm_b200.install() switches
+ * overlap on.
  * Ignored for launches with a cascade plan (those are dependents of the shared-prefix pass).
  * Every decode launch also signals launch_dependents at its start, so consecutive decode launches
  * (one per layer) overlap tail and prologue.
