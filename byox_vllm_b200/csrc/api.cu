@@ -17,6 +17,24 @@
 namespace b200 {
 static std::atomic<int64_t> g_launches{0};
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+int current_device_sm_count() {
+    static std::atomic<int> sms[64] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
+        (void)cudaGetLastError();
+        return 0;
+    }
+    int n = sms[dev].load(std::memory_order_relaxed);
+    if (n == 0) {
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) {
+            (void)cudaGetLastError();
+            return 0;
+        }
+        sms[dev].store(n, std::memory_order_relaxed);
+    }
+    return n;
+}
 }  // namespace b200
 
 namespace {
@@ -377,18 +395,7 @@ const char* b200attn_last_error(void) { return g_err; }
 
 int64_t b200attn_launch_count(void) { return b200::g_launches.load(std::memory_order_relaxed); }
 
-int b200attn_sm_count(void) {
-    static int count = [] {
-        int dev = 0, n = 0;
-        if (cudaGetDevice(&dev) != cudaSuccess ||
-            cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) {
-            (void)cudaGetLastError();
-            return 0;
-        }
-        return n;
-    }();
-    return count;
-}
+int b200attn_sm_count(void) { return b200::current_device_sm_count(); }
 
 int b200attn_store_kvcache(const void* key, int64_t key_row_stride, const void* value,
                            int64_t value_row_stride, void* k_cache, void* v_cache,

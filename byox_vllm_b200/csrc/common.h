@@ -15,6 +15,9 @@ constexpr int kHeadDim = 128;  // every BASELINE model (Qwen3 0.6B / 8B / 32B) h
 // Launch accounting (b200attn_launch_count): every kernel launch of the library calls this once.
 void count_launch(int n = 1);
 
+// SM count of the CURRENT device (cached per device ordinal: a process may drive several GPUs).
+int current_device_sm_count();
+
 // ---- store_kv.cu -----------------------------------------------------------------------------
 cudaError_t launch_store_kvcache(const void* key, int64_t key_row_stride, const void* value,
                                  int64_t value_row_stride, void* k_cache, void* v_cache,

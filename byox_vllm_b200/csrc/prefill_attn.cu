@@ -273,13 +273,16 @@ prefill_varlen_kernel(const PrefillParams p) {
 }  // namespace
 
 cudaError_t launch_prefill(const PrefillParams& p, cudaStream_t stream) {
-    static bool configured = false;
-    if (!configured) {
+    // the opt-in shared-memory size is a per-device function attribute
+    static bool configured[64] = {};
+    int dev = 0;
+    if (cudaError_t e = cudaGetDevice(&dev); e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64 || !configured[dev]) {
         cudaError_t e = cudaFuncSetAttribute(prefill_varlen_kernel,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              kPrefillSmem);
         if (e != cudaSuccess) return e;
-        configured = true;
+        if (dev >= 0 && dev < 64) configured[dev] = true;
     }
     const int q_tiles = (p.max_seqlen_q + kBlockM - 1) / kBlockM;
     dim3 grid(q_tiles, p.num_q_heads, p.num_seqs);

@@ -910,16 +910,8 @@ cudaError_t launch_tc_emu(int emu, dim3 grid, const PrefillParams& p, const CUte
 }
 
 int device_sm_count() {
-    static int sms[kMaxDevices] = {};
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return 148;
-    if (sms[dev] == 0) {
-        int n = 0;
-        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
-            n = 148;
-        sms[dev] = n;
-    }
-    return sms[dev];
+    const int n = current_device_sm_count();
+    return n > 0 ? n : 148;
 }
 
 }  // namespace

@@ -266,12 +266,8 @@ cudaError_t launch_qk_norm_rope_store(const QkNormRopeParams& p, cudaStream_t st
     // rows of >= 8 KiB per token amortise the per-token barrier / issue chain; below that
     // (TP = 8 shards) and for short batches the direct kernel is faster (measured)
     if (bulk_ok && (mode == 1 || (mode == 0 && p.n_tokens >= 2048 && row_bytes >= 8192))) {
-        static int sm_count = [] {
-            int dev = 0, n = 148;
-            cudaGetDevice(&dev);
-            cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-            return n > 0 ? n : 148;
-        }();
+        int sm_count = current_device_sm_count();
+        if (sm_count <= 0) sm_count = 148;
         static const int warps = [] {
             const char* e = std::getenv("B200ATTN_NORMROPE_WARPS");
             const int w = e ? std::atoi(e) : 4;

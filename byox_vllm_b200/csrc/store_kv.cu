@@ -132,12 +132,8 @@ cudaError_t launch_store_kvcache(const void* key, int64_t key_row_stride, const 
     const int smem = kCopyStages * 2 * row_bytes + kCopyStages * 8 + 128;
     if (smem <= 64 * 1024 &&
         mode == 1 && row_bytes >= 256) {
-        static int sm_count = [] {
-            int dev = 0, n = 148;
-            cudaGetDevice(&dev);
-            cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-            return n > 0 ? n : 148;
-        }();
+        int sm_count = current_device_sm_count();
+        if (sm_count <= 0) sm_count = 148;
         cudaError_t e = cudaFuncSetAttribute(store_kvcache_bulk_kernel,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;

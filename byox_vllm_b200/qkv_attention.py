@@ -148,6 +148,12 @@ def qkv_attention(attn, qkv: torch.Tensor, positions: torch.Tensor, q_weight, k_
         return _attn.prefill_varlen(q, k, v, context.cu_seqlens_q, context.cu_seqlens_k,
                                     context.max_seqlen_q, context.max_seqlen_k, attn.scale,
                                     block_tables=context.block_tables)
+    if not have_cache:
+        # Attention.forward would be called with the empty placeholder caches of __init__
+        # (attention.py:62): a decode step has nothing to attend to before ModelRunner injected
+        # the cache views (model_runner.py:145-150)
+        raise RuntimeError("byox_vllm_b200: decode step before the KV cache was injected into "
+                           "the Attention module (k_cache / v_cache are still empty)")
     plan, chunks = _attn._step_plan(context, qkv.size(0), Hq, Hkv, k_cache)
     if plan is not None:
         # shared-prefix cascade: its prefix pass reads q through a TMA map, so q is materialised
