@@ -301,12 +301,6 @@ static int store_decode_impl(const void* q, int64_t q_row_stride, const void* ke
     if (num_splits == 1) p.tun.dyn_ok = 0;  // no counters: static regime (one CTA walks every item)
     p.trace = g_decode_trace;
     p.overlap = (g_decode_overlap.load(std::memory_order_relaxed) != 0 && plan == nullptr) ? 1 : 0;
-    static const int prefetch_tiles = [] {
-        const char* e = std::getenv("B200ATTN_DECODE_PREFETCH");
-        const int v = e ? std::atoi(e) : 6;
-        return v < 0 ? 0 : (v > 64 ? 64 : v);
-    }();
-    p.prefetch_tiles = prefetch_tiles;
     p.scale_log2 = scale * 1.4426950408889634f;
     if (with_store && fused_store) {
         p.new_key = key;

@@ -128,9 +128,6 @@ struct DecodeParams {
     // Requires that context_lens / block_tables are not written by that kernel. Ignored with the
     // cascade armed (the launch is then a dependent of the prefix pass).
     int32_t overlap;
-    // K/V tiles the producer asks the L2 for ahead of the shared-memory ring
-    // (cp.async.bulk.prefetch.tensor; B200ATTN_DECODE_PREFETCH, 0 = off)
-    int32_t prefetch_tiles;
     // debug: 16 uint64 stamps per CTA (b200attn_debug_decode_trace); nullptr = the product kernel
     unsigned long long* trace;
 };

@@ -699,29 +699,6 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
                 }
                 const int block_id = __shfl_sync(0xffffffffu, my_block, page - page_base);
                 const int slot = block_id * p.block_size + in_page * kTile;
-                // L2 run-ahead: a CTA keeps only kStages tiles (96 KiB) in flight through the ring,
-                // ~64 GB/s at HBM latency — what bounds the tail of a ragged batch, when the few
-                // CTAs with long rows stream alone. Tiles beyond the ring are requested into the
-                // L2 now, so the ring later refills at L2 latency. (Tiles outside the 32-page
-                // window in registers, and the row's newest tile before the grid-dependency wait,
-                // are simply not prefetched.)
-                if (p.prefetch_tiles > 0) {
-                    const int d_lo = t == cur.t_begin ? kStages : p.prefetch_tiles;
-                    for (int dd = d_lo; dd <= p.prefetch_tiles; ++dd) {
-                        const int tp = t + dd;
-                        const int pg = idiv_rcp(tp, tiles_per_page, rcp_tpp);
-                        const bool ok = tp < cur.t_end && pg - page_base < 32 && pg <= last_page &&
-                                        (waited || tp != cur.tiles_total - 1);
-                        const int blk = __shfl_sync(0xffffffffu, my_block, (pg - page_base) & 31);
-                        if (ok && lane == 0) {
-                            const int ps = blk * p.block_size + (tp - pg * tiles_per_page) * kTile;
-                            tma_prefetch_l2_3d(&k_map, 0, cur.kvh, ps);
-                            tma_prefetch_l2_3d(&k_map, 64, cur.kvh, ps);
-                            tma_prefetch_l2_3d(&v_map, 0, cur.kvh, ps);
-                            tma_prefetch_l2_3d(&v_map, 64, cur.kvh, ps);
-                        }
-                    }
-                }
                 if (lane == 0) {
                     uint8_t* dst = smem + stage * kStageBytes;
                     mbar_wait(&empty_bar[stage], phase ^ 1u);
