@@ -1,9 +1,8 @@
-for m in 1 2; do
-  B200ATTN_EXP_EMU=$m timeout 200 python bench.py --workload prefill > gpurun_out/r02_prefill_v6_emu_$m.json 2> gpurun_out/err_$m.txt; tail -2 gpurun_out/err_$m.txt
-  python - <<EOF
-import json
-d=json.loads(open("gpurun_out/r02_prefill_v6_emu_$m.json").read())["extra"]
-print("== emu $m")
-for k,v in d.items(): print(k, "ms %.4f frac %.3f vsFA %.2f diff %.4f"%(v["ms_per_launch"],v["frac"],v.get("vs_flash_attn",0),v.get("max_abs_diff_vs_flash_attn",-1)))
-EOF
-done
+timeout 300 python -m pytest tests/test_gpu_decode.py tests/test_gpu_cascade.py tests/test_gpu_guard_bands.py -x -q 2>&1 | tail -2
+for d in 0 3 6 12; do echo "== prefetch $d"; B200ATTN_DECODE_PREFETCH=$d timeout 200 python tools/sweep_ragged_splits.py 2>&1 | python -c "
+import sys, json
+for l in sys.stdin:
+    try: r = json.loads(l)
+    except Exception: continue
+    print(r['B'], r['ctx'], r['heads'], 'ov' if r['overlap'] else '--', r['us']['None'], r['auto_frac'])
+"; done
