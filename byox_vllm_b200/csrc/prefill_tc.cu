@@ -590,10 +590,27 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
 
         uint32_t kv_it = 0, q_it = 0;
         uint32_t sp_it[2] = {0, 0};  // S/P rounds per sub-tile so far (s_full / p_full phases)
-        Item it;
-        for (int k = 0; consume_item(k, bar, items, it); ++k) {
+        // Items are picked up one ahead: the next item is read from the ring at the top of the
+        // current item's LAST tile step (its loads do not depend on that step, so it has been
+        // published or is about to be), and its first S MMAs go out right behind the last PV
+        // instead of a ring wait + ~1000 clk of cold code later.
+        Item it, nxt;
+        bool have = consume_item(0, bar, items, it);
+        for (int k = 0; have; ++k) {
+            bool got_next = false, more = false;
+            auto take_next = [&]() {
+                if (!got_next) {
+                    more = consume_item(k + 1, bar, items, nxt);
+                    got_next = true;
+                }
+            };
             const int n_max = it.n_max;
-            if (n_max == 0) continue;
+            if (n_max == 0) {
+                take_next();
+                it = nxt;
+                have = more;
+                continue;
+            }
             unsigned long long* tri = nullptr;
             if constexpr (kTrace) {
                 if (trace != nullptr && lane == 0 && q_it < kTraceSteps)
@@ -621,6 +638,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
                         tr = trace + (2 * kTraceSteps + tr_step) * 4;
                     ++tr_step;
                 }
+                if (j == n_max - 1) take_next();
                 wait_bar(&bar->v_full[s], (kv_it / kStages) & 1u);
                 // Rows at or beyond Lk inside the tile are masked (P = 0), but 0 * NaN would still
                 // poison O: clear those V rows (unwritten cache slots may hold anything).
@@ -666,6 +684,9 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
                 __syncwarp();
             }
             if (kTrace && tri) tri[3] = clock64();
+            take_next();
+            it = nxt;
+            have = more;
         }
     } else if (warp < kProducerWarp) {
         // ============================ softmax / correction / epilogue ============================
@@ -678,8 +699,11 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
         const float c = p.scale_log2;
         uint32_t sp_it = 0;   // S/P rounds of this sub-tile so far
         uint32_t o_it = 0;    // items of this sub-tile with work so far
-        Item it;
-        for (int k = 0; consume_item(k, bar, items, it); ++k) {
+        // The next item is read from the ring between the last P signal and the epilogue, i.e.
+        // while this item's last PV MMAs run.
+        Item it, nxt;
+        bool have = consume_item(0, bar, items, it);
+        for (int k = 0; have; ++k) {
         // (selects, not it.row0[i]: a runtime index would push the item into local memory)
         const int row = (i ? it.row0[1] : it.row0[0]) + (r >> g_shift);  // token (cascade: batch row)
         const int head = it.kvh * p.group + (r & (p.group - 1));
@@ -778,6 +802,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
             if (kTrace && tr) tr[3] = clock64();
         }
 
+        const bool more = consume_item(k + 1, bar, items, nxt);
         if constexpr (kCascade) {
             // ---- epilogue: normalised fp32 partial + log2-sum-exp of this prefix chunk ----
             const int b = row;
@@ -846,6 +871,8 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
             for (int v = 0; v < 16; ++v) st_v4(orow_g + v * 16, make_int4(0, 0, 0, 0));
         }
         }  // !kCascade
+        it = nxt;
+        have = more;
         }  // items
     }
 
