@@ -340,6 +340,27 @@ __device__ void build_schedule(const PrefillParams& p, Barriers* bar, int32_t* p
         keys[t] = key;
     }
     __syncthreads();
+    if (T <= 2 * kTcThreads) {
+        // Few items (every BASELINE prefill step): rank sort, no barrier rounds. A key's position
+        // is the number of smaller keys (keys are unique); all threads read the same address in
+        // each iteration (shared-memory broadcast).
+        uint32_t mine[2] = {0xffffffffu, 0xffffffffu};
+        int rank[2] = {0, 0};
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+            if (tid + h * kTcThreads < T) mine[h] = keys[tid + h * kTcThreads];
+        for (int u = 0; u < T; ++u) {
+            const uint32_t other = keys[u];
+            rank[0] += other < mine[0];
+            rank[1] += other < mine[1];
+        }
+        __syncthreads();
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+            if (tid + h * kTcThreads < T) keys[rank[h]] = mine[h];
+        __syncthreads();
+        return;
+    }
     for (int k = 2; k <= n2; k <<= 1) {
         for (int j = k >> 1; j > 0; j >>= 1) {
             for (int idx = tid; idx < n2; idx += kTcThreads) {
@@ -388,6 +409,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
         if (static_cast<int>(blockIdx.y) >= pc.valid) return;  // uniform (also: no shared prefix)
     }
     const int g_shift = __ffs(p.group) - 1;  // G is a power of two (128 % G == 0)
+    const long long t_entry = kTrace ? clock64() : 0;
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>(
@@ -442,6 +464,12 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
             trace = p.trace + static_cast<size_t>(blockIdx.x) * kTraceStreams * kTraceSteps * 4;
     }
     uint32_t tr_step = 0;  // tile steps this role has stamped
+    if constexpr (kTrace) {  // last slot of the producer's item stream: {CTA entry, roles start}
+        if (trace != nullptr && threadIdx.x == 0) {
+            trace[(4 * kTraceSteps + kTraceSteps - 1) * 4 + 0] = t_entry;
+            trace[(4 * kTraceSteps + kTraceSteps - 1) * 4 + 1] = clock64();
+        }
+    }
 
     // setmaxnreg sits inside each role branch so ptxas budgets every role separately.
     if (warp == kProducerWarp) {

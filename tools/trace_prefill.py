@@ -103,8 +103,17 @@ def main():
             rec["cta0_items"] = [
                 {"issuer": [int(x - base) for x in t[0, 3, n]], "producer": [int(x - base) for x in t[0, 4, n]],
                  "softmax0": [int(x - base) for x in t[0, 5, n]]} for n in range(8)]
+            # per traced CTA: prologue (entry -> roles start) and busy span (roles start -> last row
+            # stored by softmax group 0), in clocks; the kernel itself took event_us
+            spans = []
+            for cta in range(CTAS):
+                entry, start = int(t[cta, 4, STEPS - 1, 0]), int(t[cta, 4, STEPS - 1, 1])
+                last = int(t[cta, 5, :, 3].max())
+                n_items = int((t[cta, 5, :STEPS - 1, 3] > 0).sum())
+                spans.append({"prologue": start - entry, "busy": last - start, "items": n_items})
+            rec["cta_spans"] = spans
             rows.append(rec)
-            print(json.dumps({k2: v2 for k2, v2 in rec.items() if k2 not in ("cta0_first_steps", "cta0_items")}), flush=True)
+            print(json.dumps({k2: v2 for k2, v2 in rec.items() if k2 not in ("cta0_first_steps", "cta0_items", "cta_spans")}), flush=True)
     (ROOT / "gpurun_out").mkdir(exist_ok=True)
     (ROOT / "gpurun_out" / "trace_prefill.json").write_text(json.dumps(rows, indent=1))
 
