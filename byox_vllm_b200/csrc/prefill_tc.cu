@@ -323,7 +323,7 @@ __device__ void build_schedule(const PrefillParams& p, Barriers* bar, int32_t* p
     if (!bar->use_keys) return;  // one sequence (cost is monotone in the pair index) or too many
     int n2 = 1;
     while (n2 < T) n2 <<= 1;
-    for (int t = tid; t < n2; t += kTcThreads) {
+    for (int t = tid; t < max(n2, 4); t += kTcThreads) {  // (>= 4: the rank sort reads uint4)
         uint32_t key = 0xffffffffu;
         if (t < T) {
             int lo = 0, hi = S;
@@ -349,10 +349,14 @@ __device__ void build_schedule(const PrefillParams& p, Barriers* bar, int32_t* p
 #pragma unroll
         for (int h = 0; h < 2; ++h)
             if (tid + h * kTcThreads < T) mine[h] = keys[tid + h * kTcThreads];
-        for (int u = 0; u < T; ++u) {
-            const uint32_t other = keys[u];
-            rank[0] += other < mine[0];
-            rank[1] += other < mine[1];
+        if (tid < T) {  // (keys[T .. n2) hold the 0xffffffff padding: never smaller)
+            const uint4* k4 = reinterpret_cast<const uint4*>(keys);
+            for (int u = 0; u < n2 / 4 + (n2 < 4); ++u) {
+                const uint4 o = k4[u];
+#pragma unroll
+                for (int h = 0; h < 2; ++h)
+                    rank[h] += (o.x < mine[h]) + (o.y < mine[h]) + (o.z < mine[h]) + (o.w < mine[h]);
+            }
         }
         __syncthreads();
 #pragma unroll
