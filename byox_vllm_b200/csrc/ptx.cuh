@@ -158,7 +158,13 @@ __device__ __forceinline__ void st_v4(void* p, const int4& v) {
                  : "memory");
 }
 
-// 32-byte store (sm_100: 256-bit global accesses); p is 32-byte aligned.
+// 32-byte read-only load / store (sm_100: 256-bit global accesses); p is 32-byte aligned.
+__device__ __forceinline__ void ld_nc_v8(const void* p, uint32_t (&v)[8]) {
+    asm volatile("ld.global.nc.L1::no_allocate.v8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]),
+                   "=r"(v[6]), "=r"(v[7])
+                 : "l"(p));
+}
 __device__ __forceinline__ void st_v8(void* p, const uint32_t (&v)[8]) {
     asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "r"(v[0]),
                  "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
