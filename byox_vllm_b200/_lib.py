@@ -12,8 +12,20 @@ from pathlib import Path
 
 LIB_PATH = Path(__file__).resolve().parent / "libb200attn.so"
 
-ABI_VERSION = 8
+ABI_VERSION = 9
 DTYPE_BF16 = 0
+DTYPE_F16 = 1
+
+
+def dtype_code(dtype) -> int:
+    """C-ABI dtype code of a torch dtype (bf16 -> 0, fp16 -> 1); anything else raises."""
+    import torch
+
+    if dtype == torch.bfloat16:
+        return DTYPE_BF16
+    if dtype == torch.float16:
+        return DTYPE_F16
+    raise RuntimeError(f"byox_vllm_b200: 16-bit dtypes only (bf16 / fp16), got {dtype}")
 
 E_BADARG = -1
 E_UNSUPPORTED = -2

@@ -68,7 +68,7 @@ def store_kvcache(key: torch.Tensor, value: torch.Tensor, k_cache: torch.Tensor,
     lib = _lib.load()
     rc = lib.b200attn_store_kvcache(
         key.data_ptr(), key.stride(0), value.data_ptr(), value.stride(0), k_cache.data_ptr(),
-        v_cache.data_ptr(), slot_mapping.data_ptr(), N, D, num_slots, _lib.DTYPE_BF16,
+        v_cache.data_ptr(), slot_mapping.data_ptr(), N, D, num_slots, _lib.dtype_code(key.dtype),
         _stream(key.device))
     _lib.check("b200attn_store_kvcache", rc)
 
@@ -163,8 +163,7 @@ def paged_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
     B, Hq, D = q.shape
     num_blocks, block_size, Hkv, Dc = k_cache.shape
     assert Dc == D and v_cache.shape == k_cache.shape
-    if q.dtype != torch.bfloat16:
-        raise RuntimeError(f"paged_decode: bf16 only, got {q.dtype}")
+    dcode = _lib.dtype_code(q.dtype)  # bf16 or fp16
     assert k_cache.dtype == q.dtype and v_cache.dtype == q.dtype
     assert k_cache.is_contiguous() and v_cache.is_contiguous()
     assert context_lens.dtype == torch.int32 and context_lens.numel() == B
@@ -208,7 +207,7 @@ def paged_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
             k_cache.data_ptr(), v_cache.data_ptr(), block_tables.data_ptr(),
             block_tables.stride(0), W, context_lens.data_ptr(), out.data_ptr(), _ptr(ws),
             ws_bytes, B, Hq, Hkv, D, block_size, num_blocks, float(scale), num_splits,
-            plan.data_ptr(), prefix_chunks, _lib.DTYPE_BF16, stream)
+            plan.data_ptr(), prefix_chunks, dcode, stream)
         _lib.check("b200attn_store_decode_cascade", rc)
     elif key is not None:
         rc = lib.b200attn_store_decode(
@@ -216,14 +215,14 @@ def paged_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
             slot_mapping.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(),
             block_tables.data_ptr(), block_tables.stride(0), W, context_lens.data_ptr(),
             out.data_ptr(), _ptr(ws), ws_bytes, B, Hq, Hkv, D, block_size, num_blocks,
-            float(scale), num_splits, _lib.DTYPE_BF16, stream)
+            float(scale), num_splits, dcode, stream)
         _lib.check("b200attn_store_decode", rc)
     else:
         rc = lib.b200attn_decode(
             q.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(), block_tables.data_ptr(),
             block_tables.stride(0), W, context_lens.data_ptr(), out.data_ptr(), _ptr(ws),
             ws_bytes, B, Hq, Hkv, D, block_size, num_blocks, float(scale), num_splits,
-            _lib.DTYPE_BF16, stream)
+            dcode, stream)
         _lib.check("b200attn_decode", rc)
     return out
 
@@ -240,8 +239,7 @@ def prefill_varlen(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, cu_seqlens
     """
     _require_cuda(q, k, v, cu_seqlens_q, cu_seqlens_k, block_tables)
     total_q, Hq, D = q.shape
-    if q.dtype != torch.bfloat16:
-        raise RuntimeError(f"prefill_varlen: bf16 only, got {q.dtype}")
+    dcode = _lib.dtype_code(q.dtype)  # bf16 or fp16
     assert k.dtype == q.dtype and v.dtype == q.dtype
     assert cu_seqlens_q.dtype == torch.int32 and cu_seqlens_k.dtype == torch.int32
     assert cu_seqlens_q.is_contiguous() and cu_seqlens_k.is_contiguous()
@@ -265,7 +263,7 @@ def prefill_varlen(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, cu_seqlens
             q.data_ptr(), k.data_ptr(), k.stride(0), v.data_ptr(), v.stride(0), None, None, None,
             0, 0, cu_seqlens_q.data_ptr(), cu_seqlens_k.data_ptr(), num_seqs, total_q, k.size(0),
             int(max_seqlen_q), int(max_seqlen_k), out.data_ptr(), Hq, Hkv, D, 0, 0, float(scale),
-            _lib.DTYPE_BF16, stream)
+            dcode, stream)
     else:
         assert k.dim() == 4 and v.shape == k.shape and k.size(3) == D
         assert k.is_contiguous() and v.is_contiguous()
@@ -276,7 +274,7 @@ def prefill_varlen(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, cu_seqlens
             q.data_ptr(), None, 0, None, 0, k.data_ptr(), v.data_ptr(), block_tables.data_ptr(),
             block_tables.stride(0), block_tables.size(1), cu_seqlens_q.data_ptr(),
             cu_seqlens_k.data_ptr(), num_seqs, total_q, 0, int(max_seqlen_q), int(max_seqlen_k),
-            out.data_ptr(), Hq, Hkv, D, block_size, num_blocks, float(scale), _lib.DTYPE_BF16,
+            out.data_ptr(), Hq, Hkv, D, block_size, num_blocks, float(scale), dcode,
             stream)
     _lib.check("b200attn_prefill_varlen", rc)
     return out

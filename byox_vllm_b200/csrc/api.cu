@@ -160,8 +160,8 @@ int prefill_mode_from_env() {
 
 int check_attn_shape(int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim,
                      int32_t block_size, int32_t dtype) {
-    if (dtype != B200ATTN_DTYPE_BF16)
-        return fail(B200ATTN_E_UNSUPPORTED, "dtype %d unsupported (bf16 only)", dtype);
+    if (dtype != B200ATTN_DTYPE_BF16 && dtype != B200ATTN_DTYPE_F16)
+        return fail(B200ATTN_E_UNSUPPORTED, "dtype %d unsupported (0 = bf16, 1 = fp16)", dtype);
     if (head_dim != b200::kHeadDim)
         return fail(B200ATTN_E_UNSUPPORTED, "head_dim %d unsupported (128 only)", head_dim);
     if (num_q_heads <= 0 || num_kv_heads <= 0 || num_q_heads % num_kv_heads != 0)
@@ -215,6 +215,8 @@ static int store_decode_impl(const void* q, int64_t q_row_stride, const void* ke
                              int32_t num_splits, const int32_t* plan, int32_t prefix_chunks,
                              int32_t dtype, void* stream, const b200::NormRopeArgs* nr) {
     if (int rc = check_attn_shape(num_q_heads, num_kv_heads, head_dim, block_size, dtype)) return rc;
+    if (nr && dtype != B200ATTN_DTYPE_BF16)
+        return fail(B200ATTN_E_UNSUPPORTED, "the fused q/k norm + RoPE decode is bf16 only");
     if (prefix_chunks < 0 || prefix_chunks > 32 || (prefix_chunks > 0) != (plan != nullptr))
         return fail(B200ATTN_E_BADARG, "plan and prefix_chunks (0..32) must be given together");
     if (nr && prefix_chunks > 0)
@@ -301,6 +303,7 @@ static int store_decode_impl(const void* q, int64_t q_row_stride, const void* ke
     if (num_splits == 1) p.tun.dyn_ok = 0;  // no counters: static regime (one CTA walks every item)
     p.trace = g_decode_trace;
     p.overlap = (g_decode_overlap.load(std::memory_order_relaxed) != 0 && plan == nullptr) ? 1 : 0;
+    p.f16 = dtype == B200ATTN_DTYPE_F16 ? 1 : 0;
     p.scale_log2 = scale * 1.4426950408889634f;
     if (with_store && fused_store) {
         p.new_key = key;
@@ -351,6 +354,7 @@ static int store_decode_impl(const void* q, int64_t q_row_stride, const void* ke
         pp.block_size = block_size;
         pp.scale_log2 = p.scale_log2;
         pp.plan = plan;
+        pp.f16 = dtype == B200ATTN_DTYPE_F16 ? 1 : 0;
         pp.ws_o = p.prefix_o;
         pp.ws_lse = p.prefix_lse;
         pp.batch = batch;
@@ -401,8 +405,8 @@ int b200attn_store_kvcache(const void* key, int64_t key_row_stride, const void* 
                            int64_t value_row_stride, void* k_cache, void* v_cache,
                            const int32_t* slot_mapping, int32_t n_tokens, int32_t row_elems,
                            int64_t num_slots, int32_t dtype, void* stream) {
-    if (dtype != B200ATTN_DTYPE_BF16)
-        return fail(B200ATTN_E_UNSUPPORTED, "dtype %d unsupported (16-bit bf16 only)", dtype);
+    if (dtype != B200ATTN_DTYPE_BF16 && dtype != B200ATTN_DTYPE_F16)  // a byte copy of 16-bit rows
+        return fail(B200ATTN_E_UNSUPPORTED, "dtype %d unsupported (0 = bf16, 1 = fp16)", dtype);
     if (n_tokens < 0 || row_elems <= 0 || num_slots < 0)
         return fail(B200ATTN_E_BADARG, "negative size");
     if (n_tokens == 0) return 0;
@@ -574,6 +578,7 @@ int b200attn_prefill_varlen(const void* q, const void* key, int64_t key_row_stri
     p.group = num_q_heads / num_kv_heads;
     p.block_size = block_size;
     p.scale_log2 = scale * 1.4426950408889634f;
+    p.f16 = dtype == B200ATTN_DTYPE_F16 ? 1 : 0;
     p.trace = g_prefill_trace;
     // Kernel choice from host-visible sizes only. The tcgen05 kernel works on pairs of 128-row
     // tiles of (token, group head) rows and 128-token KV tiles: it needs pages that are multiples

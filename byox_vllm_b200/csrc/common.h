@@ -128,6 +128,7 @@ struct DecodeParams {
     // Requires that context_lens / block_tables are not written by that kernel. Ignored with the
     // cascade armed (the launch is then a dependent of the prefix pass).
     int32_t overlap;
+    int32_t f16;  // 1: fp16 storage / operands (dtype code 1), 0: bf16
     // debug: 16 uint64 stamps per CTA (b200attn_debug_decode_trace); nullptr = the product kernel
     unsigned long long* trace;
 };
@@ -191,6 +192,7 @@ struct PrefillParams {
     int32_t prefix_chunks; // split-KV chunks over the shared prefix (grid.y)
     int32_t ws_slot0;      // chunk c writes slot ws_slot0 + c
     int32_t ws_slots;
+    int32_t f16;           // 1: fp16 storage / operands (dtype code 1), 0: bf16
     int32_t sched_mode;    // prefill_tc.cu: 0 clc (work stealing), 1 static zig-zag, 2 one item per CTA
     // debug: [kTraceCtas][kTraceStreams][kTraceSteps][4] uint64 stamps (b200attn_debug_prefill_trace); nullptr =
     // the product kernel

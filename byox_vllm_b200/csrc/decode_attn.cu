@@ -98,6 +98,7 @@ struct MergeSrc {
 // One warp combines the sources of a row into out[row]: lane l holds the weight of source l of
 // each group of 32; the O loads of 8 sources are issued together so their latencies overlap.
 // Loads go through L2 (ld.global.cg): the partials were written by other SMs a moment ago.
+template <bool kF16>
 __device__ __forceinline__ void merge_row(const MergeSrc& src, __nv_bfloat16* __restrict__ out,
                                           int lane) {
     const int n = src.n_piece + src.n_prefix;
@@ -138,8 +139,8 @@ __device__ __forceinline__ void merge_row(const MergeSrc& src, __nv_bfloat16* __
     for (int off = 16; off > 0; off >>= 1) wsum += __shfl_xor_sync(0xffffffffu, wsum, off);
     const float inv = wsum > 0.f ? 1.f / wsum : 0.f;
     uint2 pk;
-    pk.x = pack_bf16x2(acc.x * inv, acc.y * inv);
-    pk.y = pack_bf16x2(acc.z * inv, acc.w * inv);
+    pk.x = pack_16x2<kF16>(acc.x * inv, acc.y * inv);
+    pk.y = pack_16x2<kF16>(acc.z * inv, acc.w * inv);
     *reinterpret_cast<uint2*>(out + src.row * kHeadDim + lane * 4) = pk;
 }
 
@@ -359,7 +360,10 @@ __device__ __forceinline__ unsigned long long global_timer_ns() {
 // kRows = true: the rows engine - grid (KV head, split, sequence), one piece per CTA, the hardware
 //   block scheduler hands out the rows. No scan, no queue: every CTA derives its piece from its
 //   own context_lens entry, so its first TMA is two dependent loads from kernel entry.
-template <int kStages, bool kTrace, bool kRows>
+// kF16: fp16 storage / MMA operands (dtype code 1) instead of bf16; the 16-bit zero pattern, the
+// tile geometry and the fp32 softmax are the same. The fused q/k norm + RoPE prologue
+// (b200attn_qkv_decode) exists for bf16 only.
+template <int kStages, bool kTrace, bool kRows, bool kF16 = false>
 __global__ void __launch_bounds__(kDecodeThreads, 2)
 decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
                      const __grid_constant__ CUtensorMap v_map, const DecodeParams p) {
@@ -520,7 +524,7 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
                     for (int h = warp; h < G; h += kConsumerWarps + 1) {
                         src.h_local = h;
                         src.row = q_row0 + h;
-                        merge_row(src, static_cast<__nv_bfloat16*>(p.out), lane);
+                        merge_row<kF16>(src, static_cast<__nv_bfloat16*>(p.out), lane);
                     }
                 }
             }
@@ -846,7 +850,7 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
                 uint32_t a[4];
                 ldmatrix_x4(a, kb + (ks >> 2) * kSubTileBytes +
                                    swz128(k_row, (ks & 3) * 2 + k_csel));
-                mma_bf16_16816(s, a, qf[ks][0], qf[ks][1]);
+                mma_16816<kF16>(s, a, qf[ks][0], qf[ks][1]);
             }
 
             // ---- mask + online softmax (log2 domain) ----
@@ -890,8 +894,8 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
             }
 
             // ---- O^T[128 dims x 8 heads] = alpha * O^T + V^T . P^T ----
-            const uint32_t pb0 = movmatrix_trans(pack_bf16x2(p0, p1));
-            const uint32_t pb1 = movmatrix_trans(pack_bf16x2(p2, p3));
+            const uint32_t pb0 = movmatrix_trans(pack_16x2<kF16>(p0, p1));
+            const uint32_t pb1 = movmatrix_trans(pack_16x2<kF16>(p2, p3));
 #pragma unroll
             for (int mt = 0; mt < 8; ++mt) {
                 uint32_t a[4];
@@ -901,7 +905,7 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
                 o[mt][1] *= alpha1;
                 o[mt][2] *= alpha0;
                 o[mt][3] *= alpha1;
-                mma_bf16_16816(o[mt], a, pb0, pb1);
+                mma_16816<kF16>(o[mt], a, pb0, pb1);
             }
 
             __syncwarp();
@@ -1030,8 +1034,8 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
                 }
                 const bool live = l > 0.f;
                 uint2 pk;
-                pk.x = pack_bf16x2(live ? acc.x / l : 0.f, live ? acc.y / l : 0.f);
-                pk.y = pack_bf16x2(live ? acc.z / l : 0.f, live ? acc.w / l : 0.f);
+                pk.x = pack_16x2<kF16>(live ? acc.x / l : 0.f, live ? acc.y / l : 0.f);
+                pk.y = pack_16x2<kF16>(live ? acc.z / l : 0.f, live ? acc.w / l : 0.f);
                 *reinterpret_cast<uint2*>(static_cast<__nv_bfloat16*>(p.out) + row * kHeadDim +
                                           4 * lane) = pk;
             } else {
@@ -1065,7 +1069,7 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
             for (int h = warp; h < G; h += kConsumerWarps) {
                 src.h_local = h;
                 src.row = q_row0 + h;
-                merge_row(src, static_cast<__nv_bfloat16*>(p.out), lane);
+                merge_row<kF16>(src, static_cast<__nv_bfloat16*>(p.out), lane);
             }
         }
         if (kTrace && threadIdx.x == 0) {
@@ -1087,7 +1091,7 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
     if (p.plan != nullptr) grid_dependency_wait();
 }
 
-template <int kStages, bool kTrace, bool kRows>
+template <int kStages, bool kTrace, bool kRows, bool kF16 = false>
 cudaError_t launch_stream(const DecodeParams& p, const CUtensorMap& k_map, const CUtensorMap& v_map,
                           cudaStream_t stream) {
     constexpr int smem = DecodeSmem<kStages>::kBytes;
@@ -1096,7 +1100,7 @@ cudaError_t launch_stream(const DecodeParams& p, const CUtensorMap& k_map, const
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) dev = 0;
     if (dev < 0 || dev >= 64 || !configured[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(decode_stream_kernel<kStages, kTrace, kRows>,
+        cudaError_t e = cudaFuncSetAttribute(decode_stream_kernel<kStages, kTrace, kRows, kF16>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
         if (dev >= 0 && dev < 64) configured[dev] = true;
@@ -1122,7 +1126,7 @@ cudaError_t launch_stream(const DecodeParams& p, const CUtensorMap& k_map, const
         cfg.numAttrs = 1;
     }
     cudaError_t e =
-        cudaLaunchKernelEx(&cfg, decode_stream_kernel<kStages, kTrace, kRows>, k_map, v_map, p);
+        cudaLaunchKernelEx(&cfg, decode_stream_kernel<kStages, kTrace, kRows, kF16>, k_map, v_map, p);
     count_launch();
     return e != cudaSuccess ? e : cudaGetLastError();
 }
@@ -1335,6 +1339,7 @@ int decode_partition_host(const int32_t* context_lens, int32_t batch, int32_t nu
 cudaError_t launch_decode(const DecodeParams& p, const CUtensorMap& k_map, const CUtensorMap& v_map,
                           cudaStream_t stream) {
     if (p.batch == 0) return cudaSuccess;
+    if (p.f16) return launch_stream<3, false, true, true>(p, k_map, v_map, stream);  // rows engine
     if (decode_engine_rows()) {
         if (p.trace != nullptr) return launch_stream<3, true, true>(p, k_map, v_map, stream);
         switch (decode_stages_from_env()) {

@@ -39,6 +39,7 @@ __device__ __forceinline__ void load_tile_async(uint8_t* smem_tile, RowPtr row_p
     }
 }
 
+template <bool kF16>  // fp16 storage / operands (dtype code 1) instead of bf16
 __global__ void __launch_bounds__(kPrefillThreads, 2)
 prefill_varlen_kernel(const PrefillParams p) {
     extern __shared__ uint8_t smem_raw[];
@@ -160,8 +161,8 @@ prefill_varlen_kernel(const PrefillParams p) {
                 const uint32_t tok = np * 16 + ((lane >> 4) << 3) + (lane & 7);
                 const uint32_t chunk = (ks & 3) * 2 + ((lane >> 3) & 1);
                 ldmatrix_x4(bfr, kb + (ks >> 2) * kHalfBytes + swz128(tok, chunk));
-                mma_bf16_16816(s[2 * np], qf[ks], bfr[0], bfr[1]);
-                mma_bf16_16816(s[2 * np + 1], qf[ks], bfr[2], bfr[3]);
+                mma_16816<kF16>(s[2 * np], qf[ks], bfr[0], bfr[1]);
+                mma_16816<kF16>(s[2 * np + 1], qf[ks], bfr[2], bfr[3]);
             }
         }
 
@@ -215,18 +216,18 @@ prefill_varlen_kernel(const PrefillParams p) {
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk) {  // 16 tokens per k-step
             uint32_t a[4];
-            a[0] = pack_bf16x2(s[2 * kk][0], s[2 * kk][1]);
-            a[1] = pack_bf16x2(s[2 * kk][2], s[2 * kk][3]);
-            a[2] = pack_bf16x2(s[2 * kk + 1][0], s[2 * kk + 1][1]);
-            a[3] = pack_bf16x2(s[2 * kk + 1][2], s[2 * kk + 1][3]);
+            a[0] = pack_16x2<kF16>(s[2 * kk][0], s[2 * kk][1]);
+            a[1] = pack_16x2<kF16>(s[2 * kk][2], s[2 * kk][3]);
+            a[2] = pack_16x2<kF16>(s[2 * kk + 1][0], s[2 * kk + 1][1]);
+            a[3] = pack_16x2<kF16>(s[2 * kk + 1][2], s[2 * kk + 1][3]);
 #pragma unroll
             for (int np = 0; np < 8; ++np) {  // pairs of 8-dim n-tiles
                 uint32_t bfr[4];
                 const uint32_t tok = kk * 16 + (((lane >> 3) & 1) << 3) + (lane & 7);
                 const uint32_t ntile = np * 2 + (lane >> 4);
                 ldmatrix_x4_trans(bfr, vb + (ntile >> 3) * kHalfBytes + swz128(tok, ntile & 7));
-                mma_bf16_16816(o[2 * np], a, bfr[0], bfr[1]);
-                mma_bf16_16816(o[2 * np + 1], a, bfr[2], bfr[3]);
+                mma_16816<kF16>(o[2 * np], a, bfr[0], bfr[1]);
+                mma_16816<kF16>(o[2 * np + 1], a, bfr[2], bfr[3]);
             }
         }
         __syncthreads();  // stage is free for the prefetch issued by the next iteration
@@ -250,9 +251,9 @@ prefill_varlen_kernel(const PrefillParams p) {
         const int chunk = n;  // 8 dims = one 16-byte chunk; this thread holds 2 of its 8 dims
         uint8_t* base = q_smem + (chunk >> 3) * kHalfBytes;
         *reinterpret_cast<uint32_t*>(base + swz128(row_in_tile, chunk & 7) + (lane & 3) * 4) =
-            pack_bf16x2(o[n][0] * inv0, o[n][1] * inv0);
+            pack_16x2<kF16>(o[n][0] * inv0, o[n][1] * inv0);
         *reinterpret_cast<uint32_t*>(base + swz128(row_in_tile + 8, chunk & 7) + (lane & 3) * 4) =
-            pack_bf16x2(o[n][2] * inv1, o[n][3] * inv1);
+            pack_16x2<kF16>(o[n][2] * inv1, o[n][3] * inv1);
     }
     __syncthreads();
     uint8_t* og = static_cast<uint8_t*>(p.out);
@@ -272,13 +273,15 @@ prefill_varlen_kernel(const PrefillParams p) {
 
 }  // namespace
 
-cudaError_t launch_prefill(const PrefillParams& p, cudaStream_t stream) {
+namespace {
+template <bool kF16>
+cudaError_t launch_prefill_t(const PrefillParams& p, cudaStream_t stream) {
     // the opt-in shared-memory size is a per-device function attribute
     static bool configured[64] = {};
     int dev = 0;
     if (cudaError_t e = cudaGetDevice(&dev); e != cudaSuccess) return e;
     if (dev < 0 || dev >= 64 || !configured[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(prefill_varlen_kernel,
+        cudaError_t e = cudaFuncSetAttribute(prefill_varlen_kernel<kF16>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              kPrefillSmem);
         if (e != cudaSuccess) return e;
@@ -286,9 +289,14 @@ cudaError_t launch_prefill(const PrefillParams& p, cudaStream_t stream) {
     }
     const int q_tiles = (p.max_seqlen_q + kBlockM - 1) / kBlockM;
     dim3 grid(q_tiles, p.num_q_heads, p.num_seqs);
-    prefill_varlen_kernel<<<grid, kPrefillThreads, kPrefillSmem, stream>>>(p);
+    prefill_varlen_kernel<kF16><<<grid, kPrefillThreads, kPrefillSmem, stream>>>(p);
     count_launch();
     return cudaGetLastError();
+}
+}  // namespace
+
+cudaError_t launch_prefill(const PrefillParams& p, cudaStream_t stream) {
+    return p.f16 ? launch_prefill_t<true>(p, stream) : launch_prefill_t<false>(p, stream);
 }
 
 }  // namespace b200

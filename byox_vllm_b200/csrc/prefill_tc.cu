@@ -399,7 +399,8 @@ __device__ void build_schedule(const PrefillParams& p, Barriers* bar, int32_t* p
 // first S issued, last step issued}, stream 4 = producer {item fetched, first K/V issued, Q buffer
 // free, all tiles issued}, stream 5 = softmax group 0 {item fetched, last P signalled, O complete,
 // rows stored}; layout [cta][stream][step][4] uint64 (tools/trace_prefill.py).
-template <bool kCascade, int kEmu, bool kTrace = false>
+// kF16: fp16 storage / MMA operands (dtype code 1 of the C-ABI) instead of bf16.
+template <bool kCascade, int kEmu, bool kTrace = false, bool kF16 = false>
 __global__ void __launch_bounds__(kTcThreads, 1)
 prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
                   const __grid_constant__ CUtensorMap k_map,
@@ -554,8 +555,8 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
     } else if (warp == kMmaWarp) {
         // ============================ MMA issuer ============================
         tc::reg_dec<kRegsControl>();
-        constexpr uint32_t idesc_s = tc::idesc_bf16_f32(kTM, kTN, false);
-        constexpr uint32_t idesc_o = tc::idesc_bf16_f32(kTM, kHeadDim, true);
+        constexpr uint32_t idesc_s = tc::idesc_f32acc(kTM, kTN, false, kF16);
+        constexpr uint32_t idesc_o = tc::idesc_f32acc(kTM, kHeadDim, true, kF16);
         // Every tcgen05.mma operand below is a COMPILE-TIME constant, so an MMA is a few uniform
         // moves + UTCHMMA. With run-time descriptors ptxas cannot prove warp-uniformity and emits
         // ~13 dependent vector instructions per MMA (ELECT / R2UR broadcast loop), 75-84 clk for
@@ -822,7 +823,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
                         x.y = fast_exp2(x.y);
                     }
                     ls[t & 1] = __fadd2_rn(ls[t & 1], x);
-                    pr[t] = pack_bf16x2(x.x, x.y);
+                    pr[t] = pack_16x2<kF16>(x.x, x.y);
                 }
                 tc::tmem_st32(s_tmem + hh * 32, pr);
             }
@@ -887,7 +888,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
                         uint32_t pk[8];               // LSU work of 16-byte ones
 #pragma unroll
                         for (int w = 0; w < 8; ++w)
-                            pk[w] = pack_bf16x2(__uint_as_float(orow[v8 * 16 + 2 * w]) * inv,
+                            pk[w] = pack_16x2<kF16>(__uint_as_float(orow[v8 * 16 + 2 * w]) * inv,
                                                 __uint_as_float(orow[v8 * 16 + 2 * w + 1]) * inv);
                         st_v8(orow_g + q4 * 64 + v8 * 32, pk);
                     }
@@ -936,7 +937,7 @@ int exp_emu_from_env(int dflt) {
 constexpr int kMaxDevices = 64;
 constexpr int kDefaultExpEmu = 0;
 
-template <bool kCascade, int kEmu, bool kTrace = false>
+template <bool kCascade, int kEmu, bool kTrace = false, bool kF16 = false>
 cudaError_t launch_tc(dim3 grid, const PrefillParams& p, const CUtensorMap& q_map,
                       const CUtensorMap& k_map, const CUtensorMap& v_map, cudaStream_t stream) {
     // the opt-in shared-memory size is a per-device function attribute
@@ -944,13 +945,13 @@ cudaError_t launch_tc(dim3 grid, const PrefillParams& p, const CUtensorMap& q_ma
     int dev = 0;
     if (cudaError_t e = cudaGetDevice(&dev); e != cudaSuccess) return e;
     if (dev < 0 || dev >= kMaxDevices || !configured[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(prefill_tc_kernel<kCascade, kEmu, kTrace>,
+        cudaError_t e = cudaFuncSetAttribute(prefill_tc_kernel<kCascade, kEmu, kTrace, kF16>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              kTcSmemBytes);
         if (e != cudaSuccess) return e;
         if (dev >= 0 && dev < kMaxDevices) configured[dev] = true;
     }
-    prefill_tc_kernel<kCascade, kEmu, kTrace><<<grid, kTcThreads, kTcSmemBytes, stream>>>(
+    prefill_tc_kernel<kCascade, kEmu, kTrace, kF16><<<grid, kTcThreads, kTcSmemBytes, stream>>>(
         q_map, k_map, v_map, p);
     count_launch();
     return cudaGetLastError();
@@ -960,6 +961,9 @@ template <bool kCascade>
 cudaError_t launch_tc_emu(int emu, dim3 grid, const PrefillParams& p, const CUtensorMap& q_map,
                           const CUtensorMap& k_map, const CUtensorMap& v_map,
                           cudaStream_t stream) {
+    if (p.f16)  // fp16: the default exponentials only
+        return launch_tc<kCascade, kDefaultExpEmu, false, true>(grid, p, q_map, k_map, v_map,
+                                                                stream);
     switch (emu) {
         case 0: return launch_tc<kCascade, 0>(grid, p, q_map, k_map, v_map, stream);
         case 1: return launch_tc<kCascade, 1>(grid, p, q_map, k_map, v_map, stream);

@@ -38,12 +38,16 @@ __device__ __forceinline__ uint64_t desc_mnmajor(uint32_t smem_addr, uint32_t mn
     return smem_desc_sw128(smem_addr, mn_block_bytes, 1024);
 }
 
-// Instruction descriptor for kind::f16 with bf16 A/B and fp32 accumulate.
-//   [4,6) D format (1 = f32)  [7,10) A format (1 = bf16)  [10,13) B format (1 = bf16)
+// Instruction descriptor for kind::f16 with bf16 (or fp16) A/B and fp32 accumulate.
+//   [4,6) D format (1 = f32)  [7,10) A format (0 = f16, 1 = bf16)  [10,13) B format (same codes)
 //   bit 15 A major (0 = K)    bit 16 B major (0 = K, 1 = MN)   [17,23) N >> 3   [24,29) M >> 4
+__host__ __device__ constexpr uint32_t idesc_f32acc(int m, int n, bool b_mn_major, bool f16) {
+    return (1u << 4) | ((f16 ? 0u : 1u) << 7) | ((f16 ? 0u : 1u) << 10) |
+           ((b_mn_major ? 1u : 0u) << 16) | (static_cast<uint32_t>(n >> 3) << 17) |
+           (static_cast<uint32_t>(m >> 4) << 24);
+}
 __host__ __device__ constexpr uint32_t idesc_bf16_f32(int m, int n, bool b_mn_major) {
-    return (1u << 4) | (1u << 7) | (1u << 10) | ((b_mn_major ? 1u : 0u) << 16) |
-           (static_cast<uint32_t>(n >> 3) << 17) | (static_cast<uint32_t>(m >> 4) << 24);
+    return idesc_f32acc(m, n, b_mn_major, false);
 }
 
 // ----------------------------------------------------------------------------------------------

@@ -172,6 +172,17 @@ def qwen3_attention_forward(self, positions: torch.Tensor,
     """Drop-in for Qwen3Attention.forward (models/qwen3.py:70-86): qkv_proj and o_proj stay the
     reference's own layers (and o_proj's all_reduce stays NCCL); everything between them is the
     fused path."""
+    if hidden_states.dtype != torch.bfloat16:
+        # The fused norm / RoPE kernels restate the reference's bf16 rounding points and exist for
+        # bf16 only; an fp16 checkpoint (model_runner.py:30 takes the dtype from the config) keeps
+        # the reference's own q_norm / k_norm / rotary_emb and enters at Attention.forward, whose
+        # kernels (store, decode, cascade, prefill) do take fp16.
+        from . import install as _install
+
+        if _install._ORIG_QWEN3_FORWARD is None:
+            raise RuntimeError("byox_vllm_b200: fused QKV path is bf16 only and the reference's "
+                               "Qwen3Attention.forward is not available to fall back to")
+        return _install._ORIG_QWEN3_FORWARD(self, positions, hidden_states)
     qkv = self.qkv_proj(hidden_states)
     has_norm = not self.qkv_bias
     o = qkv_attention(self.attn, qkv, positions,

@@ -32,7 +32,10 @@
  *   - Return value: 0 on success; negative = argument / unsupported-shape error
  *     (B200ATTN_E_*); positive = cudaError_t of the failed launch. b200attn_last_error()
  *     returns a thread-local human-readable message for the last non-zero return.
- *   - dtype: 16-bit storage; `dtype` 0 = bfloat16 (the only arithmetic type built in this round).
+ *   - dtype: 16-bit storage; `dtype` 0 = bfloat16, 1 = float16 (store, decode, cascade, prefill;
+ *     fp32 accumulation and softmax in both). The fused q/k norm + RoPE entry points
+ *     (b200attn_qk_norm_rope_store, b200attn_qkv_decode) restate the reference's bf16 rounding
+ *     points and are bf16 only.
  *   - There is no CPU fallback: without a CUDA device every compute entry point fails.
  */
 #ifndef B200ATTN_H_
@@ -45,9 +48,10 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 8
+#define B200ATTN_ABI_VERSION 9
 
 #define B200ATTN_DTYPE_BF16 0
+#define B200ATTN_DTYPE_F16 1
 
 #define B200ATTN_E_BADARG (-1)      /* null pointer / negative size / misalignment           */
 #define B200ATTN_E_UNSUPPORTED (-2) /* head_dim != 128, dtype, block_size % 64, G > 8 ...     */
