@@ -77,3 +77,22 @@ def test_eager_engine_matches_graph_engine(ref_logits):
         a, b = l_o.float(), l_r.float()
         assert ((a - b).abs() <= ATOL + RTOL * b.abs()).all(), f"step {i}"
         assert (a - b).pow(2).mean().sqrt() <= RMS_REL * b.pow(2).mean().sqrt(), f"step {i}"
+
+
+def test_fp16_engine_matches_reference_engine(ref_logits):
+    """An fp16 checkpoint (the reference takes the dtype from the config, model_runner.py:30):
+    reference attention vs the drop-in with every install() flag on - the fused q/k norm + RoPE
+    path is bf16 only, so install()'s forward falls back to the reference's own norm / rotary and
+    enters at Attention.forward, whose kernels run in fp16."""
+    tmp, _ = ref_logits
+    ref = _run(tmp, "ref_f16", "--impl", "ref", "--dtype", "float16")
+    got = _run(tmp, "ours_f16", "--impl", "ours", "--dtype", "float16")
+    assert got["info"]["libb200attn_launches"] > 0
+    assert got["info"]["steps"] == ref["info"]["steps"] > 25
+    for i, ((p_r, n_r, l_r), (p_o, n_o, l_o)) in enumerate(zip(ref["steps"], got["steps"])):
+        assert (p_r, n_r) == (p_o, n_o)
+        assert l_o.dtype == torch.float16
+        a, b = l_o.float(), l_r.float()
+        assert torch.isfinite(a).all()
+        assert ((a - b).abs() <= ATOL + RTOL * b.abs()).all(), f"step {i}"
+        assert (a - b).pow(2).mean().sqrt() <= RMS_REL * b.pow(2).mean().sqrt(), f"step {i}"

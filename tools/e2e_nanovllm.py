@@ -47,13 +47,14 @@ MODELS = {
 }
 
 
-def make_model_dir(name: str) -> str:
-    d = Path(tempfile.gettempdir()) / f"synthetic-qwen3-{name}"
+def make_model_dir(name: str, dtype: str = "bfloat16") -> str:
+    d = Path(tempfile.gettempdir()) / (f"synthetic-qwen3-{name}" +
+                                       ("" if dtype == "bfloat16" else f"-{dtype}"))
     d.mkdir(exist_ok=True)
     cfg = dict(architectures=["Qwen3ForCausalLM"], model_type="qwen3", head_dim=128,
                hidden_act="silu", vocab_size=151936, max_position_embeddings=40960,
                rms_norm_eps=1e-6, rope_theta=1000000, attention_bias=False,
-               torch_dtype="bfloat16", dtype="bfloat16", bos_token_id=151643,
+               torch_dtype=dtype, dtype=dtype, bos_token_id=151643,
                eos_token_id=151645)
     cfg.update(MODELS[name])
     if cfg["vocab_size"] < 151936:

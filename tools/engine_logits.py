@@ -38,6 +38,7 @@ def main():
     ap.add_argument("--fuse-qkv", default="1")
     ap.add_argument("--fast-meta", default="1")
     ap.add_argument("--eager", action="store_true")
+    ap.add_argument("--dtype", default="bfloat16", choices=["bfloat16", "float16"])
     ap.add_argument("--out", required=True)
     args = ap.parse_args()
     os.environ["B200ATTN_FUSE_QKV"] = args.fuse_qkv
@@ -75,7 +76,7 @@ def main():
 
     mr.ModelRunner._run_model = run_model
 
-    path = harness.make_model_dir("tiny")
+    path = harness.make_model_dir("tiny", args.dtype)
     llm = LLM(path, enforce_eager=args.eager, max_model_len=2048, gpu_memory_utilization=0.3,
               tensor_parallel_size=1, max_num_batched_tokens=4096, max_num_seqs=16)
     record.clear()
@@ -91,13 +92,14 @@ def main():
     llm.generate([[rng.randint(0, 19999) for _ in range(77)]], sp(6), use_tqdm=False)
 
     info = {"impl": args.impl, "fuse_qkv": args.fuse_qkv, "fast_meta": args.fast_meta,
-            "eager": args.eager, "steps": len(record),
+            "eager": args.eager, "dtype": args.dtype, "steps": len(record),
             "prefill_steps": sum(1 for r in record if r[0])}
     if args.impl == "ours":
         from byox_vllm_b200 import _lib
 
         info["libb200attn_launches"] = int(_lib.load().b200attn_launch_count())
-    torch.save({"info": info, "steps": [(p, n, l.to(torch.bfloat16)) for p, n, l in record]},
+    keep = torch.bfloat16 if args.dtype == "bfloat16" else torch.float16
+    torch.save({"info": info, "steps": [(p, n, l.to(keep)) for p, n, l in record]},
                args.out)
     print(info, flush=True)
 
