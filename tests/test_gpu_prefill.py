@@ -111,6 +111,17 @@ def test_prefill_persistent_schedule(cuda_dev, case):
         out.fill_(float("nan"))
 
 
+def test_prefill_more_sequences_than_the_schedule_holds(cuda_dev):
+    """> 1023 sequences in one call: the tcgen05 kernel's shared-memory schedule does not hold
+    them, the call takes the mma.sync shape fallback (csrc/api.cu) - same results."""
+    lens = [1 + (i * 7) % 5 for i in range(1100)]
+    c = synth.prefill_case(lens, 16, 8, seed=77)
+    got, _ = _forward(cuda_dev, c, 16, 8)
+    ctx = type("Ctx", (), dict(c.meta))()
+    want = orc.attention_forward_ref(c.q, c.k, c.v, c.k_cache, c.v_cache, ctx, c.scale)
+    assert_close(got, want, "1100 sequences")
+
+
 def test_warmup_path_without_cache(cuda_dev):
     """_warmup_model (model_runner.py:102-113): empty caches, no slots, dense attention."""
     from byox_vllm_b200.attention import Attention
