@@ -105,14 +105,14 @@ struct Barriers {
 constexpr int kItemReaders = 1 + kProducerWarp;  // MMA warp + softmax warps (lane 0 arrives)
 static_assert(sizeof(Barriers) <= 256, "barrier block overflows its shared-memory slot");
 
-// Bounded wait: a protocol bug traps (launch error) after ~2 s instead of hanging the GPU
+// Bounded wait: a protocol bug traps (launch error) after ~20 s instead of hanging the GPU
 // (mbarrier.try_wait itself may block for a while, so the bound is on the clock, not on spins).
 __device__ __forceinline__ void wait_bar(uint64_t* bar, uint32_t parity) {
     if (mbar_try_wait(bar, parity)) return;
     const long long t0 = clock64();
     uint32_t spins = 0;
     while (!mbar_try_wait(bar, parity)) {
-        if ((++spins & 1023u) == 0 && clock64() - t0 > 4000000000LL) __trap();
+        if ((++spins & 1023u) == 0 && clock64() - t0 > 40000000000LL) __trap();
     }
 }
 

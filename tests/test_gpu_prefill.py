@@ -122,6 +122,32 @@ def test_prefill_more_sequences_than_the_schedule_holds(cuda_dev):
     assert_close(got, want, "1100 sequences")
 
 
+def test_prefill_more_items_than_the_sort_holds(cuda_dev):
+    """Two sequences of 66 000 tokens at heads 8/1 (32 tokens per 256-row item): 4126 items per KV
+    head, more than the 4096 sort keys the schedule holds -> the kernel walks them in descending
+    index order instead of cost order (csrc/prefill_tc.cu: use_keys == 0 with several sequences).
+    Sampled rows against an fp32 einsum on the device; every row written."""
+    from byox_vllm_b200.attention import prefill_varlen
+
+    dev = cuda_dev
+    L, S, Hq, Hkv = 66000, 2, 8, 1
+    g = torch.Generator(device=dev).manual_seed(3)
+    q, k, v = synth._qkv(L * S, Hq, Hkv, 128, g, dev)
+    cu = torch.arange(0, S + 1, dtype=torch.int32, device=dev) * L
+    scale = 128 ** -0.5
+    o = torch.full_like(q, float("nan"))
+    prefill_varlen(q, k, v, cu, cu, L, L, scale, out=o)
+    torch.cuda.synchronize()
+    assert not torch.isnan(o.float()).any(), "an item was skipped"
+    for s, r in ((0, 0), (0, 31), (0, 32), (0, 40000), (0, L - 1), (1, 0), (1, 12345), (1, L - 1)):
+        i = s * L + r
+        kk = k[s * L:s * L + r + 1].float().repeat_interleave(Hq // Hkv, 1)
+        vv = v[s * L:s * L + r + 1].float().repeat_interleave(Hq // Hkv, 1)
+        p_ = torch.softmax(torch.einsum("hd,khd->hk", q[i].float(), kk) * scale, -1)
+        want = torch.einsum("hk,khd->hd", p_, vv)
+        assert_close(o[i], want.cpu(), f"sequence {s} row {r}")
+
+
 def test_warmup_path_without_cache(cuda_dev):
     """_warmup_model (model_runner.py:102-113): empty caches, no slots, dense attention."""
     from byox_vllm_b200.attention import Attention
