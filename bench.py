@@ -27,8 +27,8 @@ What one line carries besides the contract's keys:
   extra         (N=1) kernel-level rooflines the headline shape does not show: c3 = batch 128 x
                 ctx 4096 (the "batch >= 64, ctx >= 4k" target), c4 per-rank shape with the shared
                 prefix (cascade), c5 corners, the TP=8 per-rank shape of c2, varlen prefill
-                (tensor pipe), store_kvcache (HBM), each beside flash-attn / the reference's
-                Triton scatter.
+                (tensor pipe), store_kvcache (HBM), the fused q/k norm + RoPE + store pass (HBM),
+                each beside flash-attn / the reference's Triton scatter / its norm + RoPE chain.
   engine_e2e    (N=1) the unmodified reference engine (baseline/_ref) on BASELINE config 2 end to
                 end (tools/e2e_nanovllm.py): reference attention vs the drop-in at the frozen
                 Attention.forward boundary vs the drop-in with every (f) row enabled.
@@ -36,7 +36,7 @@ What one line carries besides the contract's keys:
 
 `--impl reference` times the CPU restatement of the same path (oracle/, the reference has no
 CPU attention path of its own and is pure Python + CUDA-only wheels) on the host cores.
-`--workload prefill|store|c4|c5|tp8` print the corresponding extra block alone.
+`--workload prefill|store|c4|c5|tp8|qkv` print the corresponding extra block alone.
 """
 from __future__ import annotations
 
@@ -60,7 +60,7 @@ WORKLOADS = {
     "c2": dict(model="Qwen3-0.6B", layers=28, Hq=16, Hkv=8, batch=256, ctx="bench"),
     "c3": dict(model="Qwen3-8B", layers=36, Hq=32, Hkv=8, batch=128, ctx=4096),
 }
-EXTRA_ONLY = ("prefill", "store", "c4", "c5", "tp8")
+EXTRA_ONLY = ("prefill", "store", "c4", "c5", "tp8", "qkv")
 D, BLOCK = 128, 256
 GROUP_LAYERS = 4          # layers per host->device slab / captured graph of the e2e leg
 CPU_SAMPLE_SEQS = 64      # sequences of the CPU legs' sample (both legs use the same one)
@@ -702,6 +702,74 @@ def extra_store(N, Hq, Hkv):
     return rec
 
 
+def extra_qkv(N, Hq, Hkv):
+    """SURVEY §8f-4, prefill-size pass: q/k RMSNorm + RoPE + KV scatter on the raw qkv_proj output
+    in ONE launch, beside the reference's chain (its own RMSNorm x 2 and RotaryEmbedding modules,
+    torch.compile'd as shipped, + its Triton store_kvcache: four launches)."""
+    from byox_vllm_b200 import qkv_attention as fused
+
+    eps, max_pos = 1e-6, 40960
+    g = torch.Generator(device="cuda").manual_seed(N + Hq)
+    qkv = torch.empty(N, (Hq + 2 * Hkv) * D, dtype=torch.bfloat16,
+                      device="cuda").normal_(generator=g)
+    pos = torch.randint(0, max_pos, (N,), generator=g, device="cuda")
+    nb = (N + BLOCK - 1) // BLOCK * 2
+    kc = torch.zeros(nb, BLOCK, Hkv, D, dtype=torch.bfloat16, device="cuda")
+    vc = torch.zeros_like(kc)
+    slots = torch.randperm(nb * BLOCK, generator=g, device="cuda")[:N].to(torch.int32)
+    wq = torch.empty(D, dtype=torch.bfloat16, device="cuda").normal_(1.0, 0.25, generator=g)
+    wk = torch.empty(D, dtype=torch.bfloat16, device="cuda").normal_(1.0, 0.25, generator=g)
+    inv = 1.0 / (1e6 ** (torch.arange(0, D, 2, device="cuda").float() / D))
+    fr = torch.arange(max_pos, device="cuda").float()[:, None] * inv[None]
+    cache = torch.cat([fr.cos(), fr.sin()], dim=-1).contiguous()  # rotary_embedding.py:27-35
+    work = qkv.clone()
+    # algorithmic bytes: row read + q_out + k in place (dense prefill reads it) + K/V cache rows
+    alg = N * ((Hq + 2 * Hkv) * 256 + Hq * 256 + Hkv * 256 + 2 * Hkv * 256 + 12)
+    ms = timed_call(lambda: fused.qk_norm_rope_store(work, pos, wq, wk, eps, cache, Hq, Hkv, D,
+                                                     k_cache=kc, v_cache=vc, slot_mapping=slots),
+                    iters=10)
+    pk, pk_kind = peaks()
+    rec = {"workload": f"q/k norm + RoPE + KV store, {N} tokens x heads {Hq}/{Hkv}", "bound": "hbm",
+           "ms_per_launch": ms, "algorithmic_bytes_per_launch": alg, "achieved": alg / ms / 1e6,
+           "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": alg / ms / 1e6 / pk["hbm_gbs"],
+           "peak_kind": pk_kind, "timing": "one call, L2 flushed before each, CUDA events, median of 10"}
+    mods, why = load_reference_attention()
+    try:
+        if not mods:
+            raise ImportError(why)
+        import importlib
+
+        ln = importlib.import_module("nanovllm.layers.layernorm")
+        ro = importlib.import_module("nanovllm.layers.rotary_embedding")
+        torch.set_default_device("cuda")
+        try:
+            rope = ro.RotaryEmbedding(D, D, max_pos, 1e6)
+            torch.set_default_dtype(torch.bfloat16)
+            qn, kn = ln.RMSNorm(D, eps), ln.RMSNorm(D, eps)
+        finally:
+            torch.set_default_dtype(torch.float32)
+            torch.set_default_device("cpu")
+        qn.weight.data.copy_(wq)
+        kn.weight.data.copy_(wk)
+        kc2, vc2 = torch.zeros_like(kc), torch.zeros_like(vc)
+
+        def ref():
+            q, k, v = qkv.split([Hq * D, Hkv * D, Hkv * D], dim=-1)
+            q, k, v = q.view(-1, Hq, D), k.view(-1, Hkv, D), v.view(-1, Hkv, D)
+            q, k = rope(pos, qn(q), kn(k))
+            mods[0].store_kvcache(k, v, kc2, vc2, slots)
+            return q
+
+        ms_ref = timed_call(ref, iters=10)
+        rec.update(reference_chain_ms=ms_ref, vs_reference=ms_ref / ms,
+                   v_cache_bit_equal=bool(torch.equal(vc, vc2)))
+    except Exception as e:  # torch.compile / triton not usable on this box
+        rec["reference_unavailable"] = f"{type(e).__name__}: {str(e)[:200]}"
+    del qkv, work, kc, vc
+    torch.cuda.empty_cache()
+    return rec
+
+
 def run_extras(which):
     out = {}
     with torch.inference_mode():
@@ -727,6 +795,9 @@ def run_extras(which):
                     ("4x4096", [4096] * 4, None, 32, 8), ("1x16384", [16384], None, 32, 8),
                     ("32x(7680+512)", [8192] * 32, [7680] * 32, 8, 1)):
                 out[f"prefill_{name}"] = extra_prefill(name, lens, cached, Hq, Hkv)
+        if "qkv" in which:
+            out["qkv_prep_16384_32_8"] = extra_qkv(16384, 32, 8)
+            out["qkv_prep_16384_8_1"] = extra_qkv(16384, 8, 1)
         if "store" in which:
             out["store_16384x8"] = extra_store(16384, 32, 8)
             out["store_16384x1"] = extra_store(16384, 4, 1)
@@ -846,7 +917,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS) + list(EXTRA_ONLY))
     ap.add_argument("--extras", default=None,
-                    help="comma list of extra blocks (c3,c4,c5,tp8,prefill,store) or 'none'; "
+                    help="comma list of extra blocks (c3,c4,c5,tp8,prefill,store,qkv) or 'none'; "
                          "default: all at N=1, none at N>1")
     ap.add_argument("--engine", default=None, choices=["on", "off"],
                     help="run the reference-engine e2e arms (default: on at N=1; "
@@ -885,7 +956,7 @@ def main():
                 line["extra"] = run_extras(set(args.extras.split(",")))
             print(json.dumps(line), flush=True)
         elif rank == 0:
-            extras = args.extras or "c3,c4,c5,tp8,prefill,store"
+            extras = args.extras or "c3,c4,c5,tp8,prefill,store,qkv"
             if extras != "none":
                 line["extra"] = run_extras(set(extras.split(",")))
             engine = args.engine or ("off" if os.environ.get("B200_BENCH_ENGINE") == "0" else "on")
