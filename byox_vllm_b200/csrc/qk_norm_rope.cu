@@ -128,6 +128,66 @@ qk_norm_rope_store_kernel(const QkNormRopeParams p, uint32_t qk_blocks, uint32_t
 
 
 // ---------------------------------------------------------------------------------------------
+// Narrow rows (tensor-parallel shards: Hq + 2 Hkv <= kTokenRows heads per token, e.g. 8/1 at
+// TP = 8): a half-warp takes ONE WHOLE TOKEN - every q, k and v head row, all loads issued up
+// front (2.5 KiB in flight per half-warp at 8/1), position / slot / cos-sin row fetched once per
+// token instead of once per group of 4 heads, no idle lanes in a partly filled head group and no
+// separate v blocks. Same arithmetic (norm_rope_row16), bit-identical results.
+constexpr int kTokenRows = 12;
+
+template <bool kHasNorm>
+__global__ void __launch_bounds__(kThreads, 2)
+qk_norm_rope_token_kernel(const QkNormRopeParams p) {
+    const int c = threadIdx.x & 15;
+    const uint32_t Hq = p.num_q_heads, Hkv = p.num_kv_heads, Hqk = Hq + Hkv, R = Hqk + Hkv;
+    uint32_t tok = (blockIdx.x * kThreads + threadIdx.x) >> 4;
+    const bool live = tok < static_cast<uint32_t>(p.n_tokens);
+    if (!live) tok = 0;  // the other half of the warp still needs this half in its shuffles
+    const float* cs_row = cos_sin_row(p.nr, tok);  // head of the only dependent load chain
+    const uint8_t* src = static_cast<const uint8_t*>(p.qkv) +
+                         static_cast<int64_t>(tok) * p.qkv_row_stride * 2 + c * 16;
+    uint4 raw[kTokenRows];
+#pragma unroll
+    for (int u = 0; u < kTokenRows; ++u)
+        if (u < R) raw[u] = ld_v4(src + u * 256);
+    uint4 wq = make_uint4(0, 0, 0, 0), wk = wq;
+    if (kHasNorm) {
+        wq = *reinterpret_cast<const uint4*>(static_cast<const uint8_t*>(p.nr.q_weight) + c * 16);
+        wk = *reinterpret_cast<const uint4*>(static_cast<const uint8_t*>(p.nr.k_weight) + c * 16);
+    }
+    const CosSin8 cs = load_cos_sin8(cs_row, c);
+    int64_t slot = p.slot_mapping != nullptr ? p.slot_mapping[tok] : -1;
+    if (slot >= p.num_slots) slot = -1;
+    uint8_t* q_dst = static_cast<uint8_t*>(p.q_out) + static_cast<int64_t>(tok) * Hq * 256 + c * 16;
+    uint8_t* k_dst = p.k_out == nullptr
+                         ? nullptr
+                         : static_cast<uint8_t*>(p.k_out) +
+                               static_cast<int64_t>(tok) * p.k_out_row_stride * 2 + c * 16;
+    uint8_t* kc_dst =
+        slot < 0 ? nullptr : static_cast<uint8_t*>(p.k_cache) + slot * Hkv * 256 + c * 16;
+    uint8_t* vc_dst =
+        slot < 0 ? nullptr : static_cast<uint8_t*>(p.v_cache) + slot * Hkv * 256 + c * 16;
+    // arithmetic on the q / k rows with the warp converged (R, Hq, Hkv are launch-uniform)
+#pragma unroll
+    for (int u = 0; u < kTokenRows; ++u)
+        if (u < Hqk)
+            raw[u] = norm_rope_row16(raw[u], u < Hq ? wq : wk, kHasNorm, p.nr.eps, cs, c,
+                                     0xffffffffu);
+    if (!live) return;
+#pragma unroll
+    for (int u = 0; u < kTokenRows; ++u) {
+        if (u < Hq) {
+            st_u4(q_dst + u * 256, raw[u]);
+        } else if (u < Hqk) {
+            if (k_dst != nullptr) st_u4(k_dst + (u - Hq) * 256, raw[u]);
+            if (kc_dst != nullptr) st_u4(kc_dst + (u - Hq) * 256, raw[u]);
+        } else if (u < R) {
+            if (vc_dst != nullptr) st_u4(vc_dst + (u - Hqk) * 256, raw[u]);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
 // Bulk-staged variant (default for prefill-size launches): the bytes in flight are bounded by
 // shared memory instead of registers. A persistent CTA walks tokens t = blockIdx.x, + gridDim.x,
 // ...; a producer thread runs kBulkStages tokens ahead: it reads the token's position and slot,
@@ -251,7 +311,7 @@ static int normrope_mode_from_env() {
     static int mode = [] {
         const char* e = std::getenv("B200ATTN_NORMROPE");
         if (!e) return 0;
-        return e[0] == 'b' ? 1 : (e[0] == 'd' ? 2 : 0);
+        return e[0] == 'b' ? 1 : (e[0] == 'd' ? 2 : (e[0] == 'g' ? 3 : 0));
     }();
     return mode;
 }
@@ -288,6 +348,17 @@ cudaError_t launch_qk_norm_rope_store(const QkNormRopeParams& p, cudaStream_t st
         const int64_t want = static_cast<int64_t>(sm_count) * per_sm;
         const unsigned grid = static_cast<unsigned>(p.n_tokens < want ? p.n_tokens : want);
         kern<<<grid, (warps + 1) * 32, smem, stream>>>(p, stage_bytes);
+        count_launch();
+        return cudaGetLastError();
+    }
+    // B200ATTN_NORMROPE=groups keeps narrow rows on the head-group kernel below (A/B runs)
+    if (p.num_q_heads + 2 * p.num_kv_heads <= kTokenRows && p.n_tokens >= 256 && mode != 3) {
+        const unsigned grid =
+            static_cast<unsigned>((static_cast<int64_t>(p.n_tokens) * 16 + kThreads - 1) / kThreads);
+        if (p.nr.q_weight != nullptr)
+            qk_norm_rope_token_kernel<true><<<grid, kThreads, 0, stream>>>(p);
+        else
+            qk_norm_rope_token_kernel<false><<<grid, kThreads, 0, stream>>>(p);
         count_launch();
         return cudaGetLastError();
     }
