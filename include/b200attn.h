@@ -253,8 +253,12 @@ int b200attn_store_decode_cascade(const void* q, const void* key, int64_t key_ro
  *   q [total_q, num_q_heads, head_dim] contiguous; out same. Rows with no visible key get zeros.
  *   total_k = number of rows of key/value (dense; bounds the TMA tensor map), ignored when paged.
  * Kernel choice depends on host-visible sizes only: the tcgen05/TMEM kernel (rows = query token x
- * GQA group head) whenever pages are multiples of 128 tokens and the group divides 128, else the
- * mma.sync kernel (B200ATTN_PREFILL=tc|mma forces one).
+ * GQA group head) whenever pages are multiples of 128 tokens, the group divides 128 and the call
+ * has at most 1023 sequences, else the mma.sync kernel (B200ATTN_PREFILL=tc|mma forces one).
+ * The tcgen05 kernel is persistent: its grid is sized from total_q / num_seqs (an upper bound of
+ * the 256-row work items), the items are ordered by cost on the device from cu_seqlens and the
+ * running CTAs take them through the hardware work queue (clusterlaunchcontrol.try_cancel):
+ * nothing to allocate, no counter to reset, CUDA-graph capturable like every other entry point.
  */
 int b200attn_prefill_varlen(const void* q, const void* key, int64_t key_row_stride,
                             const void* value, int64_t value_row_stride, const void* k_cache,
