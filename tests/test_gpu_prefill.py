@@ -148,6 +148,40 @@ def test_prefill_more_items_than_the_sort_holds(cuda_dev):
         assert_close(o[i], want.cpu(), f"sequence {s} row {r}")
 
 
+def test_prefill_under_cuda_graph_capture_and_replay(cuda_dev):
+    """The persistent kernel (device-built schedule, hardware work queue) is captured like any other
+    launch; a replay with other lengths (same total / buffers, new cu_seqlens contents) follows the
+    device data, bit-identical to the eager call."""
+    from byox_vllm_b200.attention import prefill_varlen
+
+    dev = cuda_dev
+    Hq, Hkv, total, S = 16, 8, 3000, 6
+    g = torch.Generator(device=dev).manual_seed(9)
+    q, k, v = synth._qkv(total, Hq, Hkv, 128, g, dev)
+    cu = torch.zeros(S + 1, dtype=torch.int32, device=dev)
+    out = torch.empty_like(q)
+    scale = 128 ** -0.5
+
+    def set_lens(lens):
+        cu.copy_(torch.tensor([0] + list(__import__("itertools").accumulate(lens)),
+                              dtype=torch.int32))
+
+    set_lens([500, 500, 500, 500, 500, 500])
+    prefill_varlen(q, k, v, cu, cu, total, total, scale, out=out)  # eager warm-up (attributes)
+    torch.cuda.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        prefill_varlen(q, k, v, cu, cu, total, total, scale, out=out)
+    for lens in ([1, 2, 997, 1000, 700, 300], [3000, 0, 0, 0, 0, 0], [129, 127, 128, 1, 2614, 1]):
+        set_lens(lens)
+        out.fill_(float("nan"))
+        graph.replay()
+        torch.cuda.synchronize()
+        want = prefill_varlen(q, k, v, cu, cu, total, total, scale)
+        torch.cuda.synchronize()
+        assert torch.equal(out.view(torch.int16), want.view(torch.int16)), lens
+
+
 def test_warmup_path_without_cache(cuda_dev):
     """_warmup_model (model_runner.py:102-113): empty caches, no slots, dense attention."""
     from byox_vllm_b200.attention import Attention
