@@ -501,16 +501,6 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
                     clc_try_cancel(smem + kSmemClc + slot * 16, &bar->sched_full[slot]);
                 }
                 if (it.n_max == 0) continue;
-                if (q_it > 0) {
-                    // The Q buffer is still in use by the previous item (it is released by that
-                    // item's last S MMA): ask the L2 for this item's Q tiles now, so that the
-                    // load behind q_empty pays the L2 latency, not the HBM one.
-                    const int n_q = it.n_kv[1] > 0 ? 2 : 1;
-                    for (int i = 0; i < n_q; ++i) {
-                        tma_prefetch_l2_3d(&q_map, 0, it.q_c1, it.q_c2[i]);
-                        tma_prefetch_l2_3d(&q_map, 64, it.q_c1, it.q_c2[i]);
-                    }
-                }
                 unsigned long long* tri = nullptr;
                 if constexpr (kTrace) {
                     if (trace != nullptr && q_it < kTraceSteps)
@@ -639,7 +629,6 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
         // instead of a ring wait + ~1000 clk of cold code later.
         Item it, nxt;
         bool have = consume_item(0, bar, items, it);
-        bool early_s0 = false;  // S_0 of the item about to start was issued during the previous one
         for (int k = 0; have; ++k) {
             bool got_next = false, more = false;
             auto take_next = [&]() {
@@ -666,8 +655,7 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
             ++q_it;
             wait_bar(&bar->k_full[kv_it % kStages], (kv_it / kStages) & 1u);
             tc::fence_after_sync();
-            if (it.n_kv[0] > 0 && !early_s0) issue_s_rt(integral_constant<int, 0>{}, kv_it % kStages);
-            early_s0 = false;
+            if (it.n_kv[0] > 0) issue_s_rt(integral_constant<int, 0>{}, kv_it % kStages);
             if (it.n_kv[1] > 0) issue_s_rt(integral_constant<int, 1>{}, kv_it % kStages);
             if (lane == 0) {
                 tc::commit(&bar->k_empty[kv_it % kStages]);
@@ -720,21 +708,6 @@ prefill_tc_kernel(const __grid_constant__ CUtensorMap q_map,
                     if (kTrace && tr && i == 0) tr[3] = clock64();
                 };
                 sub_tile(integral_constant<int, 0>{});
-                // Last step: sub-tile 0 is done with this item once PV_0 is issued. If the next
-                // item's Q and first K tile have landed already, its S_0 goes out now instead of
-                // behind the wait for sub-tile 1's last P (never a blocking wait here: PV_1 must
-                // not queue behind a late Q load). Same in-order argument as inside an item.
-                if (j == n_max - 1 && more && nxt.n_max > 0 && nxt.n_kv[0] > 0 && !early_s0) {
-                    const uint32_t kvn = kv_it + 1;
-                    const bool ready = mbar_try_wait(&bar->q_full, q_it & 1u) &&
-                                       mbar_try_wait(&bar->k_full[kvn % kStages],
-                                                     (kvn / kStages) & 1u);
-                    if (__all_sync(0xffffffffu, ready)) {
-                        tc::fence_after_sync();
-                        issue_s_rt(integral_constant<int, 0>{}, kvn % kStages);
-                        early_s0 = true;
-                    }
-                }
                 sub_tile(integral_constant<int, 1>{});
                 if (lane == 0) {
                     tc::commit(&bar->v_empty[s]);

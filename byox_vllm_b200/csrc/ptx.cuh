@@ -83,15 +83,6 @@ __device__ __forceinline__ void tma_load_3d_hint(void* smem_dst, const void* map
         : "memory");
 }
 
-// Ask the L2 for a box of a tensor map without a shared-memory destination: the later TMA load of
-// the same box then pays the L2 latency instead of the HBM one.
-__device__ __forceinline__ void tma_prefetch_l2_3d(const void* map, int c0, int c1, int c2) {
-    asm volatile("cp.async.bulk.prefetch.tensor.3d.L2.global.tile [%0, {%1, %2, %3}];" ::"l"(
-                     reinterpret_cast<uint64_t>(map)),
-                 "r"(c0), "r"(c1), "r"(c2)
-                 : "memory");
-}
-
 // ----------------------------------------------------------------------------------------------
 // cp.async (LDGSTS) 16-byte copies, used where the source is not describable by one tensor map
 // ----------------------------------------------------------------------------------------------
