@@ -33,7 +33,7 @@ def main():
     txt = f"""{MARK} (one call on one B200: `pytest -m gpu`, `smoke()`, then `python bench.py`)
 
 Source: `profiles/r02_bench_c2_default.json` (the JSON line `bench.py --steps 20 --warmup 3` printed, same
-`gpurun` call as `profiles/r02_gputests.log`: 220 passed) and `profiles/r02_bench_c2_reference_arm.json`
+`gpurun` call as `profiles/r02_gputests.log`: 222 passed) and `profiles/r02_bench_c2_reference_arm.json`
 (`bench.py --impl reference`). Peaks of that pod: HBM {d['roofline']['peak']:.1f} GB/s, bf16 burst 1628.7 TF/s
 (`MEASURED_PEAKS.json`). flash-attn = the reference's own module from `baseline/_ref` / flash-attn 2.8.3 on the
 same tensors in the same process, timed the same way, never inside ours' timed region. This section is generated
