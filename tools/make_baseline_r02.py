@@ -19,8 +19,9 @@ def main():
     rows = []
     for k, v in d["extra"].items():
         rate = f"{v['achieved']:.0f} GB/s" if v["bound"] == "hbm" else f"{v['achieved']:.0f} TFLOP/s"
-        vs = v.get("vs_flash_attn") or v.get("vs_reference")
-        other = v.get("flash_attn_ms") or v.get("reference_triton_ms")
+        vs = v.get("vs_flash_attn") or v.get("vs_reference") or float("nan")
+        other = (v.get("flash_attn_ms") or v.get("reference_triton_ms") or
+                 v.get("reference_chain_ms") or float("nan"))
         rows.append(f"| `{k}` | {v.get('workload', k)} | {v['ms_per_launch'] * 1e3:.1f} | {rate} | "
                     f"{v['frac']:.2f} | {other * 1e3:.1f} | {vs:.2f}× |")
     e = d["engine_e2e"]
@@ -49,7 +50,7 @@ by `tools/make_baseline_r02.py` from the committed JSON lines.
 | `cpu_baseline` (oracle, {d['cpu_baseline']['cores']} host threads, 1 layer × 64 sequences scaled) | {d['cpu_baseline']['value']:.1f} tok/s; `--impl reference` {ref['value']:.1f} tok/s on the same sample — its `ms_per_step` ({ref['ms_per_step']:.0f} ms) is ONE sampled pass extrapolated to 28 layers × 256 sequences, which is why the driver's `fits_in_driver_run` is false for that arm by construction |
 
 `extra` block (kernel-level, L2 flushed or > L2 of independent inputs; "other" = flash-attn 2.8.3, for the store the
-reference's Triton kernel):
+reference's Triton kernel, for the qkv pass the reference's norm + RoPE + store chain):
 
 | key | workload | ours µs | achieved | of measured peak | other µs | ours ÷ other |
 |---|---|---|---|---|---|---|
