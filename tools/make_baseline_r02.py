@@ -63,6 +63,12 @@ Scaling on one 8×B200 node (torchrun, the driver's command line; `profiles/r02_
 | 1 | {d['value']:.0f} | 1.00 | {d['e2e']['value']:.0f} | 1.00 | {d['roofline']['frac']:.2f} | {d['vs_flash_attn']:.2f}× |
 """ + "\n".join(scale) + """
 
+Engine end to end at TP > 1 (unmodified `baseline/_ref`, `tools/e2e_nanovllm.py`, same `gpurun` call per row; the
+ours arms run on `install()` alone — `fast_rpc` is the product's transport — the reference arm needs the harness's
+128 MiB block, token-free decode copies and the `run` fix to take a step at all): config 2 (Qwen3-0.6B) TP=2
+reference 15 059 / frozen boundary 17 236 / all (f) rows 19 358 tok/s; TP=8 15 161 / — / 19 020; config 3
+(Qwen3-8B, 128 × (4032 + 64)) TP=2 1427 / — / 1713 tok/s, decode 7971 / — / 10 343 (`profiles/r02_e2e_*`).
+
 Round-2 changes behind these numbers: persistent prefill with hardware work stealing, compile-time MMA operands
 and an item ring (DESIGN §3.3; bench24 100 → 74 µs, 1×16384 1767 → 1707 µs), decode overlap mode with pre-wait tile
 requests (DESIGN §3.2; TP=8 per-rank shape 0.74 → 0.77–0.80 of HBM), slab-staged e2e leg (e2e/value 0.86 → 0.88,
