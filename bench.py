@@ -62,7 +62,9 @@ WORKLOADS = {
 }
 EXTRA_ONLY = ("prefill", "store", "c4", "c5", "tp8", "qkv")
 D, BLOCK = 128, 256
-GROUP_LAYERS = 4          # layers per host->device slab / captured graph of the e2e leg
+# layers per host->device slab / captured graph of the e2e leg (measured: 4 -> e2e/value 0.879,
+# 2 -> 0.895, 1 -> 0.869: below 2 the per-group host work shows)
+GROUP_LAYERS = int(os.environ.get("B200_BENCH_GROUP", "2"))
 CPU_SAMPLE_SEQS = 64      # sequences of the CPU legs' sample (both legs use the same one)
 
 
