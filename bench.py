@@ -62,9 +62,10 @@ WORKLOADS = {
 }
 EXTRA_ONLY = ("prefill", "store", "c4", "c5", "tp8", "qkv")
 D, BLOCK = 128, 256
-# layers per host->device slab / captured graph of the e2e leg (measured: 4 -> e2e/value 0.879,
-# 2 -> 0.895, 1 -> 0.869: below 2 the per-group host work shows)
-GROUP_LAYERS = int(os.environ.get("B200_BENCH_GROUP", "2"))
+# layers per host->device slab / captured graph of the e2e leg. Measured at N=1: 4 -> e2e/value
+# 0.879, 2 -> 0.895, 1 -> 0.869 (below 2 the per-group host work shows). Under tensor parallelism
+# a rank's group is N times shorter on the GPU while the host work per group stays: 4 there.
+GROUP_LAYERS = int(os.environ.get("B200_BENCH_GROUP", "0"))
 CPU_SAMPLE_SEQS = 64      # sequences of the CPU legs' sample (both legs use the same one)
 
 
@@ -322,7 +323,8 @@ def run_ours(args, w, rank, world, dev):
     # (Attention.forward per layer + its output gathered into an output slab) once its slab has
     # landed, ONE D2H of the group's outputs on a second copy stream. The step ends when the last
     # output is on the host.
-    groups = [(g0, min(g0 + GROUP_LAYERS, L)) for g0 in range(0, L, GROUP_LAYERS)]
+    group_layers = GROUP_LAYERS or (2 if world == 1 else 4)
+    groups = [(g0, min(g0 + group_layers, L)) for g0 in range(0, L, group_layers)]
     eslab = torch.empty_like(dslab)                       # device staging of the host inputs
     dout = torch.empty(L, B, 1, Hq, D, dtype=torch.bfloat16, device=dev)
     host_out = torch.empty(L, B, 1, Hq, D, dtype=torch.bfloat16).pin_memory()
@@ -413,7 +415,7 @@ def run_ours(args, w, rank, world, dev):
         },
         "e2e": {"value": B / (ms_e2e * 1e-3), "unit": "tokens/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e,
-                "path": f"pinned HOST q/k/v slab per {GROUP_LAYERS}-layer group -> device (copy "
+                "path": f"pinned HOST q/k/v slab per {group_layers}-layer group -> device (copy "
                         f"stream), captured graph of Attention.forward per group, outputs back to "
                         f"pinned host (second copy stream); H2D/D2H inside the timed region"},
         "gpu_launches": int(launches_per_step * args.steps),
