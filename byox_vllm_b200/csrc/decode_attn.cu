@@ -1140,9 +1140,8 @@ int env_int(const char* name, int dflt, int lo, int hi) {
 
 int decode_stages_from_env() {
     static int stages = [] {
-        // 0 = by grid size (6 stages when the grid has at most one CTA per SM), 2 | 3 | 6 force
-        const int s = env_int("B200ATTN_DECODE_STAGES", 0, 0, 6);
-        return (s == 0 || s == 2 || s == 3 || s == 6) ? s : 0;
+        const int s = env_int("B200ATTN_DECODE_STAGES", 3, 2, 3);
+        return s;
     }();
     return stages;
 }
@@ -1343,23 +1342,13 @@ cudaError_t launch_decode(const DecodeParams& p, const CUtensorMap& k_map, const
     if (p.f16) return launch_stream<3, false, true, true>(p, k_map, v_map, stream);  // rows engine
     if (decode_engine_rows()) {
         if (p.trace != nullptr) return launch_stream<3, true, true>(p, k_map, v_map, stream);
-        // Small grids (at most one CTA per SM: small batches, long rows cut into a few splits) are
-        // bound by what ONE CTA keeps in flight, not by HBM: a 6-stage ring (192 KiB, one CTA per
-        // SM) doubles it. Larger grids keep 3 stages and two CTAs per SM.
-        int stages = decode_stages_from_env();
-        if (stages == 0) {
-            const int64_t ctas = static_cast<int64_t>(p.num_kv_heads) * p.num_splits * p.batch;
-            const int sms = current_device_sm_count();
-            stages = ctas <= (sms > 0 ? sms : 148) ? 6 : 3;
-        }
-        switch (stages) {
+        switch (decode_stages_from_env()) {
             case 2: return launch_stream<2, false, true>(p, k_map, v_map, stream);
-            case 6: return launch_stream<6, false, true>(p, k_map, v_map, stream);
             default: return launch_stream<3, false, true>(p, k_map, v_map, stream);
         }
     }
     if (p.trace != nullptr) return launch_stream<3, true, false>(p, k_map, v_map, stream);
-    switch (decode_stages_from_env()) {  // stream engine: 2 or 3 stages
+    switch (decode_stages_from_env()) {
         case 2: return launch_stream<2, false, false>(p, k_map, v_map, stream);
         default: return launch_stream<3, false, false>(p, k_map, v_map, stream);
     }
