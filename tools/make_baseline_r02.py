@@ -68,7 +68,7 @@ ours arms run on `install()` alone — `fast_rpc` is the product's transport —
 128 MiB block, token-free decode copies and the `run` fix to take a step at all): config 2 (Qwen3-0.6B) TP=2
 reference 15 059 / frozen boundary 17 236 / all (f) rows 19 358 tok/s; TP=8 15 161 / — / 19 020; config 3
 (Qwen3-8B, 128 × (4032 + 64)) TP=1 868 / 1020 / 1064 tok/s, decode 5370 / 7087 / 7260 (1.35×), prefill 65.3k /
-75.2k / 78.7k; TP=2 1427 / — / 1713 tok/s, decode 7971 / — / 10 343; config 4's batch at TP=1
+75.2k / 78.7k; TP=2 1427 / — / 1713 tok/s, decode 7971 / — / 10 343; TP=8 2548 / — / 3104 tok/s, decode 11 831 / — / 14 724; config 4's batch at TP=1
 (Qwen3-32B, 256 × (7680 shared + 512) + 64 out, same box) **776 / — / 1478 tok/s, decode 2086 / — / 7330 (3.5×, the
 shared-prefix cascade), prefill 157.8k / — / 238.5k** (`profiles/r02_e2e_*`).
 
