@@ -74,7 +74,7 @@ shared-prefix cascade), prefill 157.8k / — / 238.5k** (`profiles/r02_e2e_*`).
 
 Round-2 changes behind these numbers: persistent prefill with hardware work stealing, compile-time MMA operands
 and an item ring (DESIGN §3.3; bench24 100 → 74 µs, 1×16384 1767 → 1707 µs), decode overlap mode with pre-wait tile
-requests (DESIGN §3.2; TP=8 per-rank shape 0.74 → 0.77–0.80 of HBM), slab-staged e2e leg (e2e/value 0.86 → 0.88,
+requests (DESIGN §3.2; TP=8 per-rank shape 0.74 → 0.77–0.80 of HBM), slab-staged e2e leg (e2e/value 0.86 → 0.90,
 N=8 e2e efficiency 0.26 → 0.60), fp16 (tests only; every BASELINE model is bf16).
 """
     p = ROOT / "BASELINE.md"
