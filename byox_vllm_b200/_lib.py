@@ -43,6 +43,7 @@ PROTOTYPES = {
         _i32, [_vp, _i64, _vp, _i64, _vp, _vp, _vp, _i32, _i32, _i64, _i32, _vp]),
     "b200attn_decode_pick_splits": (_i32, [_i32, _i32, _i32, _i32, _i32]),
     "b200attn_decode_partition_host": (_i32, [_vp, _i32, _i32, _i32, _i32, _i32, _vp, _i32]),
+    "b200attn_prefill_schedule_host": (_i32, [_vp, _vp, _i32, _i32, _i32, _vp, _i32]),
     "b200attn_debug_decode_trace": (None, [_vp]),
     "b200attn_debug_prefill_trace": (None, [_vp]),
     "b200attn_set_decode_overlap": (_i32, [_i32]),

@@ -443,6 +443,22 @@ int b200attn_decode_partition_host(const int32_t* context_lens, int32_t batch,
                                        block_size, pieces, max_pieces);
 }
 
+int b200attn_prefill_schedule_host(const int32_t* cu_seqlens_q, const int32_t* cu_seqlens_k,
+                                   int32_t num_seqs, int32_t num_q_heads, int32_t num_kv_heads,
+                                   int32_t* items, int32_t max_items) {
+    if (num_seqs < 0 || num_q_heads <= 0 || num_kv_heads <= 0 || num_q_heads % num_kv_heads != 0 ||
+        max_items < 0)
+        return fail(B200ATTN_E_BADARG, "bad sizes");
+    const int group = num_q_heads / num_kv_heads;
+    if (group > 8 || 128 % group != 0)
+        return fail(B200ATTN_E_UNSUPPORTED, "GQA group %d does not divide 128", group);
+    if (num_seqs > 0 && (!cu_seqlens_q || !cu_seqlens_k))
+        return fail(B200ATTN_E_BADARG, "null cu_seqlens");
+    if (max_items > 0 && !items) return fail(B200ATTN_E_BADARG, "null items");
+    return b200::prefill_schedule_host(cu_seqlens_q, cu_seqlens_k, num_seqs, group, items,
+                                       max_items);
+}
+
 size_t b200attn_decode_workspace_bytes(int32_t batch, int32_t num_q_heads, int32_t head_dim,
                                        int32_t num_splits, int32_t prefix_chunks) {
     if (batch <= 0 || num_q_heads <= 0 || head_dim != b200::kHeadDim) return 0;

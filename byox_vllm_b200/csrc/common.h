@@ -214,6 +214,10 @@ cudaError_t launch_prefill_tc(const PrefillParams& p, const CUtensorMap& q_map,
                               const CUtensorMap& k_map, const CUtensorMap& v_map,
                               cudaStream_t stream);
 
+// Host mirror of the kernel's item schedule (prefill_plan.cuh), see prefill_tc.cu.
+int prefill_schedule_host(const int32_t* cu_q, const int32_t* cu_k, int32_t num_seqs,
+                          int32_t group, int32_t* items, int32_t max_items);
+
 // Shared-prefix pass of the cascade decode: q_map is the decode batch q viewed as
 // (128 dims, Hq, batch) with box 64 x G x 128/G; k_map / v_map as for launch_prefill_tc.
 cudaError_t launch_cascade_prefix(const PrefillParams& p, const CUtensorMap& q_map,

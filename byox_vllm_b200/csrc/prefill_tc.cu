@@ -37,9 +37,11 @@
 //
 // Roofline: bf16 tensor pipe. Algorithmic flops = 4 * 128 * (visible q-k pairs) per q-head.
 #include "common.h"
+#include "prefill_plan.cuh"
 #include "ptx.cuh"
 #include "tcgen05.cuh"
 
+#include <algorithm>
 #include <cstdlib>
 #include <type_traits>
 
@@ -47,8 +49,8 @@ namespace b200 {
 
 namespace {
 
-constexpr int kTM = 128;                       // query rows per sub-tile (= TMEM lanes)
-constexpr int kTN = 128;                       // KV tokens per tile
+constexpr int kTM = kPrefillRows;              // query rows per sub-tile (= TMEM lanes)
+constexpr int kTN = kPrefillKvTile;            // KV tokens per tile
 constexpr int kStages = 2;                     // K ring and V ring depth
 constexpr int kHalfBytes = 128 * 128;          // [128 rows][64 dims] bf16, 128-byte rows, SW128
 constexpr int kTileBytes = 2 * kHalfBytes;     // 32 KiB: dims 0-63 | dims 64-127
@@ -68,9 +70,6 @@ constexpr float kRescaleThreshold = 8.0f;      // log2 domain
 // Item schedule (persistent varlen prefill): exclusive scan of the 256-row pairs per sequence and
 // the sorted keys, both in shared memory. Batches beyond kTcMaxSeqs take the shape fallback
 // (api.cu); beyond kTcMaxItems pairs they run unsorted.
-constexpr int kSchedKeyBits = 13;                       // item index inside a key
-constexpr uint32_t kSchedCostMax = (1u << (32 - kSchedKeyBits)) - 1;
-
 constexpr uint32_t kSmemWindowBase = 0x400;  // first 1 KiB of the window is reserved by the system
 constexpr int kSmemQ = 0;
 constexpr int kSmemK = kSmemQ + 2 * kTileBytes;
@@ -126,13 +125,6 @@ struct Item {
     int row0[2], n_kv[2], q_c2[2];
     int n_max;
 };
-
-// KV tiles the heavier sub-tile of pair `pair` of a sequence visits (the sort key).
-__device__ __forceinline__ int pair_cost(int pair, int Lq, int Lk, int toks_per_sub) {
-    const int toks_end = min(Lq, (pair * 2 + 2) * toks_per_sub);
-    const int vis = min(Lk, toks_end + (Lk - Lq));
-    return vis > 0 ? (vis + kTN - 1) / kTN : 0;
-}
 
 // clusterlaunchcontrol: ask the hardware scheduler to cancel a CTA of this grid that has not
 // started yet; the 16-byte response (cancelled? + its blockIdx) lands in shared memory and
@@ -213,8 +205,7 @@ __device__ __forceinline__ bool fetch_item(int k, const PrefillParams& p, Barrie
         }
         const int li = static_cast<int>(g / p.num_kv_heads);
         it.kvh = static_cast<int>(g - static_cast<int64_t>(li) * p.num_kv_heads);
-        const int t = bar->use_keys ? static_cast<int>(keys[li] & ((1u << kSchedKeyBits) - 1u))
-                                    : T - 1 - li;
+        const int t = bar->use_keys ? prefill_key_item(keys[li]) : T - 1 - li;
         const int32_t* cu_q = pair_start - 2 * kSchedStride;  // shared-memory copies
         const int32_t* cu_k = pair_start - kSchedStride;
         int lo = 0, hi = p.num_seqs;  // largest seq with pair_start[seq] <= t
@@ -234,14 +225,12 @@ __device__ __forceinline__ bool fetch_item(int k, const PrefillParams& p, Barrie
         // GQA packing: a 128-row sub-tile = 128/G query tokens x the G heads of one KV head
         // (row r = token r / G, head r % G; one TMA box 64 dims x G heads x 128/G tokens), so a
         // K/V tile is loaded once per KV head and short query blocks still fill the tile.
-        const int toks_per_sub = kTM / p.group;
+        const PrefillSubTiles st = prefill_sub_tiles(pair, it.Lq, it.Lk, p.group);
 #pragma unroll
         for (int i = 0; i < 2; ++i) {
-            it.row0[i] = (pair * 2 + i) * toks_per_sub;  // first query token of the sub-tile
-            const int toks_end = min(it.Lq, it.row0[i] + toks_per_sub);
-            const int vis = it.row0[i] < it.Lq ? min(it.Lk, toks_end + it.offset) : 0;
-            it.n_kv[i] = vis > 0 ? (vis + kTN - 1) / kTN : 0;  // visible keys [0, vis)
-            it.q_c2[i] = it.q_begin + it.row0[i];
+            it.row0[i] = st.row0[i];
+            it.n_kv[i] = st.n_kv[i];
+            it.q_c2[i] = it.q_begin + st.row0[i];
         }
     }
     it.q_c1 = it.kvh * p.group;
@@ -301,7 +290,7 @@ __device__ void build_schedule(const PrefillParams& p, Barriers* bar, int32_t* p
             int n = 0;
             if (s < S) {
                 const int lq = cu_q[s + 1] - cu_q[s];
-                n = lq > 0 ? (lq + toks_per_pair - 1) / toks_per_pair : 0;
+                n = prefill_pairs(lq, p.group);
             }
             int incl = n;
 #pragma unroll
@@ -333,9 +322,7 @@ __device__ void build_schedule(const PrefillParams& p, Barriers* bar, int32_t* p
             }
             const int lq = cu_q[lo + 1] - cu_q[lo];
             const int lk = cu_k[lo + 1] - cu_k[lo];
-            const uint32_t cost = min(static_cast<uint32_t>(
-                pair_cost(t - pair_start[lo], lq, lk, kTM / p.group)), kSchedCostMax - 1);
-            key = ((kSchedCostMax - 1 - cost) << kSchedKeyBits) | static_cast<uint32_t>(t);
+            key = prefill_sched_key(prefill_pair_cost(t - pair_start[lo], lq, lk, p.group), t);
         }
         keys[t] = key;
     }
@@ -1008,6 +995,50 @@ cudaError_t launch_prefill_tc(const PrefillParams& p_in, const CUtensorMap& q_ma
         return launch_tc<false, kDefaultExpEmu, true>(grid, p, q_map, k_map, v_map, stream);
     return launch_tc_emu<false>(exp_emu_from_env(kDefaultExpEmu), grid, p, q_map, k_map, v_map,
                                 stream);
+}
+
+// The kernel's schedule on the host (b200attn_prefill_schedule_host): the same functions of
+// prefill_plan.cuh on host copies of cu_seqlens; std::sort of the unique keys = the device's rank /
+// bitonic sort. items: 8 int32 per item {seq, pair, row0_0, row0_1, n_kv_0, n_kv_1, cost, sorted}
+// in the order the CTAs take them (per KV head; the kernel's global index g walks item g / Hkv
+// for KV head g % Hkv). Returns the item count per KV head (also when it exceeds max_items).
+int prefill_schedule_host(const int32_t* cu_q, const int32_t* cu_k, int32_t num_seqs,
+                          int32_t group, int32_t* items, int32_t max_items) {
+    int T = 0;
+    for (int s = 0; s < num_seqs; ++s) T += prefill_pairs(cu_q[s + 1] - cu_q[s], group);
+    const bool sorted = num_seqs > 1 && T <= kTcMaxItems;
+    uint32_t* keys = new uint32_t[T > 0 ? T : 1];
+    int32_t* seq_of = new int32_t[T > 0 ? T : 1];
+    int32_t* pair_of = new int32_t[T > 0 ? T : 1];
+    int t = 0;
+    for (int s = 0; s < num_seqs; ++s) {
+        const int lq = cu_q[s + 1] - cu_q[s], lk = cu_k[s + 1] - cu_k[s];
+        for (int pr = 0; pr < prefill_pairs(lq, group); ++pr, ++t) {
+            seq_of[t] = s;
+            pair_of[t] = pr;
+            keys[t] = prefill_sched_key(prefill_pair_cost(pr, lq, lk, group), t);
+        }
+    }
+    if (sorted) std::sort(keys, keys + T);
+    for (int li = 0; li < T && li < max_items; ++li) {
+        const int item = sorted ? prefill_key_item(keys[li]) : T - 1 - li;
+        const int s = seq_of[item];
+        const int lq = cu_q[s + 1] - cu_q[s], lk = cu_k[s + 1] - cu_k[s];
+        const PrefillSubTiles st = prefill_sub_tiles(pair_of[item], lq, lk, group);
+        int32_t* o = items + static_cast<int64_t>(li) * 8;
+        o[0] = s;
+        o[1] = pair_of[item];
+        o[2] = st.row0[0];
+        o[3] = st.row0[1];
+        o[4] = st.n_kv[0];
+        o[5] = st.n_kv[1];
+        o[6] = prefill_pair_cost(pair_of[item], lq, lk, group);
+        o[7] = sorted ? 1 : 0;
+    }
+    delete[] keys;
+    delete[] seq_of;
+    delete[] pair_of;
+    return T;
 }
 
 cudaError_t launch_cascade_prefix(const PrefillParams& p, const CUtensorMap& q_map,

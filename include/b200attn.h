@@ -271,6 +271,19 @@ int b200attn_prefill_varlen(const void* q, const void* key, int64_t key_row_stri
                             int64_t num_blocks, float scale, int32_t dtype, void* stream);
 
 /*
+ * The item schedule of the persistent tcgen05 prefill kernel, computed on the HOST from host copies
+ * of cu_seqlens_q / cu_seqlens_k with the kernel's own code (csrc/prefill_plan.cuh): no GPU
+ * needed (tests/test_prefill_schedule.py). items: 8 int32 per item
+ * {sequence, 256-row pair, first query token of sub-tile 0, of sub-tile 1, KV tiles of sub-tile 0,
+ * of sub-tile 1, cost, 1 if cost-sorted} in the order the CTAs take them, per KV head. Returns
+ * the number of items per KV head (which may exceed max_items: only max_items are written), or a
+ * negative B200ATTN_E_* code.
+ */
+int b200attn_prefill_schedule_host(const int32_t* cu_seqlens_q, const int32_t* cu_seqlens_k,
+                                   int32_t num_seqs, int32_t num_q_heads, int32_t num_kv_heads,
+                                   int32_t* items, int32_t max_items);
+
+/*
  * Fused q/k RMSNorm + neox RoPE + KV scatter over the raw QKV projection output (the steps of
  * nanovllm/models/qwen3.py:75-84 that precede the attention call). Row i of `qkv` holds
  * num_q_heads q heads, then num_kv_heads k heads, then num_kv_heads v heads of head_dim bf16.
