@@ -66,7 +66,8 @@ Scaling on one 8×B200 node (torchrun, the driver's command line; `profiles/r02_
 Engine end to end at TP > 1 (unmodified `baseline/_ref`, `tools/e2e_nanovllm.py`, same `gpurun` call per row; the
 ours arms run on `install()` alone — `fast_rpc` is the product's transport — the reference arm needs the harness's
 128 MiB block, token-free decode copies and the `run` fix to take a step at all): config 2 (Qwen3-0.6B) TP=2
-reference 15 059 / frozen boundary 17 236 / all (f) rows 19 358 tok/s; TP=8 15 161 / — / 19 020; config 3
+reference 15 059 / frozen boundary 17 236 / all (f) rows 19 358 tok/s; TP=4 15 628 / — / 20 459; TP=8 15 161 / — /
+19 020; config 3
 (Qwen3-8B, 128 × (4032 + 64)) TP=1 868 / 1020 / 1064 tok/s, decode 5370 / 7087 / 7260 (1.35×), prefill 65.3k /
 75.2k / 78.7k; TP=2 1427 / — / 1713 tok/s, decode 7971 / — / 10 343; TP=8 2548 / — / 3104 tok/s, decode 11 831 / — / 14 724; config 4's batch at TP=1
 (Qwen3-32B, 256 × (7680 shared + 512) + 64 out, same box) **776 / — / 1478 tok/s, decode 2086 / — / 7330 (3.5×, the
