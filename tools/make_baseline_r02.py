@@ -71,7 +71,9 @@ reference 15 059 / frozen boundary 17 236 / all (f) rows 19 358 tok/s; TP=4 15 6
 (Qwen3-8B, 128 × (4032 + 64)) TP=1 868 / 1020 / 1064 tok/s, decode 5370 / 7087 / 7260 (1.35×), prefill 65.3k /
 75.2k / 78.7k; TP=2 1427 / — / 1713 tok/s, decode 7971 / — / 10 343; TP=8 2548 / — / 3104 tok/s, decode 11 831 / — / 14 724; config 4's batch at TP=1
 (Qwen3-32B, 256 × (7680 shared + 512) + 64 out, same box) **776 / — / 1478 tok/s, decode 2086 / — / 7330 (3.5×, the
-shared-prefix cascade), prefill 157.8k / — / 238.5k** (`profiles/r02_e2e_*`).
+shared-prefix cascade), prefill 157.8k / — / 238.5k**; config 4 as BASELINE.json names it, **TP=8: 4825 tok/s,
+decode 12 899, prefill 1.02 M tok/s on `install()` alone** (ours arm only: the GPU budget of the round did not
+cover the reference arm at 8 GPUs) (`profiles/r02_e2e_*`).
 
 Round-2 changes behind these numbers: persistent prefill with hardware work stealing, compile-time MMA operands
 and an item ring (DESIGN §3.3; bench24 100 → 74 µs, 1×16384 1767 → 1707 µs), decode overlap mode with pre-wait tile
