@@ -12,7 +12,7 @@ from pathlib import Path
 
 LIB_PATH = Path(__file__).resolve().parent / "libb200attn.so"
 
-ABI_VERSION = 9
+ABI_VERSION = 10
 DTYPE_BF16 = 0
 DTYPE_F16 = 1
 
@@ -50,6 +50,9 @@ PROTOTYPES = {
     "b200attn_decode_workspace_bytes": (_sz, [_i32, _i32, _i32, _i32, _i32]),
     "b200attn_decode": (
         _i32, [_vp, _vp, _vp, _vp, _i64, _i32, _vp, _vp, _vp, _sz,
+               _i32, _i32, _i32, _i32, _i32, _i64, _f32, _i32, _i32, _vp]),
+    "b200attn_decode_static_scratch": (
+        _i32, [_vp, _vp, _vp, _vp, _i64, _i32, _vp, _vp,
                _i32, _i32, _i32, _i32, _i32, _i64, _f32, _i32, _i32, _vp]),
     "b200attn_store_decode": (
         _i32, [_vp, _vp, _i64, _vp, _i64, _vp, _vp, _vp, _vp, _i64, _i32, _vp, _vp, _vp, _sz,

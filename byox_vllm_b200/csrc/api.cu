@@ -213,7 +213,8 @@ static int store_decode_impl(const void* q, int64_t q_row_stride, const void* ke
                              int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim,
                              int32_t block_size, int64_t num_blocks, float scale,
                              int32_t num_splits, const int32_t* plan, int32_t prefix_chunks,
-                             int32_t dtype, void* stream, const b200::NormRopeArgs* nr) {
+                             int32_t dtype, void* stream, const b200::NormRopeArgs* nr,
+                             int32_t* own_counters = nullptr, int64_t own_count = 0) {
     if (int rc = check_attn_shape(num_q_heads, num_kv_heads, head_dim, block_size, dtype)) return rc;
     if (nr && dtype != B200ATTN_DTYPE_BF16)
         return fail(B200ATTN_E_UNSUPPORTED, "the fused q/k norm + RoPE decode is bf16 only");
@@ -322,7 +323,12 @@ static int store_decode_impl(const void* q, int64_t q_row_stride, const void* ke
         const int64_t rows =
             (rows_engine || batch < b200::kDecodeMaxBatch) ? batch : b200::kDecodeMaxBatch;
         // layout of the registered buffer: [rows * Hkv arrival counters | ... | sched[2] at the end]
-        p.split_counters = split_counters_for(rows * num_kv_heads + 2, &p.sched);
+        if (own_counters != nullptr) {  // b200attn_decode_static_scratch: sizes already checked
+            p.split_counters = own_counters;
+            p.sched = own_counters + own_count - 2;
+        } else {
+            p.split_counters = split_counters_for(rows * num_kv_heads + 2, &p.sched);
+        }
         if (p.split_counters == nullptr)
             return fail(B200ATTN_E_WORKSPACE,
                         "num_splits %d > 1 needs %lld zeroed counters registered with "
@@ -388,6 +394,91 @@ static int store_decode_impl(const void* q, int64_t q_row_stride, const void* ke
         if (e != cudaSuccess) return cuda_fail(e, "decode launch");
     }
     return 0;
+}
+
+// ---- b200attn_decode_static_scratch: split decode on library-owned scratch ------------------------
+// The partial results of cut rows and the arrival / scheduler counters of a split decode launch
+// live in this file-scope array instead of caller-provided buffers. It is part of the module image:
+// every device that loads libb200attn.so holds these 8 MiB + 16 KiB from module load to process
+// exit, whether or not the entry point is ever called.
+namespace {
+constexpr size_t kStaticPartialBytes = B200ATTN_STATIC_SCRATCH_PARTIAL_BYTES;
+constexpr int64_t kStaticCounters = B200ATTN_STATIC_SCRATCH_COUNTERS;
+constexpr size_t kStaticScratchBytes = kStaticPartialBytes + kStaticCounters * sizeof(int32_t);
+}  // namespace
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+// `g_static_scratch` names a host-side shadow here, not device memory: the address a kernel can
+// use has to be asked for, per device (each device has its own copy of the array), with that
+// device current. Resolved on the first call on a device and kept.
+static unsigned char* static_scratch_for_current_device() {
+    static std::mutex mu;
+    static unsigned char* ptrs[64] = {};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) {
+        cuda_fail(e, "cudaGetDevice");
+        return nullptr;
+    }
+    if (dev < 0 || dev >= 64) {
+        fail(B200ATTN_E_UNSUPPORTED, "device %d out of range", dev);
+        return nullptr;
+    }
+    std::lock_guard<std::mutex> lock(mu);
+    if (ptrs[dev] == nullptr) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (e != cudaSuccess || p == nullptr) {
+            cuda_fail(e, "cudaGetSymbolAddress(static decode scratch)");
+            return nullptr;
+        }
+        ptrs[dev] = static_cast<unsigned char*>(p);
+    }
+    return ptrs[dev];
+}
+
+extern "C" int b200attn_decode_static_scratch(
+    const void* q, const void* k_cache, const void* v_cache, const int32_t* block_tables,
+    int64_t table_row_stride, int32_t table_width, const int32_t* context_lens, void* out,
+    int32_t batch, int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim, int32_t block_size,
+    int64_t num_blocks, float scale, int32_t num_splits, int32_t dtype, void* stream) {
+    if (int rc = check_attn_shape(num_q_heads, num_kv_heads, head_dim, block_size, dtype)) return rc;
+    if (batch < 0 || num_splits < 1) return fail(B200ATTN_E_BADARG, "negative or zero size");
+    if (batch == 0) return 0;
+    unsigned char* scratch = nullptr;
+    if (num_splits > 1) {
+        const size_t need = b200::decode_workspace_bytes(batch, num_q_heads, num_splits, 0);
+        if (need > kStaticPartialBytes)
+            return fail(B200ATTN_E_WORKSPACE,
+                        "batch %d x %d q heads x %d splits needs %zu B of partials; the built-in "
+                        "scratch holds %zu B (use b200attn_decode with a caller workspace)",
+                        batch, num_q_heads, num_splits, need, kStaticPartialBytes);
+        const int64_t counters = static_cast<int64_t>(batch) * num_kv_heads + 2;
+        if (counters > kStaticCounters)
+            return fail(B200ATTN_E_WORKSPACE,
+                        "batch %d x %d KV heads needs %lld counters; the built-in scratch holds %lld "
+                        "(use b200attn_decode with b200attn_set_split_counters)",
+                        batch, num_kv_heads, static_cast<long long>(counters),
+                        static_cast<long long>(kStaticCounters));
+        scratch = static_scratch_for_current_device();
+        if (scratch == nullptr) return B200ATTN_E_DRIVER;  // message already set
+        // The counters must read zero when the kernel starts. The kernel leaves them at zero, but
+        // an aborted launch (or a racing one) may not have: clear them in stream order each call.
+        // The partials need no clearing (every slot is written before the merge reads it).
+        cudaError_t e = cudaMemsetAsync(scratch + kStaticPartialBytes, 0,
+                                        kStaticCounters * sizeof(int32_t),
+                                        static_cast<cudaStream_t>(stream));
+        if (e != cudaSuccess) return cuda_fail(e, "cudaMemsetAsync(static decode counters)");
+    }
+    return store_decode_impl(q, static_cast<int64_t>(num_q_heads) * head_dim, nullptr, 0, nullptr,
+                             0, nullptr, const_cast<void*>(k_cache), const_cast<void*>(v_cache),
+                             block_tables, table_row_stride, table_width, context_lens, out,
+                             scratch, scratch ? kStaticPartialBytes : 0, batch, num_q_heads,
+                             num_kv_heads, head_dim, block_size, num_blocks, scale, num_splits,
+                             nullptr, 0, dtype, stream, nullptr,
+                             scratch ? reinterpret_cast<int32_t*>(scratch + kStaticPartialBytes)
+                                     : nullptr,
+                             kStaticCounters);
 }
 
 

@@ -48,7 +48,7 @@
 extern "C" {
 #endif
 
-#define B200ATTN_ABI_VERSION 9
+#define B200ATTN_ABI_VERSION 10
 
 #define B200ATTN_DTYPE_BF16 0
 #define B200ATTN_DTYPE_F16 1
@@ -180,6 +180,51 @@ int b200attn_decode(const void* q, const void* k_cache, const void* v_cache,
                     int32_t batch, int32_t num_q_heads, int32_t num_kv_heads, int32_t head_dim,
                     int32_t block_size, int64_t num_blocks, float scale, int32_t num_splits,
                     int32_t dtype, void* stream);
+
+/*
+ * Split paged decode for callers that have no device memory to give. No counterpart in the
+ * reference (flash_attn_with_kvcache allocates its split-KV accumulators through torch itself).
+ *
+ * b200attn_decode with num_splits > 1 needs two pieces of scratch from its caller: the fp32
+ * workspace for the partial results of cut rows, and the zeroed counters registered with
+ * b200attn_set_split_counters. Some callers cannot supply them. An engine that has already handed
+ * every free byte of HBM to its KV cache (nanovllm sizes the cache from what is left after warm-up,
+ * engine/model_runner.py:114-140) gets an out-of-memory error from any later allocation. A plugin
+ * called inside another framework's stream capture must not allocate at all. A binding from a
+ * language without a device allocator (cgo, JNI, N-API) has only the buffers it was handed. For
+ * them this entry point computes exactly what b200attn_decode computes (same arguments, minus the
+ * workspace pair; same kernel) with the scratch taken from an array built into the library image.
+ * It calls no cudaMalloc / cudaFree and no allocating library routine.
+ *
+ * Limits (checked; beyond them the call fails with B200ATTN_E_WORKSPACE and a message that names
+ * the sizes - use b200attn_decode with your own buffers then):
+ *     b200attn_decode_workspace_bytes(batch, num_q_heads, head_dim, num_splits, 0)
+ *                                        <= B200ATTN_STATIC_SCRATCH_PARTIAL_BYTES   (8 MiB)
+ *     batch * num_kv_heads + 2           <= B200ATTN_STATIC_SCRATCH_COUNTERS        (4096;
+ *                                        implied by the first limit today, checked all the same)
+ * num_splits == 1 uses no scratch and has no limit. The price of the convenience: every GPU on
+ * which the library is loaded carries the 8 MiB + 16 KiB array until the process exits, used or not.
+ *
+ * First call on a device: the library looks up the device address of the array (with that device
+ * current; one driver query, result kept per device). Make that first call outside any stream
+ * capture. Later calls only enqueue a 16 KiB memset of the counters and the kernel on `stream`.
+ *
+ * Sharing: there is ONE array per device. Every call on that device uses it, the counters are
+ * cleared at the start of each call and the partials keep whatever the previous call left (the
+ * kernel writes each slot before it reads it, so stale partials are harmless). Two calls whose GPU
+ * work can overlap - different streams without an event between them, or two host threads - race on
+ * it and produce wrong rows without any error. Keep calls on one device in stream order. The array
+ * is separate from the buffer of b200attn_set_split_counters: this entry point neither needs nor
+ * disturbs that registration.
+ */
+#define B200ATTN_STATIC_SCRATCH_PARTIAL_BYTES (8u << 20)
+#define B200ATTN_STATIC_SCRATCH_COUNTERS 4096
+int b200attn_decode_static_scratch(const void* q, const void* k_cache, const void* v_cache,
+                                   const int32_t* block_tables, int64_t table_row_stride,
+                                   int32_t table_width, const int32_t* context_lens, void* out,
+                                   int32_t batch, int32_t num_q_heads, int32_t num_kv_heads,
+                                   int32_t head_dim, int32_t block_size, int64_t num_blocks,
+                                   float scale, int32_t num_splits, int32_t dtype, void* stream);
 
 /*
  * Fused decode step of one layer in ONE launch: scatter this step's K/V rows (as
