@@ -577,8 +577,17 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
         if (item_live) iter.init(st, item);
         int pre_item = 0;        // lane 0: the number requested from sched[0]
         bool pre_valid = false;  // a request is outstanding (warp-uniform)
+        // Overlap mode: the preceding grid may be another decode launch that is still drawing
+        // items from sched[0] (and whose last CTA resets it). The counter belongs to the stream
+        // order: no request goes out before the wait. A CTA whose first item is an empty padding
+        // row (ctx == 0) asks for its next item before it has issued a tile, i.e. in the prologue.
+        bool waited = !p.overlap;
         auto request_item = [&]() {
             if (dynamic && !pre_valid) {
+                if (!waited) {
+                    grid_dependency_wait();
+                    waited = true;
+                }
                 if (lane == 0) pre_item = static_cast<int>(gridDim.x) + atomicAdd(p.sched, 1);
                 pre_valid = true;
             }
@@ -653,7 +662,6 @@ decode_stream_kernel(const __grid_constant__ CUtensorMap k_map,
         // steps, so its loads go out while the preceding grid (the previous layer's decode) is
         // still draining: the ring is full when the consumers are released, and the first-tile
         // latency (~2-4 us of a ~20 us launch at the TP=8 shapes) is off the critical path.
-        bool waited = !p.overlap;
         if (!kRows && !waited) {
             grid_dependency_wait();
             waited = true;

@@ -389,6 +389,82 @@ def test_overlap_mode_back_to_back(cuda_dev, shape):
         set_decode_overlap(prev)
 
 
+@pytest.mark.parametrize("fused", [False, True], ids=["decode", "store_decode"])
+@pytest.mark.parametrize("shape", [(32, 16, 8), (48, 4, 1), (3, 32, 8)],
+                         ids=["graph32", "ragged48", "cut3"])
+def test_overlap_mode_adjacent_launches_with_padding_rows(cuda_dev, shape, fused):
+    """The chain bench.py's layer loop and the 1024-row chunk loop build: decode launches with
+    NOTHING between them, so each one really is a programmatic dependent of the previous decode
+    (in test_overlap_mode_back_to_back the q copy sits between them and serialises the pair). The
+    batch is a CUDA-graph batch that is not full: rows with context_lens == 0 in front, in the
+    middle and at the end, so some CTAs start on an empty row and ask for more work in their
+    prologue. Ten launches on ten pre-staged q (and, fused, ten new K/V rows for the same slots),
+    eagerly and from one graph: bit-equal to the same launches with overlap off."""
+    from byox_vllm_b200.attention import paged_decode, set_decode_overlap
+
+    B, Hq, Hkv = shape
+    rng = np.random.default_rng(11)
+    ctx = rng.integers(1, 2500, size=B).tolist() if B > 3 else [9000, 1, 5000]
+    c = synth.decode_case(B, ctx, Hq, Hkv, seed=78)
+    d = to_dev(c, cuda_dev)
+    m = d["meta"]
+    lens = m["context_lens"].clone()
+    slots = m["slot_mapping"].clone()
+    if B > 3:
+        pad = [0, 1, 2, B // 2, B // 2 + 1, B - 3, B - 2, B - 1]
+    else:
+        pad = [1]
+    lens[pad] = 0
+    slots[pad] = -1
+    g = torch.Generator(device=cuda_dev).manual_seed(4)
+    qs = [torch.empty_like(d["q"]).normal_(generator=g) for _ in range(10)]
+    ks = [torch.empty_like(d["k"]).normal_(generator=g) for _ in range(10)]
+    vs = [torch.empty_like(d["k"]).normal_(generator=g) for _ in range(10)]
+    k0, v0 = d["k_cache"].clone(), d["v_cache"].clone()
+
+    def run_all(outs):
+        for i in range(10):
+            kw = dict(key=ks[i], value=vs[i], slot_mapping=slots) if fused else {}
+            paged_decode(qs[i], d["k_cache"], d["v_cache"], lens, m["block_tables"], c.scale,
+                         out=outs[i], **kw)
+
+    def fresh():
+        d["k_cache"].copy_(k0)
+        d["v_cache"].copy_(v0)
+        torch.cuda.synchronize()
+        return [torch.full_like(qs[0], float("nan")) for _ in range(10)]
+
+    prev = set_decode_overlap(False)
+    try:
+        want = fresh()
+        run_all(want)
+        torch.cuda.synchronize()
+        for i in (0, 9):
+            assert torch.isfinite(want[i].float()).all()
+            assert torch.count_nonzero(want[i][pad]) == 0
+        if not fused:
+            assert_close(want[7], orc.paged_decode_ref(qs[7].cpu(), c.k_cache, c.v_cache,
+                                                       lens.cpu(), c.meta["block_tables"], c.scale),
+                         "overlap off vs oracle")
+        set_decode_overlap(True)
+        got = fresh()
+        run_all(got)
+        torch.cuda.synchronize()
+        for i in range(10):
+            assert torch.equal(got[i], want[i]), f"eager launch {i} differs with overlap on"
+        got = fresh()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            run_all(got)
+        for _ in range(3):
+            graph.replay()
+        torch.cuda.synchronize()
+        for i in range(10):
+            assert torch.equal(got[i], want[i]), f"graph launch {i} differs with overlap on"
+    finally:
+        set_decode_overlap(prev)
+
+
 def test_stream_engine_passes_the_decode_and_cascade_tests():
     """The persistent stream engine (B200ATTN_DECODE_ENGINE=stream; the engine is read once per
     process) against the same parity tests as the default rows engine."""
