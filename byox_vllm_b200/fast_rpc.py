@@ -11,7 +11,8 @@ per sequence (model_runner.py:206-226), a prefill step `num_tokens, num_cached_t
 and the token ids that are not cached (:160-204). This module replaces the transport, not the
 protocol (same shared-memory block name, same events, same `call()` dispatch):
 
-  wire format   int32 header {payload bytes, kind, batch, aux}, then
+  wire format   int32 header {magic, payload bytes, kind, batch, aux, 0, 0, 0} + 32 flag bytes
+                (flag r = 1 once rank r has attached the block through THIS module), then
                 kind 1 (decode)   last_token[B] | num_tokens[B] | table_len[B] | blocks[sum]  int32
                                   - exactly fast_meta.pack_decode_record, so a worker hands it to
                                   its DecodeMetaStager without building a single Python object
@@ -24,8 +25,20 @@ protocol (same shared-memory block name, same events, same `call()` dispatch):
                 one formats `logits.shape`, and logits is None on every rank > 0, so the unmodified
                 reference dies on its first step at any tensor-parallel size > 1.
 
-bind() / unbind() rebinding is done by install.install(fast_rpc=True) (default on; it only acts
-when world_size > 1). Pure host code: no CUDA, no torch tensors on the wire.
+  mixed installs    the block is NOT readable by the reference's _read_shm (and the reference's
+                pickles are not readable here). A spawned rank that did not re-run install() - the
+                launcher called it under `if __name__ == "__main__":` - would unpickle garbage and
+                die while rank 0 hangs in NCCL. So every call starts with MAGIC (a reader that finds
+                anything else says so), every bound worker raises its flag byte when it attaches the
+                block, and rank 0's first _write_shm waits for all flags and otherwise raises with
+                the instruction to call install() at module top level. (Falling back to the pickle
+                transport would not help such a rank: the reference's own `run` cannot take a step
+                on ranks > 0, see above.)
+
+bind() / unbind() rebinding is done by install.install(fast_rpc=True) (default on). The transport
+(_write_shm / _read_shm, the block size) only runs when world_size > 1; `ModelRunner.run` and the
+`__init__` wrapper that records the engine limits are replaced at every tensor-parallel size, 1
+included. Pure host code: no CUDA, no torch tensors on the wire.
 """
 from __future__ import annotations
 
@@ -36,8 +49,11 @@ from itertools import chain
 import numpy as np
 
 KIND_PICKLE, KIND_DECODE, KIND_PREFILL = 0, 1, 2
-HEADER_INTS = 4  # payload bytes, kind, batch, aux (prefill: number of uncached token ids)
-HEADER_BYTES = HEADER_INTS * 4
+MAGIC = 0x42323A02  # "B2:" + wire-format version 2; first word of every call
+HEADER_INTS = 16  # magic, payload bytes, kind, batch, aux (prefill: uncached token ids), 3 spare,
+HEADER_BYTES = HEADER_INTS * 4  # then bytes 32..63: one "attached through fast_rpc" flag per rank
+FLAGS_AT, MAX_RANKS = 32, 32
+ATTACH_TIMEOUT_S = 60.0
 
 
 # ---- records ------------------------------------------------------------------------------------
@@ -183,7 +199,7 @@ def write_call(buf, method_name: str, args: tuple) -> int:
         if HEADER_BYTES + n > len(buf):
             raise OverflowError(f"pickled call of {n} bytes exceeds the {len(buf)}-byte block")
         buf[HEADER_BYTES:HEADER_BYTES + n] = data
-    head[:] = (n, kind, batch, aux)
+    head[:5] = (MAGIC, n, kind, batch, aux)  # bytes 32..63 are the workers' flags: not ours
     return HEADER_BYTES + n
 
 
@@ -191,7 +207,13 @@ def read_call(buf, block_size: int):
     """-> (method_name, args). Compact records come back as the worker-side method names
     `_b200_run_decode` / `_b200_run_prefill` with a private copy of the record."""
     words = np.frombuffer(buf, dtype=np.int32)
-    n, kind, batch, aux = words[:HEADER_INTS].tolist()
+    magic, n, kind, batch, aux = words[:5].tolist()
+    if magic != MAGIC:
+        raise RuntimeError(
+            f"nanovllm shared-memory block starts with {magic & 0xFFFFFFFF:#010x}, not the fast_rpc "
+            f"magic {MAGIC:#010x}: rank 0 writes the reference's pickle format (or another "
+            "fast_rpc version). Call byox_vllm_b200.install() at module top level of the "
+            "launcher so that every spawned rank and rank 0 bind the same transport.")
     if kind == KIND_PICKLE:
         method_name, *args = pickle.loads(bytes(buf[HEADER_BYTES:HEADER_BYTES + n]))
         return method_name, args
@@ -208,9 +230,41 @@ _ORIG: dict = {}
 _STATS = {"steps": 0, "bytes": 0, "host_s": 0.0}
 
 
+def mark_attached(buf, rank: int) -> None:
+    """A worker that attached the block through this module says so (flag byte of its rank)."""
+    if 0 < rank < MAX_RANKS:
+        buf[FLAGS_AT + rank] = 1
+
+
+def missing_ranks(buf, world_size: int) -> list[int]:
+    return [r for r in range(1, min(world_size, MAX_RANKS)) if buf[FLAGS_AT + r] != 1]
+
+
+def wait_for_workers(buf, world_size: int, timeout_s: float | None = None) -> None:
+    """Rank 0, before its first call: every worker must have attached through fast_rpc. Workers
+    attach right after the barrier rank 0 has just left (model_runner.py:43-49), so this returns
+    at once in a consistent install; otherwise it raises instead of letting rank 0 hang in NCCL."""
+    deadline = time.monotonic() + (ATTACH_TIMEOUT_S if timeout_s is None else timeout_s)
+    while True:
+        missing = missing_ranks(buf, world_size)
+        if not missing:
+            return
+        if time.monotonic() >= deadline:
+            raise RuntimeError(
+                f"fast_rpc: tensor-parallel rank(s) {missing} did not attach the shared-memory "
+                "block through byox_vllm_b200.fast_rpc: they run the reference's transport and "
+                "cannot read this format. Call byox_vllm_b200.install() at module top level of the "
+                "launcher script (not under `if __name__ == '__main__':`) so that spawned ranks "
+                "re-apply it, or pass install(fast_rpc=False) on every rank.")
+        time.sleep(0.002)
+
+
 def _write_shm(self, method_name, *args):
     """ModelRunner._write_shm (model_runner.py:93-100) with the compact wire format."""
     assert self.world_size > 1 and self.rank == 0
+    if not getattr(self, "_b200_rpc_workers_ok", False):
+        wait_for_workers(self.shm.buf, self.world_size)
+        self._b200_rpc_workers_ok = True
     t0 = time.perf_counter()
     used = write_call(self.shm.buf, method_name, args)
     _STATS["host_s"] += time.perf_counter() - t0
@@ -285,6 +339,8 @@ def _sized_shared_memory(mr_module):
             if create:
                 size = max(size, mr_module._b200_rpc_block_bytes)
             super().__init__(name=name, create=create, size=size)
+            if not create:  # a worker (model_runner.py:48): tell rank 0 this rank speaks fast_rpc
+                mark_attached(self.buf, getattr(mr_module, "_b200_rpc_rank", 0))
 
     return SizedSharedMemory
 
@@ -302,6 +358,7 @@ def bind(mr_module) -> None:
         mr_module._b200_rpc_block_bytes = block_bytes(
             config.max_num_seqs, config.max_model_len, config.kvcache_block_size,
             config.max_num_batched_tokens)
+        mr_module._b200_rpc_rank = rank  # one ModelRunner per process (llm_engine.py:24-31)
         orig_init(self, config, rank, event)
 
     mr_module._b200_rpc_block_bytes = 1 << 20

@@ -20,7 +20,8 @@ The reference binds the op by name: `from nanovllm.layers.attention import Atten
      fast_meta.prepare_decode / run_model: the decode metadata is expanded on the device into the
      CUDA-graph input buffers by one copy + one launch.
   6. (RPC half, `fast_rpc`, default on; B200ATTN_FAST_RPC=0 or fast_rpc=False
-     disables; acts only at tensor_parallel_size > 1) rebinds ModelRunner._write_shm / _read_shm /
+     disables; the transport runs only at tensor_parallel_size > 1, the `run` / `__init__`
+     replacements at every size; EVERY rank must bind it - rank 0 checks and raises) rebinds ModelRunner._write_shm / _read_shm /
      run and the shared-memory block size (engine/model_runner.py:44,57-65,85-100) to
      fast_rpc: rank 0 ships a compact int32 record per step instead of pickled Sequence objects,
      in a block sized from the engine's limits; `run` loses the debug f-string that dereferences

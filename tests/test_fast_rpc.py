@@ -178,6 +178,7 @@ def test_block_sized_from_engine_limits_and_fallbacks():
 def _worker(name, size, event, n_calls, q):
     """Rank > 0: ModelRunner._loop's read side (model_runner.py:78-91) on the bound drop-in."""
     shm = SharedMemory(name=name)
+    rpc.mark_attached(shm.buf, 1)  # what the bound SharedMemory subclass does on attach
 
     class Runner:
         world_size, rank, block_size = 2, 1, BLOCK
@@ -240,6 +241,56 @@ def test_two_processes_through_shared_memory():
     finally:
         shm.close()
         shm.unlink()
+
+
+def test_mixed_installs_fail_loudly():
+    """A rank that did not bind fast_rpc cannot read the block and the reference's pickles cannot
+    be read here: a reader says what it found instead of unpickling garbage, and rank 0 refuses to
+    send its first call until every worker has raised its flag (instead of hanging in NCCL later)."""
+    rng = random.Random(6)
+    block = memoryview(bytearray(rpc.block_bytes(8, 1024, BLOCK, 1024)))
+    # the reference's format (model_runner.py:93-98): length word, then the pickle
+    data = pickle.dumps(["run", [1, 2], False])
+    block[0:4] = len(data).to_bytes(4, "little")
+    block[4:4 + len(data)] = data
+    with pytest.raises(RuntimeError, match="not the fast_rpc magic"):
+        rpc.read_call(block, BLOCK)
+    rpc.write_call(block, "run", (make_seqs(rng, 3, 500), False))
+    assert int.from_bytes(block[0:4], "little") == rpc.MAGIC
+    assert rpc.read_call(block, BLOCK)[0] == "_b200_run_decode"
+    # an unbound reference reader would take MAGIC for the pickle length: far beyond any block
+    assert rpc.MAGIC > (1 << 28)
+
+    class Runner:
+        world_size, rank = 4, 0
+
+    r = Runner()
+
+    class Ev:
+        def __init__(self):
+            self.n = 0
+
+        def set(self):
+            self.n += 1
+
+    r.shm = type("Shm", (), {"buf": block})()
+    r.event = [Ev(), Ev(), Ev()]
+    rpc.mark_attached(block, 1)
+    rpc.mark_attached(block, 3)
+    assert rpc.missing_ranks(block, 4) == [2]
+    old = rpc.ATTACH_TIMEOUT_S
+    rpc.ATTACH_TIMEOUT_S = 0.05
+    try:
+        with pytest.raises(RuntimeError, match=r"rank\(s\) \[2\] did not attach"):
+            rpc._write_shm(r, "run", make_seqs(rng, 3, 500), False)
+        assert all(e.n == 0 for e in r.event)  # nothing was announced to the workers
+        rpc.mark_attached(block, 2)
+        rpc._write_shm(r, "run", make_seqs(rng, 3, 500), False)
+        assert all(e.n == 1 for e in r.event)
+        # the flags survive the header rewrite of every call
+        assert rpc.missing_ranks(block, 4) == []
+    finally:
+        rpc.ATTACH_TIMEOUT_S = old
 
 
 def test_reference_sequence_objects_and_bound_model_runner():
