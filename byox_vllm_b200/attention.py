@@ -73,29 +73,36 @@ def store_kvcache(key: torch.Tensor, value: torch.Tensor, k_cache: torch.Tensor,
     _lib.check("b200attn_store_kvcache", rc)
 
 
-_SPLIT_COUNTERS: dict[int, torch.Tensor] = {}
+_SPLIT_COUNTERS: dict[int, list[torch.Tensor]] = {}  # per device, newest (registered) last
 _SPLIT_COUNTER_SLOTS = 1 << 16  # (sequence, KV head) pairs; 256 KiB per device
 
 
-def ensure_split_counters(device: torch.device) -> None:
+def ensure_split_counters(device: torch.device, need: int = 0) -> None:
     """Register the zeroed arrival counters that let split-KV decode merge inside its own launch
     (b200attn_set_split_counters). Allocated once per device, outside any graph capture (the
     reference warms every batch size up eagerly before capturing it, model_runner.py:281), kept
-    alive for the life of the process; every launch leaves them zero."""
+    alive for the life of the process; every launch leaves them zero.
+
+    `need` = counters the coming call uses (rows x KV heads + 2). The default buffer covers every
+    batch the engine issues; an eager call beyond it (>= 65535 (sequence, KV head) pairs with an
+    explicit num_splits > 1) registers a larger buffer. Buffers already handed to the library stay
+    allocated: graphs captured earlier keep launching on them."""
     idx = device.index if device.index is not None else torch.cuda.current_device()
-    if idx in _SPLIT_COUNTERS:
+    bufs = _SPLIT_COUNTERS.setdefault(idx, [])
+    if bufs and bufs[-1].numel() >= need:
         return
     if torch.cuda.is_current_stream_capturing():
         raise RuntimeError(
             "byox_vllm_b200: the decode arrival counters must be registered before CUDA-graph "
             "capture; run one eager decode step (or attention.ensure_split_counters(device)) "
             "first, as ModelRunner's warm-up before capture does (model_runner.py:281)")
+    slots = max(_SPLIT_COUNTER_SLOTS, 1 << max(int(need) - 1, 1).bit_length())
     with torch.cuda.device(idx):
-        buf = torch.zeros(_SPLIT_COUNTER_SLOTS, dtype=torch.int32, device=device)
+        buf = torch.zeros(slots, dtype=torch.int32, device=device)
         torch.cuda.current_stream(device).synchronize()
         rc = _lib.load().b200attn_set_split_counters(buf.data_ptr(), buf.numel())
     _lib.check("b200attn_set_split_counters", rc)
-    _SPLIT_COUNTERS[idx] = buf
+    bufs.append(buf)
 
 
 def set_decode_overlap(on: bool) -> bool:
@@ -188,7 +195,7 @@ def paged_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
         assert plan.dtype == torch.int32 and plan.numel() >= 4 and plan.is_cuda
     ws, ws_bytes = None, 0
     if num_splits > 1:
-        ensure_split_counters(q.device)
+        ensure_split_counters(q.device, B * Hkv + 2)
     if num_splits > 1 or prefix_chunks > 0:
         ws_bytes = lib.b200attn_decode_workspace_bytes(B, Hq, D, num_splits, prefix_chunks)
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=q.device)

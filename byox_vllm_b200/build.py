@@ -20,7 +20,9 @@ LIB_PATH = PKG_DIR / "libb200attn.so"
 
 SOURCES = ["store_kv.cu", "decode_attn.cu", "prefill_attn.cu", "prefill_tc.cu", "cascade.cu",
            "qk_norm_rope.cu", "prepare_meta.cu", "api.cu"]
-HEADERS = ["common.h", "decode_plan.cuh", "ptx.cuh", "tcgen05.cuh", "norm_rope.cuh", "../../include/b200attn.h"]
+# every header under csrc/ (a new one is picked up without editing this file) + the C-ABI header
+HEADERS = sorted(p.name for p in CSRC.glob("*.h")) + sorted(p.name for p in CSRC.glob("*.cuh")) + \
+    ["../../include/b200attn.h"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

@@ -113,7 +113,7 @@ def qkv_decode(qkv: torch.Tensor, positions: torch.Tensor, q_weight, k_weight, e
     lib = _lib.load()
     ws, ws_bytes = None, 0
     if num_splits > 1:
-        _attn.ensure_split_counters(qkv.device)
+        _attn.ensure_split_counters(qkv.device, B * Hkv + 2)
         ws_bytes = lib.b200attn_decode_workspace_bytes(B, Hq, D, num_splits, 0)
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=qkv.device)
     rc = lib.b200attn_qkv_decode(

@@ -229,7 +229,7 @@ def test_in_launch_merge_of_cut_rows(cuda_dev, batch, ctx, Hq, Hkv, splits):
         lens[1] = 0  # padding row of a captured batch
     args = (d["q"], d["k_cache"], d["v_cache"], lens, m["block_tables"], c.scale)
     A.ensure_split_counters(cuda_dev)
-    counters = A._SPLIT_COUNTERS[cuda_dev.index or 0]
+    counters = A._SPLIT_COUNTERS[cuda_dev.index or 0][-1]
     one = A.paged_decode(*args, num_splits=1)
     torch.cuda.synchronize()
     first = None
@@ -258,7 +258,7 @@ def test_cut_rows_need_registered_counters(cuda_dev):
     d = to_dev(c, cuda_dev)
     m = d["meta"]
     A.ensure_split_counters(cuda_dev)
-    counters = A._SPLIT_COUNTERS[cuda_dev.index or 0]
+    counters = A._SPLIT_COUNTERS[cuda_dev.index or 0][-1]
     try:
         assert lib.b200attn_set_split_counters(None, 0) == 0
         with pytest.raises(_lib.B200AttnError) as e:
@@ -387,6 +387,37 @@ def test_overlap_mode_back_to_back(cuda_dev, shape):
             assert torch.equal(got[i], want[i]), f"graph launch {i} differs with overlap on"
     finally:
         set_decode_overlap(prev)
+
+
+def test_split_counters_grow_with_the_batch(cuda_dev, monkeypatch):
+    """The registered counter buffer follows the call: rows x KV heads + 2 beyond the current
+    buffer registers a larger one (an eager call with an explicit num_splits > 1 on more
+    (sequence, KV head) pairs than the default 65536 used to fail with B200ATTN_E_WORKSPACE).
+    Checked at a small scale by starting from a 64-slot default."""
+    from byox_vllm_b200 import _lib
+    from byox_vllm_b200 import attention as A
+
+    idx = cuda_dev.index or 0
+    A.ensure_split_counters(cuda_dev)
+    kept = A._SPLIT_COUNTERS.pop(idx)  # stays alive: earlier graphs may hold it
+    monkeypatch.setattr(A, "_SPLIT_COUNTER_SLOTS", 64)
+    try:
+        sizes = []
+        for B, seed in ((4, 41), (24, 42), (100, 43), (24, 44)):
+            c = synth.decode_case(B, [300 + 37 * (i % 9) for i in range(B)], 16, 8, seed=seed)
+            d = to_dev(c, cuda_dev)
+            got = _decode(d, c.scale, num_splits=2)
+            want = orc.paged_decode_ref(c.q, c.k_cache, c.v_cache, c.meta["context_lens"],
+                                        c.meta["block_tables"], c.scale)
+            assert_close(got, want, f"B={B} after counter registration")
+            sizes.append(A._SPLIT_COUNTERS[idx][-1].numel())
+            assert sizes[-1] >= B * 8 + 2
+            assert all(int(b.abs().max()) == 0 for b in A._SPLIT_COUNTERS[idx])
+        assert sizes == [64, 256, 1024, 1024]
+    finally:
+        A._SPLIT_COUNTERS[idx] = kept
+        rc = _lib.load().b200attn_set_split_counters(kept[-1].data_ptr(), kept[-1].numel())
+        _lib.check("b200attn_set_split_counters", rc)
 
 
 @pytest.mark.parametrize("fused", [False, True], ids=["decode", "store_decode"])
