@@ -524,14 +524,25 @@ def l2_flush():
     _flush_buf.zero_()
 
 
-def timed_call(fn, iters=8, warm=3):
-    """Median ms of ONE call, L2 flushed (512 MiB written) before every timed call."""
+def l2_flush_clean():
+    """l2_flush(), then a 512 MiB READ: the timed kernel's data is as cold as after l2_flush(), but
+    L2 holds clean lines. After the write-flush alone L2 is full of the flush buffer's DIRTY lines,
+    and a kernel that writes (the KV scatter) pays their write-back inside its own timed region:
+    ncu, whose cache control leaves L2 clean, times store_kvcache_kernel at 22 us where the
+    write-flushed timing says 28.7 (profiles/r03_store_full.txt)."""
+    l2_flush()
+    _flush_buf.view(torch.int32).max()
+
+
+def timed_call(fn, iters=8, warm=3, clean=False):
+    """Median ms of ONE call, L2 flushed (512 MiB written; clean=True: then 512 MiB read) before
+    every timed call."""
     for _ in range(warm):
         fn()
     torch.cuda.synchronize()
     ts = []
     for _ in range(iters):
-        l2_flush()
+        (l2_flush_clean if clean else l2_flush)()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         fn()
@@ -736,8 +747,11 @@ def extra_store(N, Hq, Hkv):
     slots = torch.randperm(nb * BLOCK, generator=g, device="cuda")[:N].to(torch.int32)
     alg = N * row * 2 * 2 * 2 + 4 * N
     ms = timed_call(lambda: store_kvcache(k, v, kc, vc, slots), iters=12)
+    ms_clean = timed_call(lambda: store_kvcache(k, v, kc, vc, slots), iters=12, clean=True)
     pk, pk_kind = peaks()
     rec = {"workload": f"store_kvcache {N} tokens x Hkv {Hkv}", "bound": "hbm", "ms_per_launch": ms,
+           "ms_per_launch_clean_l2": ms_clean,
+           "frac_clean_l2": alg / ms_clean / 1e6 / pk["hbm_gbs"],
            "algorithmic_bytes_per_launch": alg, "achieved": alg / ms / 1e6, "peak": pk["hbm_gbs"],
            "unit": "GB/s", "frac": alg / ms / 1e6 / pk["hbm_gbs"], "peak_kind": pk_kind,
            "timing": "one call, L2 flushed before each, CUDA events, median of 12"}
@@ -745,7 +759,11 @@ def extra_store(N, Hq, Hkv):
     if mods:
         kc2, vc2 = torch.zeros_like(kc), torch.zeros_like(vc)
         ms_ref = timed_call(lambda: mods[0].store_kvcache(k, v, kc2, vc2, slots), iters=12)
+        ms_ref_clean = timed_call(lambda: mods[0].store_kvcache(k, v, kc2, vc2, slots), iters=12,
+                                  clean=True)
         rec.update(reference_triton_ms=ms_ref, vs_reference=ms_ref / ms,
+                   reference_triton_ms_clean_l2=ms_ref_clean,
+                   vs_reference_clean_l2=ms_ref_clean / ms_clean,
                    bit_equal=bool(torch.equal(kc, kc2) and torch.equal(vc, vc2)))
     else:
         rec["reference_unavailable"] = why
@@ -987,7 +1005,8 @@ def emit_extras(line, extra):
     enough for a log tail); the numbers the claims rest on are copied into `roofline`."""
     print(json.dumps({"extra": extra}), flush=True)
     keep = ("ms_per_launch", "frac", "frac_of_8TBs_nominal", "vs_flash_attn",
-            "max_abs_diff_vs_flash_attn", "achieved", "unit")
+            "max_abs_diff_vs_flash_attn", "achieved", "unit", "ms_per_launch_clean_l2",
+            "frac_clean_l2", "vs_reference", "vs_reference_clean_l2")
     for src, dst in (("c3_decode_b128_ctx4096", "target_c3"), ("prefill_bench24", "prefill_bench24"),
                      ("prefill_1x16384", "prefill_1x16384"), ("store_16384x8", "store_16384x8"),
                      ("c2_decode_tp8_rank", "c2_tp8_rank")):

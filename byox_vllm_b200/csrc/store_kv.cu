@@ -100,7 +100,8 @@ cudaError_t launch_store_kvcache(const void* key, int64_t key_row_stride, const 
     }();
     static const int want_tok = [] {
         const char* e = std::getenv("B200ATTN_STORE_TOK");
-        return e && std::atoi(e) == 8 ? 8 : 4;
+        const int t = e ? std::atoi(e) : 4;
+        return (t == 1 || t == 2 || t == 8) ? t : 4;
     }();
     const bool vec32 = want_vec == 32 && row_elems % 16 == 0 && key_row_stride % 16 == 0 &&
                        value_row_stride % 16 == 0 && aligned32(key) && aligned32(value) &&
@@ -113,9 +114,15 @@ cudaError_t launch_store_kvcache(const void* key, int64_t key_row_stride, const 
     // before the first store.
     if (n_tokens >= 2048) {
         if (vec32) {
-            if (want_tok == 8) launch<8, 32>(B200_STORE_ARGS); else launch<4, 32>(B200_STORE_ARGS);
+            if (want_tok == 8) launch<8, 32>(B200_STORE_ARGS);
+            else if (want_tok == 2) launch<2, 32>(B200_STORE_ARGS);
+            else if (want_tok == 1) launch<1, 32>(B200_STORE_ARGS);
+            else launch<4, 32>(B200_STORE_ARGS);
         } else {
-            if (want_tok == 8) launch<8, 16>(B200_STORE_ARGS); else launch<4, 16>(B200_STORE_ARGS);
+            if (want_tok == 8) launch<8, 16>(B200_STORE_ARGS);
+            else if (want_tok == 2) launch<2, 16>(B200_STORE_ARGS);
+            else if (want_tok == 1) launch<1, 16>(B200_STORE_ARGS);
+            else launch<4, 16>(B200_STORE_ARGS);
         }
     } else {
         launch<1, 16>(B200_STORE_ARGS);
