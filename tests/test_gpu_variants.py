@@ -56,8 +56,7 @@ print("CHECKSUMS " + " ".join(out))
 
 def _run(env_extra):
     env = dict(os.environ)
-    for k in ("B200ATTN_STORE_VEC", "B200ATTN_STORE_TOK", "B200ATTN_NORMROPE",
-              "B200ATTN_NORMROPE_WARPS"):
+    for k in ("B200ATTN_NORMROPE", "B200ATTN_NORMROPE_WARPS"):
         env.pop(k, None)
     env.update(env_extra)
     r = subprocess.run([sys.executable, "-c", _SCRIPT.format(root=str(ROOT))], env=env,
@@ -70,7 +69,6 @@ def _run(env_extra):
 def test_kernel_variants_agree_bit_for_bit(cuda_dev):
     base = _run({})
     assert len(base) == 7
-    assert _run({"B200ATTN_STORE_VEC": "16", "B200ATTN_NORMROPE": "bulk"}) == base
-    assert _run({"B200ATTN_STORE_VEC": "32", "B200ATTN_STORE_TOK": "8",
-                 "B200ATTN_NORMROPE": "direct"}) == base
+    assert _run({"B200ATTN_NORMROPE": "bulk"}) == base
+    assert _run({"B200ATTN_NORMROPE": "direct"}) == base
     assert _run({"B200ATTN_NORMROPE": "bulk", "B200ATTN_NORMROPE_WARPS": "8"}) == base
